@@ -1,0 +1,162 @@
+"""ctypes binding of libgsr_b200.so -- the ONLY FFI layer between Python and the CUDA kernels.
+
+Every function here passes raw device pointers (tensor.data_ptr()) and sizes through the
+C-ABI declared in include/gsr_b200.h.  torch is used for device memory and streams only.
+There is no CPU fallback: if the shared object is missing or a call fails, this raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Dict, Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgsr_b200.so")
+
+GSR_BUF_GEOM, GSR_BUF_BINNING, GSR_BUF_IMG = 0, 1, 2
+
+ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int, C.c_size_t)
+
+
+class GsrSettings(C.Structure):
+    _fields_ = [("image_height", C.c_int32), ("image_width", C.c_int32), ("tanfovx", C.c_float),
+                ("tanfovy", C.c_float), ("scale_modifier", C.c_float), ("sh_degree", C.c_int32),
+                ("prefiltered", C.c_int32), ("debug", C.c_int32), ("antialiasing", C.c_int32),
+                ("bg", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p),
+                ("campos", C.c_void_p)]
+
+
+class GsrGaussians(C.Structure):
+    _fields_ = [("P", C.c_int32), ("M", C.c_int32), ("means3D", C.c_void_p), ("opacities", C.c_void_p),
+                ("shs", C.c_void_p), ("colors_precomp", C.c_void_p), ("scales", C.c_void_p),
+                ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p)]
+
+
+class GsrGrads(C.Structure):
+    _fields_ = [("dL_dmeans2D", C.c_void_p), ("dL_dcolors", C.c_void_p), ("dL_dopacity", C.c_void_p),
+                ("dL_dmeans3D", C.c_void_p), ("dL_dcov3D", C.c_void_p), ("dL_dsh", C.c_void_p),
+                ("dL_dscales", C.c_void_p), ("dL_drotations", C.c_void_p)]
+
+
+_EXPORT_FIELDS = ["depths", "means2D", "cov3D", "conic_opacity", "rgb", "clamped", "tiles_touched",
+                  "point_offsets", "keys_unsorted", "vals_unsorted", "keys_sorted", "vals_sorted", "ranges",
+                  "final_T", "n_contrib"]
+
+
+class GsrStateExport(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in _EXPORT_FIELDS]
+
+
+# every symbol include/gsr_b200.h declares (tests check that the library exports them all)
+EXPORTED_SYMBOLS = [
+    "gsr_version", "gsr_last_error", "gsr_geom_bytes", "gsr_img_bytes", "gsr_binning_bytes",
+    "gsr_backward_scratch_bytes", "gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_export_state",
+    "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count",
+]
+
+_lib = None
+
+
+class GsrError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libgsr_b200.so; fail loudly when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: the CUDA extension has not been built. "
+            "Run `python -m gaussian_splatting_lightning_b200.build` (needs nvcc). "
+            "There is no CPU or PyTorch fallback for the rasterizer.")
+    L = C.CDLL(LIB_PATH)
+    L.gsr_version.restype = C.c_char_p
+    L.gsr_last_error.restype = C.c_char_p
+    L.gsr_launch_count.restype = C.c_int64
+    for name in ("gsr_geom_bytes", "gsr_img_bytes", "gsr_binning_bytes", "gsr_backward_scratch_bytes",
+                 "gsr_sort_workspace_bytes"):
+        getattr(L, name).restype = C.c_size_t
+    L.gsr_geom_bytes.argtypes = [C.c_int32]
+    L.gsr_img_bytes.argtypes = [C.c_int32, C.c_int32]
+    L.gsr_binning_bytes.argtypes = [C.c_int64, C.c_int32, C.c_int32]
+    L.gsr_backward_scratch_bytes.argtypes = [C.c_int32]
+    L.gsr_sort_workspace_bytes.argtypes = [C.c_int64]
+    L.gsr_forward.restype = C.c_int
+    L.gsr_forward.argtypes = [C.POINTER(GsrSettings), C.POINTER(GsrGaussians), C.c_void_p, C.c_void_p, C.c_void_p,
+                              ALLOC_FN, C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                              C.c_void_p]
+    L.gsr_backward.restype = C.c_int
+    L.gsr_backward.argtypes = [C.POINTER(GsrSettings), C.POINTER(GsrGaussians), C.c_void_p, C.c_void_p, C.c_void_p,
+                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(GsrGrads),
+                               C.c_void_p]
+    L.gsr_mark_visible.restype = C.c_int
+    L.gsr_mark_visible.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gsr_export_state.restype = C.c_int
+    L.gsr_export_state.argtypes = [C.POINTER(GsrSettings), C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_int64, C.c_int64, C.POINTER(GsrStateExport), C.c_void_p]
+    L.gsr_sort_pairs.restype = C.c_int
+    L.gsr_sort_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                 C.c_int32, C.c_void_p, C.c_void_p]
+    _lib = L
+    return L
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = lib().gsr_last_error().decode("utf-8", "replace")
+        raise GsrError(f"{what} failed (code {rc}): {msg}")
+
+
+def version() -> str:
+    return lib().gsr_version().decode()
+
+
+def launch_count() -> int:
+    return int(lib().gsr_launch_count())
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def f32c(t: Optional[torch.Tensor], device=None) -> Optional[torch.Tensor]:
+    """contiguous float32 (on `device` if given); None and empty tensors become None."""
+    if t is None or t.numel() == 0:
+        return None
+    if device is not None and t.device != device:
+        t = t.to(device)
+    if t.dtype != torch.float32:
+        t = t.float()
+    t = t.contiguous()
+    if t.data_ptr() % 16:
+        t = t.clone(memory_format=torch.contiguous_format)
+    return t
+
+
+def stream_ptr(device) -> int:
+    return int(torch.cuda.current_stream(device).cuda_stream)
+
+
+class Allocator:
+    """The resize callback of gsr_forward (notes/rasterizer_note.h:27-40): torch owns the memory."""
+
+    def __init__(self, device):
+        self.device = device
+        self.buffers: Dict[int, torch.Tensor] = {}
+        self.error: Optional[BaseException] = None
+        self.cfunc = ALLOC_FN(self._alloc)
+
+    def _alloc(self, _user, which, nbytes):
+        try:
+            t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self.device)
+            self.buffers[int(which)] = t
+            return t.data_ptr()
+        except BaseException as e:  # never let an exception cross the C boundary
+            self.error = e
+            return None

@@ -1,0 +1,88 @@
+"""In-tree build of libgsr_b200.so (hand-written CUDA for sm_100a + the C-ABI of include/gsr_b200.h).
+
+    python -m gaussian_splatting_lightning_b200.build [--force] [--verbose]
+
+nvcc cross-compiles without a GPU.  The shared object is written next to this file so that it
+travels to the GPU box with the repository snapshot; it is git-ignored.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+BUILD = os.path.join(CSRC, "_build")
+LIB = os.path.join(HERE, "libgsr_b200.so")
+
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
+
+# translation unit -> extra flags.  The preprocess kernels feed integer outputs (depth bits of
+# the sort keys, radii, tile rects) and therefore state every fused multiply-add explicitly.
+SOURCES = {
+    "api.cu": [],
+    "preprocess.cu": ["-fmad=false"],
+    "binning.cu": ["-fmad=false"],
+    "radix_sort.cu": [],
+    "render_forward.cu": [],
+    "render_backward.cu": [],
+    "preprocess_backward.cu": ["-fmad=false"],
+}
+HEADERS = ["gsr_common.cuh", "gsr_math.cuh", "render_common.cuh", os.path.join("..", "..", "include", "gsr_b200.h")]
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", "nvcc"):
+        if cand and (os.path.isabs(cand) and os.path.exists(cand) or not os.path.isabs(cand)):
+            return cand
+    return "nvcc"
+
+
+def _stale(target: str, deps) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    os.makedirs(BUILD, exist_ok=True)
+    hdrs = [os.path.join(CSRC, h) for h in HEADERS] + [os.path.abspath(__file__)]
+    nvcc = _nvcc()
+    logs = {}
+
+    def compile_one(item):
+        src, extra = item
+        obj = os.path.join(BUILD, src.replace(".cu", ".o"))
+        srcp = os.path.join(CSRC, src)
+        if force or _stale(obj, [srcp] + hdrs):
+            cmd = [nvcc, *ARCH, *COMMON, *extra, "-c", srcp, "-o", obj]
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            logs[src] = r.stdout + r.stderr
+            if r.returncode != 0:
+                raise RuntimeError(f"nvcc failed on {src}:\n{' '.join(cmd)}\n{r.stdout}\n{r.stderr}")
+        return obj
+
+    with ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
+        objs = list(ex.map(compile_one, SOURCES.items()))
+    if force or _stale(LIB, objs):
+        cmd = [nvcc, *ARCH, "-shared", "-o", LIB, *objs, "-lcudart"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    if logs:
+        with open(os.path.join(BUILD, "ptxas.log"), "w") as f:
+            for k, v in logs.items():
+                f.write(f"==== {k}\n{v}\n")
+        if verbose:
+            for k, v in logs.items():
+                print(f"==== {k}\n{v}")
+    return LIB
+
+
+if __name__ == "__main__":
+    p = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
+    print(p)

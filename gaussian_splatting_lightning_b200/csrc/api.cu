@@ -1,0 +1,318 @@
+// api.cu -- the C-ABI of libgsr_b200.so (declared in include/gsr_b200.h).
+//
+// Host-side orchestration only: validates arguments, carves the three scratch buffers,
+// enqueues the stage kernels on the caller's stream and reads back num_rendered.  No torch
+// types, no CPU fallback: every stage is a CUDA kernel of this library.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/gsr_b200.h"
+#include "gsr_common.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<long long> g_launches{0};
+
+int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
+  g_err = what;
+  if (e != cudaSuccess) {
+    g_err += ": ";
+    g_err += cudaGetErrorString(e);
+  }
+  return code;
+}
+
+#define GSR_CUDA(expr, what)                                   \
+  do {                                                         \
+    cudaError_t e_ = (expr);                                   \
+    if (e_ != cudaSuccess) return fail(GSR_ECUDA, what, e_);   \
+  } while (0)
+
+// With settings->debug every stage is followed by a synchronise + error check that names
+// the stage (the CHECK_CUDA behaviour of notes/rasterizer_note.h:44-53).
+#define GSR_STAGE(expr, what, debug, stream)                                  \
+  do {                                                                        \
+    cudaError_t e_ = (expr);                                                  \
+    if (e_ != cudaSuccess) return fail(GSR_ECUDA, what, e_);                  \
+    if (debug) {                                                              \
+      e_ = cudaStreamSynchronize(stream);                                     \
+      if (e_ != cudaSuccess) return fail(GSR_ECUDA, what " (debug sync)", e_); \
+    }                                                                         \
+  } while (0)
+
+// Pinned mailbox + event for the asynchronous read of num_rendered, per thread and device.
+struct Mailbox {
+  unsigned int* host = nullptr;
+  cudaEvent_t ev = nullptr;
+};
+constexpr int MAX_DEVICES = 64;
+thread_local Mailbox g_mail[MAX_DEVICES];
+
+int get_mailbox(Mailbox** out) {
+  int dev = 0;
+  GSR_CUDA(cudaGetDevice(&dev), "cudaGetDevice");
+  if (dev < 0 || dev >= MAX_DEVICES) return fail(GSR_EINVAL, "device index out of range");
+  Mailbox& m = g_mail[dev];
+  if (!m.host) {
+    GSR_CUDA(cudaMallocHost((void**)&m.host, 64), "cudaMallocHost(mailbox)");
+    GSR_CUDA(cudaEventCreateWithFlags(&m.ev, cudaEventDisableTiming), "cudaEventCreate(mailbox)");
+  }
+  *out = &m;
+  return GSR_OK;
+}
+
+int make_view(const GsrSettings* s, int M, GsrView* v) {
+  if (!s) return fail(GSR_EINVAL, "settings is NULL");
+  if (s->image_width <= 0 || s->image_height <= 0) return fail(GSR_EINVAL, "image size must be positive");
+  if (!s->bg || !s->viewmatrix || !s->projmatrix || !s->campos)
+    return fail(GSR_EINVAL, "bg / viewmatrix / projmatrix / campos must be device pointers");
+  if (s->sh_degree < 0 || s->sh_degree > 3) return fail(GSR_EINVAL, "sh_degree must be in [0,3]");
+  v->W = s->image_width; v->H = s->image_height;
+  v->gx = (v->W + GSR_TILE - 1) / GSR_TILE; v->gy = (v->H + GSR_TILE - 1) / GSR_TILE;
+  v->tanfovx = s->tanfovx; v->tanfovy = s->tanfovy;
+  v->fx = (float)v->W / (2.f * s->tanfovx);  // gs_lightning/rasterize/rasterize.py:64-65
+  v->fy = (float)v->H / (2.f * s->tanfovy);
+  v->scale_modifier = s->scale_modifier;
+  v->deg = s->sh_degree; v->M = M;
+  v->antialiasing = s->antialiasing ? 1 : 0;
+  v->view = s->viewmatrix; v->proj = s->projmatrix; v->campos = s->campos; v->bg = s->bg;
+  return GSR_OK;
+}
+
+int make_gaussians(const GsrGaussians* g, int deg, GsrGaussiansDev* d) {
+  if (!g) return fail(GSR_EINVAL, "gaussians is NULL");
+  if (g->P < 0) return fail(GSR_EINVAL, "P must be >= 0");
+  if (g->P > 0) {
+    if (!g->means3D) return fail(GSR_EINVAL, "means3D must have dimensions (num_points, 3)");
+    if (!g->opacities) return fail(GSR_EINVAL, "opacities is NULL");
+    if ((g->shs == nullptr) == (g->colors_precomp == nullptr))
+      return fail(GSR_EINVAL, "Please provide excatly one of either SHs or precomputed colors!");
+    const bool sr = g->scales != nullptr && g->rotations != nullptr;
+    if (sr == (g->cov3D_precomp != nullptr) || (g->scales != nullptr) != (g->rotations != nullptr))
+      return fail(GSR_EINVAL, "Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+    if (g->shs && g->M < (deg + 1) * (deg + 1)) return fail(GSR_EINVAL, "shs holds fewer coefficients than sh_degree needs");
+    if (g->rotations && (reinterpret_cast<uintptr_t>(g->rotations) & 15))
+      return fail(GSR_EINVAL, "rotations must be 16-byte aligned");
+  }
+  d->P = g->P; d->M = g->shs ? g->M : 0;
+  d->means3D = g->means3D; d->opacities = g->opacities; d->shs = g->shs; d->colors_precomp = g->colors_precomp;
+  d->scales = g->scales; d->rotations = g->rotations; d->cov3D_precomp = g->cov3D_precomp;
+  return GSR_OK;
+}
+
+__global__ void set_u32_kernel(unsigned int* p, unsigned int v) { *p = v; }
+
+}  // namespace
+
+namespace gsr {
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+}  // namespace gsr
+
+extern "C" {
+
+const char* gsr_version(void) { return "gsr_b200 0.1 sm_100a"; }
+const char* gsr_last_error(void) { return g_err.c_str(); }
+int64_t gsr_launch_count(void) { return (int64_t)g_launches.load(); }
+
+size_t gsr_geom_bytes(int32_t P) { return GeomState::carve(nullptr, P).bytes; }
+size_t gsr_img_bytes(int32_t W, int32_t H) { return ImgState::carve(nullptr, W, H).bytes; }
+size_t gsr_binning_bytes(int64_t capacity, int32_t, int32_t) { return BinningState::carve(nullptr, capacity).bytes; }
+size_t gsr_backward_scratch_bytes(int32_t P) { return gsr_align_up((size_t)(P > 0 ? P : 1) * 12 * sizeof(float)); }
+
+int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, uint8_t* present, void* stream) {
+  if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return fail(GSR_EINVAL, "mark_visible: bad arguments");
+  GSR_CUDA(gsr::launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream), "mark_visible kernel");
+  return GSR_OK;
+}
+
+int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, float* out_color, int32_t* radii,
+                float* out_invdepth, gsr_alloc_fn alloc, void* alloc_user, int64_t binning_hint,
+                int64_t* num_rendered, int64_t* binning_capacity, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GsrView v;
+  GsrGaussiansDev g;
+  int rc = make_gaussians(gaussians, settings ? settings->sh_degree : 0, &g);
+  if (rc) return rc;
+  rc = make_view(settings, g.M, &v);
+  if (rc) return rc;
+  if (!out_color || !out_invdepth || !alloc || (g.P > 0 && !radii)) return fail(GSR_EINVAL, "forward: NULL output or allocator");
+  const bool debug = settings->debug != 0;
+  const int P = g.P;
+  const int num_tiles = v.gx * v.gy;
+  const int end_bit = gsr_key_bits(num_tiles);
+  const int npass = gsr_sort_passes(end_bit);
+
+  char* geom_ptr = (char*)alloc(alloc_user, GSR_BUF_GEOM, GeomState::carve(nullptr, P).bytes);
+  char* img_ptr = (char*)alloc(alloc_user, GSR_BUF_IMG, ImgState::carve(nullptr, v.W, v.H).bytes);
+  if (!geom_ptr || !img_ptr) return fail(GSR_EALLOC, "allocator returned NULL");
+  GeomState geom = GeomState::carve(geom_ptr, P);
+  ImgState img = ImgState::carve(img_ptr, v.W, v.H);
+
+  // one memset clears ranges + control block, one the scan status words
+  GSR_CUDA(cudaMemsetAsync(img_ptr + img.ranges_off, 0, img.bytes - img.ranges_off, stream), "memset(ranges)");
+  GSR_CUDA(cudaMemsetAsync(geom.scan_state, 0, geom.scan_state_bytes(P), stream), "memset(scan state)");
+
+  GSR_STAGE(gsr::launch_preprocess(v, g, radii, geom, stream), "preprocess kernel", debug, stream);
+  GSR_STAGE(gsr::launch_scan(P, geom, img.ctrl, stream), "scan kernel", debug, stream);
+
+  Mailbox* mail = nullptr;
+  rc = get_mailbox(&mail);
+  if (rc) return rc;
+  GSR_CUDA(cudaMemcpyAsync(mail->host, &img.ctrl->num_rendered, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream),
+           "memcpy(num_rendered)");
+  GSR_CUDA(cudaEventRecord(mail->ev, stream), "event record");
+
+  int64_t R = -1;
+  int64_t cap = binning_hint;
+  if (cap <= 0) {
+    GSR_CUDA(cudaEventSynchronize(mail->ev), "read num_rendered");
+    R = (int64_t)*mail->host;
+    cap = R;
+  }
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    if (cap >= (1ll << 30)) return fail(GSR_ELIMIT, "more than 2^30 tile instances");
+    char* bin_ptr = (char*)alloc(alloc_user, GSR_BUF_BINNING, BinningState::carve(nullptr, cap).bytes);
+    if (!bin_ptr) return fail(GSR_EALLOC, "allocator returned NULL");
+    BinningState bin = BinningState::carve(bin_ptr, cap);
+    if (cap > 0 && P > 0) {
+      GSR_CUDA(cudaMemsetAsync(bin.sort_ws_base, 0, bin.sort_ws.bytes, stream), "memset(sort workspace)");
+      // start in the buffer that makes the last pass land in (keys_a, vals_a)
+      unsigned long long* k0 = (npass % 2 == 0) ? bin.keys_a : bin.keys_b;
+      uint32_t* v0 = (npass % 2 == 0) ? bin.vals_a : bin.vals_b;
+      unsigned long long* k1 = (npass % 2 == 0) ? bin.keys_b : bin.keys_a;
+      uint32_t* v1 = (npass % 2 == 0) ? bin.vals_b : bin.vals_a;
+      GSR_STAGE(gsr::launch_duplicate(v, P, radii, geom, k0, v0, (uint32_t)cap, img.ctrl, stream), "duplicate kernel",
+                debug, stream);
+      GSR_STAGE(gsr::launch_onesweep(k0, v0, k1, v1, &img.ctrl->num_rendered, (uint32_t)cap, end_bit, bin.sort_ws,
+                                     stream),
+                "onesweep radix sort", debug, stream);
+      GSR_STAGE(gsr::launch_tile_ranges(bin.keys_a, &img.ctrl->num_rendered, (uint32_t)cap, img.ranges, stream),
+                "tile ranges kernel", debug, stream);
+    }
+    GSR_STAGE(gsr::launch_render_forward(v, img.ranges, bin.vals_a, geom.recs, out_color, out_invdepth, img.final_T,
+                                         img.n_contrib, stream),
+              "render forward kernel", debug, stream);
+    if (R < 0) {
+      GSR_CUDA(cudaEventSynchronize(mail->ev), "read num_rendered");
+      R = (int64_t)*mail->host;
+    }
+    if (R <= cap) break;
+    // the hint was too small: the frame above rendered a truncated list. Redo binning + compositing.
+    cap = R + R / 8 + 1024;
+    GSR_CUDA(cudaMemsetAsync(img.ranges, 0, (size_t)num_tiles * sizeof(uint2), stream), "memset(ranges)");
+  }
+  if (R >= 0xFFFFFFFFll) return fail(GSR_ELIMIT, "more than 2^32 tile instances");
+  if (num_rendered) *num_rendered = R;
+  if (binning_capacity) *binning_capacity = cap;
+  return GSR_OK;
+}
+
+int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, const int32_t* radii,
+                 const float* dL_dcolor, const float* dL_dinvdepth, const void* geom_, const void* binning_,
+                 const void* img_, int64_t num_rendered, void* scratch, const GsrGrads* grads, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GsrView v;
+  GsrGaussiansDev g;
+  int rc = make_gaussians(gaussians, settings ? settings->sh_degree : 0, &g);
+  if (rc) return rc;
+  rc = make_view(settings, g.M, &v);
+  if (rc) return rc;
+  if (!grads) return fail(GSR_EINVAL, "backward: grads is NULL");
+  const int P = g.P;
+  if (P == 0) return GSR_OK;
+  if (!radii || !dL_dcolor || !geom_ || !binning_ || !img_ || !scratch)
+    return fail(GSR_EINVAL, "backward: NULL buffer");
+  if (!grads->dL_dmeans2D || !grads->dL_dcolors || !grads->dL_dopacity || !grads->dL_dmeans3D || !grads->dL_dcov3D ||
+      !grads->dL_dscales || !grads->dL_drotations || (g.shs && !grads->dL_dsh))
+    return fail(GSR_EINVAL, "backward: NULL gradient output");
+  if (reinterpret_cast<uintptr_t>(grads->dL_drotations) & 15) return fail(GSR_EINVAL, "dL_drotations must be 16-byte aligned");
+  const bool debug = settings->debug != 0;
+  GeomState geom = GeomState::carve((char*)geom_, P);
+  ImgState img = ImgState::carve((char*)img_, v.W, v.H);
+  const uint32_t* point_list = (const uint32_t*)binning_;  // vals_a sits at offset 0 (BinningState)
+  float* grad_acc = (float*)scratch;
+
+  GSR_CUDA(cudaMemsetAsync(grad_acc, 0, (size_t)P * 12 * sizeof(float), stream), "memset(grad accumulators)");
+  if (num_rendered > 0)
+    GSR_STAGE(gsr::launch_render_backward(v, img.ranges, point_list, geom.recs, img.final_T, img.n_contrib, dL_dcolor,
+                                          dL_dinvdepth, grad_acc, stream),
+              "render backward kernel", debug, stream);
+  GSR_STAGE(gsr::launch_preprocess_backward(v, g, radii, geom, grad_acc, grads->dL_dmeans2D, grads->dL_dcolors,
+                                            grads->dL_dopacity, grads->dL_dmeans3D, grads->dL_dcov3D, grads->dL_dsh,
+                                            grads->dL_dscales, grads->dL_drotations, stream),
+            "preprocess backward kernel", debug, stream);
+  return GSR_OK;
+}
+
+int gsr_export_state(const GsrSettings* settings, int32_t P, const int32_t* radii, const void* geom_,
+                     const void* binning_, const void* img_, int64_t num_rendered, int64_t binning_capacity,
+                     const GsrStateExport* out, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GsrView v;
+  int rc = make_view(settings, 0, &v);
+  if (rc) return rc;
+  if (!out || !geom_ || !img_ || (P > 0 && !radii)) return fail(GSR_EINVAL, "export: NULL buffer");
+  GeomState geom = GeomState::carve((char*)geom_, P);
+  ImgState img = ImgState::carve((char*)img_, v.W, v.H);
+  const int64_t cap = binning_capacity > 0 ? binning_capacity : num_rendered;
+  const size_t R = (size_t)num_rendered;
+  GSR_CUDA(gsr::launch_export_geom(P, radii, geom, out->depths, out->means2D, out->cov3D, out->conic_opacity, out->rgb,
+                                   out->clamped, out->tiles_touched, out->point_offsets, stream),
+           "export kernel");
+  if (R > 0 && binning_) {
+    BinningState bin = BinningState::carve((char*)binning_, cap);
+    if (out->keys_sorted)
+      GSR_CUDA(cudaMemcpyAsync(out->keys_sorted, bin.keys_a, R * 8, cudaMemcpyDeviceToDevice, stream), "export keys");
+    if (out->vals_sorted)
+      GSR_CUDA(cudaMemcpyAsync(out->vals_sorted, bin.vals_a, R * 4, cudaMemcpyDeviceToDevice, stream), "export vals");
+    if (out->keys_unsorted && out->vals_unsorted)
+      GSR_CUDA(gsr::launch_duplicate(v, P, radii, geom, (unsigned long long*)out->keys_unsorted, out->vals_unsorted,
+                                     (uint32_t)R, img.ctrl, stream),
+               "export duplicate kernel");
+  }
+  const size_t HW = (size_t)v.W * v.H;
+  if (out->ranges)
+    GSR_CUDA(cudaMemcpyAsync(out->ranges, img.ranges, (size_t)v.gx * v.gy * 8, cudaMemcpyDeviceToDevice, stream),
+             "export ranges");
+  if (out->final_T)
+    GSR_CUDA(cudaMemcpyAsync(out->final_T, img.final_T, HW * 4, cudaMemcpyDeviceToDevice, stream), "export final_T");
+  if (out->n_contrib)
+    GSR_CUDA(cudaMemcpyAsync(out->n_contrib, img.n_contrib, HW * 4, cudaMemcpyDeviceToDevice, stream),
+             "export n_contrib");
+  return GSR_OK;
+}
+
+size_t gsr_sort_workspace_bytes(int64_t n) {
+  return gsr_sort::Workspace::carve(nullptr, n).bytes + 128;  // + the device-side element count
+}
+
+int gsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                   uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n, int32_t end_bit, void* workspace,
+                   void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (n < 0 || n >= (1ll << 30)) return fail(GSR_ELIMIT, "sort: n must be in [0, 2^30)");
+  if (end_bit < 1 || end_bit > 64) return fail(GSR_EINVAL, "sort: end_bit must be in [1,64]");
+  if (n == 0) return GSR_OK;
+  if (!keys_in || !vals_in || !keys_out || !vals_out || !keys_tmp || !vals_tmp || !workspace)
+    return fail(GSR_EINVAL, "sort: NULL buffer");
+  const size_t ws_bytes = gsr_sort::Workspace::carve(nullptr, n).bytes;
+  GSR_CUDA(cudaMemsetAsync(workspace, 0, ws_bytes + 128, stream), "memset(sort workspace)");
+  gsr_sort::Workspace ws = gsr_sort::Workspace::carve((char*)workspace, n);
+  unsigned int* d_n = (unsigned int*)((char*)workspace + ws_bytes);
+  set_u32_kernel<<<1, 1, 0, stream>>>(d_n, (unsigned int)n);
+  gsr::count_launch();
+  const int npass = gsr_sort_passes(end_bit);
+  unsigned long long* ka = (unsigned long long*)((npass % 2 == 0) ? keys_out : keys_tmp);
+  uint32_t* va = (npass % 2 == 0) ? vals_out : vals_tmp;
+  unsigned long long* kb = (unsigned long long*)((npass % 2 == 0) ? keys_tmp : keys_out);
+  uint32_t* vb = (npass % 2 == 0) ? vals_tmp : vals_out;
+  GSR_CUDA(cudaMemcpyAsync(ka, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, stream), "sort: copy keys");
+  GSR_CUDA(cudaMemcpyAsync(va, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream), "sort: copy vals");
+  GSR_CUDA(gsr::launch_onesweep(ka, va, kb, vb, d_n, (uint32_t)n, end_bit, ws, stream), "onesweep radix sort");
+  return GSR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,222 @@
+// gsr_common.cuh -- shared declarations of the B200 rasterizer kernels.
+//
+// HBM layout of the three scratch buffers (opaque uint8 tensors to the caller; the
+// forward writes them, the backward only reads them):
+//
+//   geom (per Gaussian, P)     GsrRec recs[P]           48 B  packed record the tile kernels gather
+//                              float  cov3D[6P]         24 B  kept for the backward
+//                              u8     clamped[P]         1 B  bit c set: SH colour channel c was clamped at 0
+//                              u32    tiles_touched[P]   4 B
+//                              u32    point_offsets[P]   4 B  inclusive scan of tiles_touched
+//                              u64    scan_state[...]         decoupled look-back words of the scan
+//   binning (per instance, R)  u32 vals_a[cap] (sorted point list ends here), vals_b[cap], u64 keys_a[cap], keys_b[cap]
+//                              sort control (digit histograms, tile counters, look-back words)
+//   img                        float final_T[HW], u32 n_contrib[HW], uint2 ranges[T], GsrControl
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#define GSR_TILE 16
+#define GSR_TILE_PIX 256
+#define GSR_NEAR 0.2f
+
+// One packed per-Gaussian record (AoS, 48 B, 16-byte aligned): everything the forward and
+// backward compositing kernels need, fetched with three 128-bit loads.
+struct __align__(16) GsrRec {
+  float4 a;  // {mean2D.x, mean2D.y, conic.A, conic.B}
+  float4 b;  // {conic.C, opacity (AA-scaled), r, g}
+  float4 c;  // {b, 1/z_view, tau = ln(255*opacity), z_view}
+};
+
+// Per-frame device-side control block (zeroed by one memset at the start of a frame).
+struct GsrControl {
+  unsigned int num_rendered;   // R = sum(tiles_touched), written by the scan
+  unsigned int scan_counter;   // dynamic tile id of the scan
+  unsigned int overflow;       // set when R exceeded the binning capacity
+  unsigned int pad;
+};
+
+// Kernel-side view of one camera + flags.
+struct GsrView {
+  int W, H, gx, gy;
+  float tanfovx, tanfovy, fx, fy;
+  float scale_modifier;
+  int deg, M;
+  int antialiasing;
+  const float* view;
+  const float* proj;
+  const float* campos;
+  const float* bg;
+};
+
+static inline size_t gsr_align_up(size_t x, size_t a = 128) { return (x + a - 1) / a * a; }
+
+// ---- geometry buffer carving -------------------------------------------------------
+struct GeomState {
+  GsrRec* recs;
+  float* cov3D;
+  uint8_t* clamped;
+  uint32_t* tiles_touched;
+  uint32_t* point_offsets;
+  unsigned long long* scan_state;
+  size_t bytes;
+  static constexpr int SCAN_ITEMS = 2048;  // items per scan tile (256 threads x 8)
+  static GeomState carve(char* base, int P) {
+    GeomState g;
+    size_t off = 0;
+    auto take = [&](size_t n) { size_t o = off; off = gsr_align_up(off + n); return base ? base + o : (char*)nullptr; };
+    const size_t Pp = (size_t)(P > 0 ? P : 1);
+    g.recs = (GsrRec*)take(Pp * sizeof(GsrRec));
+    g.cov3D = (float*)take(Pp * 6 * sizeof(float));
+    g.clamped = (uint8_t*)take(Pp);
+    g.tiles_touched = (uint32_t*)take(Pp * 4);
+    g.point_offsets = (uint32_t*)take(Pp * 4);
+    const size_t ntiles = (Pp + SCAN_ITEMS - 1) / SCAN_ITEMS;
+    g.scan_state = (unsigned long long*)take(ntiles * 8);
+    g.bytes = off;
+    return g;
+  }
+  size_t scan_state_bytes(int P) const { return ((size_t)(P > 0 ? P : 1) + SCAN_ITEMS - 1) / SCAN_ITEMS * 8; }
+};
+
+// ---- image buffer carving ----------------------------------------------------------
+struct ImgState {
+  float* final_T;
+  uint32_t* n_contrib;
+  uint2* ranges;
+  GsrControl* ctrl;
+  size_t ranges_off, bytes;
+  static ImgState carve(char* base, int W, int H) {
+    ImgState s;
+    size_t off = 0;
+    auto take = [&](size_t n) { size_t o = off; off = gsr_align_up(off + n); return base ? base + o : (char*)nullptr; };
+    const size_t HW = (size_t)W * H;
+    const size_t T = (size_t)((W + GSR_TILE - 1) / GSR_TILE) * ((H + GSR_TILE - 1) / GSR_TILE);
+    s.final_T = (float*)take(HW * 4);
+    s.n_contrib = (uint32_t*)take(HW * 4);
+    s.ranges_off = off;
+    s.ranges = (uint2*)take(T * 8);
+    s.ctrl = (GsrControl*)take(sizeof(GsrControl));
+    s.bytes = off;
+    return s;
+  }
+};
+
+// ---- onesweep sort configuration ------------------------------------------------------
+namespace gsr_sort {
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int THREADS = 256;
+constexpr int WARPS = THREADS / 32;
+constexpr int IPT = 16;                       // items per thread
+constexpr int TILE_ITEMS = THREADS * IPT;     // 4096 pairs per tile
+constexpr int MAX_PASSES = 8;
+
+struct Workspace {
+  uint32_t* hist;          // [MAX_PASSES][RADIX] digit histograms of all passes
+  uint32_t* tile_counter;  // [MAX_PASSES] dynamic tile ids
+  uint32_t* lookback;      // [MAX_PASSES][ntiles][RADIX]
+  size_t ntiles;
+  size_t bytes;
+  static Workspace carve(char* base, int64_t capacity) {
+    Workspace w;
+    size_t off = 0;
+    auto take = [&](size_t n) { size_t o = off; off = gsr_align_up(off + n); return base ? base + o : (char*)nullptr; };
+    w.ntiles = (size_t)((capacity + TILE_ITEMS - 1) / TILE_ITEMS);
+    if (w.ntiles == 0) w.ntiles = 1;
+    w.hist = (uint32_t*)take((size_t)MAX_PASSES * RADIX * 4);
+    w.tile_counter = (uint32_t*)take((size_t)MAX_PASSES * 4);
+    w.lookback = (uint32_t*)take((size_t)MAX_PASSES * w.ntiles * RADIX * 4);
+    w.bytes = off;
+    return w;
+  }
+};
+}  // namespace gsr_sort
+
+// ---- binning buffer carving ----------------------------------------------------------
+struct BinningState {
+  unsigned long long* keys_a;
+  unsigned long long* keys_b;
+  uint32_t* vals_a;
+  uint32_t* vals_b;
+  gsr_sort::Workspace sort_ws;
+  char* sort_ws_base;
+  size_t bytes;
+  static BinningState carve(char* base, int64_t capacity) {
+    BinningState b;
+    size_t off = 0;
+    auto take = [&](size_t n) { size_t o = off; off = gsr_align_up(off + n); return base ? base + o : (char*)nullptr; };
+    const size_t cap = (size_t)(capacity > 0 ? capacity : 1);
+    // vals_a first: the sorted point list always ends in vals_a (offset 0, independent of the
+    // capacity), which is all the backward needs from this buffer.
+    b.vals_a = (uint32_t*)take(cap * 4);
+    b.vals_b = (uint32_t*)take(cap * 4);
+    b.keys_a = (unsigned long long*)take(cap * 8);
+    b.keys_b = (unsigned long long*)take(cap * 8);
+    const gsr_sort::Workspace probe = gsr_sort::Workspace::carve(nullptr, (int64_t)cap);
+    b.sort_ws_base = take(probe.bytes);
+    b.sort_ws = gsr_sort::Workspace::carve(b.sort_ws_base, (int64_t)cap);
+    b.bytes = off;
+    return b;
+  }
+};
+
+// Number of key bits the sort must cover: 32 depth bits + bits of the largest tile id.
+static inline int gsr_key_bits(int num_tiles) {
+  int bits = 0;
+  unsigned int t = num_tiles > 1 ? (unsigned int)(num_tiles - 1) : 1u;
+  while (t) { ++bits; t >>= 1; }
+  return 32 + bits;
+}
+static inline int gsr_sort_passes(int end_bit) {
+  return (end_bit + gsr_sort::RADIX_BITS - 1) / gsr_sort::RADIX_BITS;
+}
+
+// ---- launch declarations (each stage lives in its own translation unit) ---------------
+struct GsrGaussiansDev {
+  int P, M;
+  const float* means3D;
+  const float* opacities;
+  const float* shs;
+  const float* colors_precomp;
+  const float* scales;
+  const float* rotations;
+  const float* cov3D_precomp;
+};
+
+namespace gsr {
+void count_launch(int n = 1);
+
+cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
+cudaError_t launch_preprocess(const GsrView& v, const GsrGaussiansDev& g, int32_t* radii, const GeomState& geom,
+                              cudaStream_t s);
+cudaError_t launch_scan(int P, const GeomState& geom, GsrControl* ctrl, cudaStream_t s);
+cudaError_t launch_duplicate(const GsrView& v, int P, const int32_t* radii, const GeomState& geom,
+                             unsigned long long* keys, uint32_t* vals, uint32_t capacity, GsrControl* ctrl,
+                             cudaStream_t s);
+// Sorts min(*d_n, capacity) pairs; the result lands in (keys_a, vals_a) when the pass
+// count is even, else in (keys_b, vals_b).  The workspace must be zeroed.
+cudaError_t launch_onesweep(unsigned long long* keys_a, uint32_t* vals_a, unsigned long long* keys_b,
+                            uint32_t* vals_b, const unsigned int* d_n, uint32_t capacity, int end_bit,
+                            const gsr_sort::Workspace& ws, cudaStream_t s);
+cudaError_t launch_tile_ranges(const unsigned long long* keys_sorted, const unsigned int* d_n, uint32_t capacity,
+                               uint2* ranges, cudaStream_t s);
+cudaError_t launch_render_forward(const GsrView& v, const uint2* ranges, const uint32_t* point_list,
+                                  const GsrRec* recs, float* out_color, float* out_invdepth, float* final_T,
+                                  uint32_t* n_contrib, cudaStream_t s);
+cudaError_t launch_render_backward(const GsrView& v, const uint2* ranges, const uint32_t* point_list,
+                                   const GsrRec* recs, const float* final_T, const uint32_t* n_contrib,
+                                   const float* dL_dpix, const float* dL_dinvdepth, float* grad_acc,
+                                   cudaStream_t s);
+// grad_acc: (P,12) floats {dmean2D.x, .y, dconic.A, .B | .C, dopacity, dcolor.r, .g | .b, dinvz, -, -}
+cudaError_t launch_preprocess_backward(const GsrView& v, const GsrGaussiansDev& g, const int32_t* radii,
+                                       const GeomState& geom, const float* grad_acc, float* dL_dmeans2D,
+                                       float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+                                       float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drot,
+                                       cudaStream_t s);
+cudaError_t launch_export_geom(int P, const int32_t* radii, const GeomState& geom, float* depths, float* means2D,
+                               float* cov3D, float* conic_opacity, float* rgb, uint8_t* clamped,
+                               uint32_t* tiles_touched, uint32_t* point_offsets, cudaStream_t s);
+}  // namespace gsr

@@ -1,0 +1,261 @@
+// preprocess_backward.cu -- K9+K10 fused: per-Gaussian backward through
+//   conic -> dilated cov2D -> (cov3D, mean3D via the EWA Jacobian incl. the 1.3*tanfov clamp gate),
+//   mean2D -> mean3D via the full projection, 1/z -> mean3D, colour -> (SH, direction -> mean3D)
+//   with the clamp mask, cov3D -> (scale, quaternion), and the antialiasing opacity scale.
+//
+// The forward side of each step is the reference's Python restatement
+// (gs_lightning/rasterize/render_tools.py:13-131, camera_tools.py:10-32, utils/sh.py:41-81);
+// the reference has no backward for any of it, so the derivative is the one stated in
+// oracle/gsr_oracle.cpp (gsro_preprocess_backward) and pinned there by float64 autograd.
+//
+// HBM-bound: (131 + 12M) B read, (56 + 12M) B written per visible Gaussian.  One thread per
+// Gaussian; the thread's dL_dsh row is written with 128-bit stores.
+#include "gsr_math.cuh"
+
+namespace gsr {
+
+struct PreBwdArgs {
+  GsrView v;
+  GsrGaussiansDev g;
+  const int32_t* radii;
+  const float* cov3D;
+  const uint8_t* clamped;
+  const float* grad_acc;  // (P,12)
+  float* dL_dmeans2D;
+  float* dL_dcolors;
+  float* dL_dopacity;
+  float* dL_dmeans3D;
+  float* dL_dcov3D;
+  float* dL_dsh;
+  float* dL_dscales;
+  float* dL_drot;
+};
+
+template <int DEG>
+__device__ __forceinline__ void sh_backward(const float* __restrict__ sh, float* __restrict__ dsh, int M, bool vec4,
+                                            float x, float y, float z, const float* g3, float* ddir) {
+  constexpr int N = (DEG + 1) * (DEG + 1);
+  float basis[N], bx[N], by[N], bz[N];
+  sh_basis<DEG>(x, y, z, basis);
+  sh_basis_grad<DEG>(x, y, z, bx, by, bz);
+  ddir[0] = ddir[1] = ddir[2] = 0.f;
+  float out[(3 * N + 3) / 4 * 4];
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+      out[3 * k + ch] = basis[k] * g3[ch];
+      if (k > 0) {
+        const float s = sh[3 * k + ch] * g3[ch];
+        ddir[0] += bx[k] * s; ddir[1] += by[k] * s; ddir[2] += bz[k] * s;
+      }
+    }
+  }
+  // row = 3*M floats; entries past 3*N are zero
+  const int total = 3 * M;
+  if (vec4) {
+    float4* d4 = reinterpret_cast<float4*>(dsh);
+    constexpr int NV = (3 * N + 3) / 4;
+#pragma unroll
+    for (int k = 3 * N; k < NV * 4; ++k) out[k] = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) d4[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+    for (int k = NV; k < total / 4; ++k) d4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 3 * N; ++k) dsh[k] = out[k];
+    for (int k = 3 * N; k < total; ++k) dsh[k] = 0.f;
+  }
+}
+
+__global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int P = a.g.P, M = a.g.M;
+  if (i >= P) return;
+  const bool sh_vec4 = a.dL_dsh && ((M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0);
+
+  if (!(a.radii[i] > 0)) {
+    a.dL_dmeans2D[3 * (size_t)i] = 0.f; a.dL_dmeans2D[3 * (size_t)i + 1] = 0.f; a.dL_dmeans2D[3 * (size_t)i + 2] = 0.f;
+    a.dL_dcolors[3 * (size_t)i] = 0.f; a.dL_dcolors[3 * (size_t)i + 1] = 0.f; a.dL_dcolors[3 * (size_t)i + 2] = 0.f;
+    a.dL_dopacity[i] = 0.f;
+    for (int k = 0; k < 3; ++k) { a.dL_dmeans3D[3 * (size_t)i + k] = 0.f; a.dL_dscales[3 * (size_t)i + k] = 0.f; }
+    for (int k = 0; k < 4; ++k) a.dL_drot[4 * (size_t)i + k] = 0.f;
+    for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * (size_t)i + k] = 0.f;
+    if (a.dL_dsh) {
+      float* dsh = a.dL_dsh + (size_t)i * M * 3;
+      if (sh_vec4) for (int k = 0; k < 3 * M / 4; ++k) reinterpret_cast<float4*>(dsh)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      else for (int k = 0; k < 3 * M; ++k) dsh[k] = 0.f;
+    }
+    return;
+  }
+
+  const float4 g0 = reinterpret_cast<const float4*>(a.grad_acc)[3 * (size_t)i];      // dmx dmy dA dB
+  const float4 g1 = reinterpret_cast<const float4*>(a.grad_acc)[3 * (size_t)i + 1];  // dC dop dr dg
+  const float4 g2 = reinterpret_cast<const float4*>(a.grad_acc)[3 * (size_t)i + 2];  // db dinvz - -
+  const float* __restrict__ view = a.v.view;
+  const float* __restrict__ proj = a.v.proj;
+  const float fx = a.v.fx, fy = a.v.fy;
+
+  const float px = a.g.means3D[3 * (size_t)i], py = a.g.means3D[3 * (size_t)i + 1], pz = a.g.means3D[3 * (size_t)i + 2];
+  float s6[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) s6[k] = a.cov3D[6 * (size_t)i + k];
+  JacobianCtx jc;
+  build_jacobian(view, px, py, pz, fx, fy, a.v.tanfovx, a.v.tanfovy, jc);
+  const Cov2D c0 = project_cov(s6, jc);
+  const float ca = c0.a + 0.3f, cc = c0.c + 0.3f, cb = c0.b;
+  const float det = ca * cc - cb * cb;
+
+  // conic -> dilated cov2D
+  const float dA = g0.z, dB = g0.w, dC = g1.x;
+  const float d2inv = 1.f / (det * det + 0.0000001f);
+  float da = d2inv * (-cc * cc * dA + cb * cc * dB - cb * cb * dC);
+  float dc = d2inv * (-cb * cb * dA + ca * cb * dB - ca * ca * dC);
+  float db = d2inv * (2.f * cb * cc * dA - (ca * cc + cb * cb) * dB + 2.f * ca * cb * dC);
+
+  float dop = g1.y;
+  if (a.v.antialiasing) {
+    const float det0 = c0.a * c0.c - c0.b * c0.b;
+    const float ratio = det0 / det;
+    const float h = sqrtf(fmaxf(0.000025f, ratio));
+    const float dL_dop_eff = dop;
+    dop = dL_dop_eff * h;
+    if (ratio > 0.000025f) {
+      const float dL_dratio = dL_dop_eff * a.g.opacities[i] / (2.f * h);
+      const float inv = 1.f / det, r2 = ratio * inv;
+      da += dL_dratio * (c0.c * inv - r2 * cc);
+      dc += dL_dratio * (c0.a * inv - r2 * ca);
+      db += dL_dratio * (-2.f * cb * inv + r2 * 2.f * cb);
+    }
+  }
+  a.dL_dopacity[i] = dop;
+
+  // cov2D -> cov3D
+  const float* m0 = jc.m0;
+  const float* m1 = jc.m1;
+  float dS[6];
+  dS[0] = m0[0] * m0[0] * da + m0[0] * m1[0] * db + m1[0] * m1[0] * dc;
+  dS[3] = m0[1] * m0[1] * da + m0[1] * m1[1] * db + m1[1] * m1[1] * dc;
+  dS[5] = m0[2] * m0[2] * da + m0[2] * m1[2] * db + m1[2] * m1[2] * dc;
+  dS[1] = 2.f * m0[0] * m0[1] * da + (m0[0] * m1[1] + m0[1] * m1[0]) * db + 2.f * m1[0] * m1[1] * dc;
+  dS[2] = 2.f * m0[0] * m0[2] * da + (m0[0] * m1[2] + m0[2] * m1[0]) * db + 2.f * m1[0] * m1[2] * dc;
+  dS[4] = 2.f * m0[1] * m0[2] * da + (m0[1] * m1[2] + m0[2] * m1[1]) * db + 2.f * m1[1] * m1[2] * dc;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * (size_t)i + k] = dS[k];
+
+  // cov2D -> J*R_cw -> view-space point
+  const float S[3][3] = {{s6[0], s6[1], s6[2]}, {s6[1], s6[3], s6[4]}, {s6[2], s6[4], s6[5]}};
+  float dJ00 = 0.f, dJ02 = 0.f, dJ11 = 0.f, dJ12 = 0.f;
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const float Sm0 = S[r][0] * m0[0] + S[r][1] * m0[1] + S[r][2] * m0[2];
+    const float Sm1 = S[r][0] * m1[0] + S[r][1] * m1[1] + S[r][2] * m1[2];
+    const float dm0 = 2.f * da * Sm0 + db * Sm1;
+    const float dm1 = 2.f * dc * Sm1 + db * Sm0;
+    dJ00 += dm0 * view[4 * r + 0]; dJ02 += dm0 * view[4 * r + 2];
+    dJ11 += dm1 * view[4 * r + 1]; dJ12 += dm1 * view[4 * r + 2];
+  }
+  const float tz = jc.tz, tzi = 1.f / tz, tz2 = tzi * tzi, tz3 = tz2 * tzi;
+  const float dtx = (jc.gate_x ? 1.f : 0.f) * -fx * tz2 * dJ02;
+  const float dty = (jc.gate_y ? 1.f : 0.f) * -fy * tz2 * dJ12;
+  float dtz = -fx * tz2 * dJ00 - fy * tz2 * dJ11 + 2.f * fx * jc.tx * tz3 * dJ02 + 2.f * fy * jc.ty * tz3 * dJ12;
+  dtz -= g2.y * tz2;  // inverse depth
+  float dmean[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) dmean[j] = dtx * view[4 * j + 0] + dty * view[4 * j + 1] + dtz * view[4 * j + 2];
+
+  // mean2D (NDC-scaled) -> mean3D
+  {
+    const float hx = xform_col(proj, 0, px, py, pz), hy = xform_col(proj, 1, px, py, pz);
+    const float hw = xform_col(proj, 3, px, py, pz);
+    const float mw = 1.f / (hw + 0.0000001f);
+    const float mul1 = hx * mw * mw, mul2 = hy * mw * mw;
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      dmean[j] += (proj[4 * j + 0] * mw - proj[4 * j + 3] * mul1) * g0.x +
+                  (proj[4 * j + 1] * mw - proj[4 * j + 3] * mul2) * g0.y;
+  }
+  a.dL_dmeans2D[3 * (size_t)i] = g0.x; a.dL_dmeans2D[3 * (size_t)i + 1] = g0.y; a.dL_dmeans2D[3 * (size_t)i + 2] = 0.f;
+  a.dL_dcolors[3 * (size_t)i] = g1.z; a.dL_dcolors[3 * (size_t)i + 1] = g1.w; a.dL_dcolors[3 * (size_t)i + 2] = g2.x;
+
+  // SH
+  if (a.dL_dsh) {
+    const float* __restrict__ cam = a.v.campos;
+    const float dirx = px - cam[0], diry = py - cam[1], dirz = pz - cam[2];
+    const float len = sqrtf(dirx * dirx + diry * diry + dirz * dirz);
+    const float x = dirx / len, y = diry / len, z = dirz / len;
+    const unsigned cl = a.clamped[i];
+    const float g3[3] = {(cl & 1u) ? 0.f : g1.z, (cl & 2u) ? 0.f : g1.w, (cl & 4u) ? 0.f : g2.x};
+    const float* sh = a.g.shs + (size_t)i * M * 3;
+    float* dsh = a.dL_dsh + (size_t)i * M * 3;
+    float ddir[3];
+    switch (a.v.deg) {
+      case 0: sh_backward<0>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
+      case 1: sh_backward<1>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
+      case 2: sh_backward<2>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
+      default: sh_backward<3>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
+    }
+    const float ng = x * ddir[0] + y * ddir[1] + z * ddir[2];
+    dmean[0] += (ddir[0] - x * ng) / len;
+    dmean[1] += (ddir[1] - y * ng) / len;
+    dmean[2] += (ddir[2] - z * ng) / len;
+  }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) a.dL_dmeans3D[3 * (size_t)i + j] = dmean[j];
+
+  // cov3D -> scale, rotation
+  if (!a.g.cov3D_precomp) {
+    const float4 q = reinterpret_cast<const float4*>(a.g.rotations)[i];
+    float R[3][3];
+    quat_to_R(q, R);
+    const float mod = a.v.scale_modifier;
+    const float s[3] = {mod * a.g.scales[3 * (size_t)i], mod * a.g.scales[3 * (size_t)i + 1],
+                        mod * a.g.scales[3 * (size_t)i + 2]};
+    const float Gm[3][3] = {{dS[0], 0.5f * dS[1], 0.5f * dS[2]},
+                            {0.5f * dS[1], dS[3], 0.5f * dS[4]},
+                            {0.5f * dS[2], 0.5f * dS[4], dS[5]}};
+    float dR[3][3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      float dsk = 0.f;
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const float dLrk = 2.f * (Gm[r][0] * R[0][k] + Gm[r][1] * R[1][k] + Gm[r][2] * R[2][k]) * s[k];
+        dsk += dLrk * R[r][k];
+        dR[r][k] = dLrk * s[k];
+      }
+      a.dL_dscales[3 * (size_t)i + k] = mod * dsk;
+    }
+    const float r = q.x, x = q.y, y = q.z, z = q.w;
+    float4 dq;
+    dq.x = 2.f * (-z * dR[0][1] + y * dR[0][2] + z * dR[1][0] - x * dR[1][2] - y * dR[2][0] + x * dR[2][1]);
+    dq.y = 2.f * (y * dR[0][1] + z * dR[0][2] + y * dR[1][0] - 2.f * x * dR[1][1] - r * dR[1][2] + z * dR[2][0] +
+                  r * dR[2][1] - 2.f * x * dR[2][2]);
+    dq.z = 2.f * (-2.f * y * dR[0][0] + x * dR[0][1] + r * dR[0][2] + x * dR[1][0] + z * dR[1][2] - r * dR[2][0] +
+                  z * dR[2][1] - 2.f * y * dR[2][2]);
+    dq.w = 2.f * (-2.f * z * dR[0][0] - r * dR[0][1] + x * dR[0][2] + r * dR[1][0] - 2.f * z * dR[1][1] +
+                  y * dR[1][2] + x * dR[2][0] + y * dR[2][1]);
+    reinterpret_cast<float4*>(a.dL_drot)[i] = dq;
+  } else {
+    for (int k = 0; k < 3; ++k) a.dL_dscales[3 * (size_t)i + k] = 0.f;
+    reinterpret_cast<float4*>(a.dL_drot)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+cudaError_t launch_preprocess_backward(const GsrView& v, const GsrGaussiansDev& g, const int32_t* radii,
+                                       const GeomState& geom, const float* grad_acc, float* dL_dmeans2D,
+                                       float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+                                       float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drot,
+                                       cudaStream_t s) {
+  if (g.P <= 0) return cudaSuccess;
+  PreBwdArgs a;
+  a.v = v; a.g = g; a.radii = radii; a.cov3D = geom.cov3D; a.clamped = geom.clamped; a.grad_acc = grad_acc;
+  a.dL_dmeans2D = dL_dmeans2D; a.dL_dcolors = dL_dcolors; a.dL_dopacity = dL_dopacity;
+  a.dL_dmeans3D = dL_dmeans3D; a.dL_dcov3D = dL_dcov3D; a.dL_dsh = (g.shs ? dL_dsh : nullptr);
+  a.dL_dscales = dL_dscales; a.dL_drot = dL_drot;
+  preprocess_backward_kernel<<<(g.P + 255) / 256, 256, 0, s>>>(a);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace gsr

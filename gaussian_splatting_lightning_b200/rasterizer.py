@@ -1,0 +1,252 @@
+"""Drop-in replacement of the `diff_gaussian_rasterization` Python package the reference imports
+(gs_lightning/lightning/gs_lightning_module.py:8-9, scripts/render_trained_image.py:10-11,
+tests/rasterizer_python/test_cases.py:2, tests/rasterizer_python/test_mark_visible.py:2).
+
+Same names, argument meaning and error behaviour as the package those call sites use:
+GaussianRasterizationSettings (13 fields, test_cases.py:7-18), GaussianRasterizer
+(.forward / .markVisible), rasterize_gaussians and the autograd Function _RasterizeGaussians
+returning (color, radii, invdepth) (gs_lightning_module.py:339, render_trained_image.py:115).
+The compute is libgsr_b200.so (hand-written sm_100a CUDA) reached through _native.py.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import NamedTuple, Optional
+
+import torch
+import torch.nn as nn
+
+from . import _native as N
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+    antialiasing: bool
+
+
+# Last num_rendered per (device, W, H): sizes the binning buffer of the next frame up front so
+# that the frame is enqueued without a device->host round trip (gsr_forward's binning_hint).
+_hint = {}
+
+
+def _sync_mode() -> bool:
+    return os.environ.get("GSR_SYNC_NUM_RENDERED", "0") == "1"
+
+
+class _Frame:
+    """Device tensors + ctypes structs of one call; keeps every tensor alive while the C call runs."""
+
+    def __init__(self, rs: GaussianRasterizationSettings, means3D, sh, colors_precomp, opacities, scales,
+                 rotations, cov3Ds_precomp):
+        if means3D.dim() != 2 or means3D.shape[1] != 3:
+            raise RuntimeError("means3D must have dimensions (num_points, 3)")
+        if not means3D.is_cuda:
+            raise RuntimeError("gaussian_splatting_lightning_b200 rasterizes on CUDA devices only (no CPU fallback)")
+        dev = means3D.device
+        self.device = dev
+        self.P = int(means3D.shape[0])
+        self.means3D = N.f32c(means3D) if self.P else means3D
+        self.sh = N.f32c(sh)
+        self.colors = N.f32c(colors_precomp)
+        self.opacities = N.f32c(opacities)
+        self.scales = N.f32c(scales)
+        self.rotations = N.f32c(rotations)
+        self.cov3D = N.f32c(cov3Ds_precomp)
+        self.M = int(self.sh.shape[1]) if self.sh is not None else 0
+        self.bg = N.f32c(rs.bg, dev)
+        self.view = N.f32c(rs.viewmatrix, dev)
+        self.proj = N.f32c(rs.projmatrix, dev)
+        self.campos = N.f32c(rs.campos, dev)
+        self.H, self.W = int(rs.image_height), int(rs.image_width)
+        self.settings = N.GsrSettings(
+            self.H, self.W, float(rs.tanfovx), float(rs.tanfovy), float(rs.scale_modifier), int(rs.sh_degree),
+            int(bool(rs.prefiltered)), int(bool(rs.debug)), int(bool(rs.antialiasing)),
+            N.ptr(self.bg), N.ptr(self.view), N.ptr(self.proj), N.ptr(self.campos))
+        self.gaussians = N.GsrGaussians(
+            self.P, self.M, N.ptr(self.means3D), N.ptr(self.opacities), N.ptr(self.sh), N.ptr(self.colors),
+            N.ptr(self.scales), N.ptr(self.rotations), N.ptr(self.cov3D))
+
+
+def forward_raw(rs: GaussianRasterizationSettings, means3D, sh, colors_precomp, opacities, scales, rotations,
+                cov3Ds_precomp, binning_hint: Optional[int] = None):
+    """_C.rasterize_gaussians: returns (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer,
+    invdepths, binning_capacity)."""
+    fr = _Frame(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
+    dev = fr.device
+    with torch.cuda.device(dev):
+        color = torch.empty((3, fr.H, fr.W), dtype=torch.float32, device=dev)
+        invdepth = torch.empty((1, fr.H, fr.W), dtype=torch.float32, device=dev)
+        radii = torch.empty((fr.P,), dtype=torch.int32, device=dev)
+        alloc = N.Allocator(dev)
+        key = (dev.index, fr.W, fr.H)
+        if binning_hint is None:
+            binning_hint = 0 if _sync_mode() else _hint.get(key, 0)
+        R = C.c_int64(0)
+        cap = C.c_int64(0)
+        rc = N.lib().gsr_forward(C.byref(fr.settings), C.byref(fr.gaussians), color.data_ptr(),
+                                 N.ptr(radii), invdepth.data_ptr(), alloc.cfunc, None,
+                                 int(binning_hint), C.byref(R), C.byref(cap), N.stream_ptr(dev))
+        if alloc.error is not None:
+            raise alloc.error
+        N.check(rc, "gsr_forward")
+        _hint[key] = int(R.value * 1.125) + 4096
+    return (int(R.value), color, radii, alloc.buffers[N.GSR_BUF_GEOM], alloc.buffers[N.GSR_BUF_BINNING],
+            alloc.buffers[N.GSR_BUF_IMG], invdepth, int(cap.value))
+
+
+def backward_raw(rs: GaussianRasterizationSettings, means3D, radii, sh, colors_precomp, opacities, scales,
+                 rotations, cov3Ds_precomp, dL_dcolor, dL_dinvdepth, geomBuffer, binningBuffer, imgBuffer,
+                 num_rendered: int):
+    """_C.rasterize_gaussians_backward: returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D,
+    dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)."""
+    fr = _Frame(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
+    dev, P, M = fr.device, fr.P, fr.M
+    with torch.cuda.device(dev):
+        e = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
+        g = dict(dL_dmeans2D=e(P, 3), dL_dcolors=e(P, 3), dL_dopacity=e(P, 1), dL_dmeans3D=e(P, 3),
+                 dL_dcov3D=e(P, 6), dL_dsh=e(P, M, 3), dL_dscales=e(P, 3), dL_drotations=e(P, 4))
+        if P == 0:
+            return tuple(g.values())
+        dL_dcolor = N.f32c(dL_dcolor, dev)
+        if dL_dcolor is None:
+            dL_dcolor = torch.zeros((3, fr.H, fr.W), dtype=torch.float32, device=dev)
+        dL_dinvdepth = N.f32c(dL_dinvdepth, dev)
+        scratch = torch.empty(N.lib().gsr_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
+        grads = N.GsrGrads(*[N.ptr(t) for t in g.values()])
+        rc = N.lib().gsr_backward(C.byref(fr.settings), C.byref(fr.gaussians), N.ptr(radii), N.ptr(dL_dcolor),
+                                  N.ptr(dL_dinvdepth), N.ptr(geomBuffer), N.ptr(binningBuffer), N.ptr(imgBuffer),
+                                  int(num_rendered), N.ptr(scratch), C.byref(grads), N.stream_ptr(dev))
+        N.check(rc, "gsr_backward")
+    return tuple(g.values())
+
+
+def mark_visible(positions: torch.Tensor, viewmatrix: torch.Tensor, projmatrix: torch.Tensor = None) -> torch.Tensor:
+    """_C.mark_visible (tests/rasterizer_python/test_mark_visible.py:13-14)."""
+    if not positions.is_cuda:
+        raise RuntimeError("mark_visible runs on CUDA devices only (no CPU fallback)")
+    dev = positions.device
+    p = N.f32c(positions)
+    P = int(positions.shape[0])
+    present = torch.zeros((P,), dtype=torch.uint8, device=dev)
+    if P:
+        v = N.f32c(viewmatrix, dev)
+        with torch.cuda.device(dev):
+            N.check(N.lib().gsr_mark_visible(P, N.ptr(p), N.ptr(v), N.ptr(present), N.stream_ptr(dev)),
+                    "gsr_mark_visible")
+    return present.bool()
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                raster_settings):
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths, _cap = forward_raw(
+            raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
+        ctx.raster_settings = raster_settings
+        ctx.num_rendered = num_rendered
+        ctx.has = tuple(t is not None and t.numel() > 0 for t in (sh, colors_precomp, scales, rotations, cov3Ds_precomp))
+        z = means3D.new_empty(0)
+        nz = lambda t: z if t is None else t
+        ctx.save_for_backward(nz(colors_precomp), means3D, nz(scales), nz(rotations), nz(cov3Ds_precomp), radii,
+                              nz(sh), opacities, geomBuffer, binningBuffer, imgBuffer)
+        ctx.mark_non_differentiable(radii)
+        ctx.set_materialize_grads(False)
+        return color, radii, invdepths
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _grad_radii, grad_out_depth):
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities, geomBuffer,
+         binningBuffer, imgBuffer) = ctx.saved_tensors
+        (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
+         dL_drotations) = backward_raw(ctx.raster_settings, means3D, radii, sh, colors_precomp, opacities, scales,
+                                       rotations, cov3Ds_precomp, grad_out_color, grad_out_depth, geomBuffer,
+                                       binningBuffer, imgBuffer, ctx.num_rendered)
+        has_sh, has_col, has_scale, has_rot, has_cov = ctx.has
+        return (dL_dmeans3D, dL_dmeans2D, dL_dsh if has_sh else None, dL_dcolors if has_col else None, dL_dopacity,
+                dL_dscales if has_scale else None, dL_drotations if has_rot else None,
+                dL_dcov3D if has_cov else None, None)
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                     cov3Ds_precomp, raster_settings)
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings: GaussianRasterizationSettings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        with torch.no_grad():
+            rs = self.raster_settings
+            return mark_visible(positions, rs.viewmatrix, rs.projmatrix)
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None):
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception("Please provide excatly one of either SHs or precomputed colors!")
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!")
+        if means2D is None:  # scripts/render_trained_image.py:117 passes None
+            means2D = means3D.new_zeros(means3D.shape)
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                                   cov3D_precomp, self.raster_settings)
+
+
+def export_state(rs: GaussianRasterizationSettings, P: int, radii, geomBuffer, binningBuffer, imgBuffer,
+                 num_rendered: int, binning_capacity: int = 0) -> dict:
+    """Canonical-layout dump of the opaque scratch buffers as torch tensors."""
+    dev = radii.device
+    H, W = int(rs.image_height), int(rs.image_width)
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    R = int(num_rendered)
+    f = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)
+    out = dict(depths=f(P), means2D=f(P, 2), cov3D=f(P, 6), conic_opacity=f(P, 4), rgb=f(P, 3),
+               clamped=torch.zeros((P, 3), dtype=torch.uint8, device=dev),
+               tiles_touched=torch.zeros((P,), dtype=torch.int32, device=dev),
+               point_offsets=torch.zeros((P,), dtype=torch.int32, device=dev),
+               keys_unsorted=torch.zeros((R,), dtype=torch.int64, device=dev),
+               vals_unsorted=torch.zeros((R,), dtype=torch.int32, device=dev),
+               keys_sorted=torch.zeros((R,), dtype=torch.int64, device=dev),
+               vals_sorted=torch.zeros((R,), dtype=torch.int32, device=dev),
+               ranges=torch.zeros((T, 2), dtype=torch.int32, device=dev),
+               final_T=f(H, W), n_contrib=torch.zeros((H, W), dtype=torch.int32, device=dev))
+    bg, view, proj, campos = (N.f32c(t, dev) for t in (rs.bg, rs.viewmatrix, rs.projmatrix, rs.campos))
+    st = N.GsrSettings(H, W, float(rs.tanfovx), float(rs.tanfovy), float(rs.scale_modifier), int(rs.sh_degree), 0, 0,
+                       int(bool(rs.antialiasing)), N.ptr(bg), N.ptr(view), N.ptr(proj), N.ptr(campos))
+    ex = N.GsrStateExport(*[N.ptr(out[k]) for k in N._EXPORT_FIELDS])
+    with torch.cuda.device(dev):
+        N.check(N.lib().gsr_export_state(C.byref(st), P, N.ptr(radii), N.ptr(geomBuffer), N.ptr(binningBuffer),
+                                         N.ptr(imgBuffer), R, int(binning_capacity), C.byref(ex),
+                                         N.stream_ptr(dev)), "gsr_export_state")
+        torch.cuda.synchronize(dev)
+    return out
+
+
+def sort_pairs(keys: torch.Tensor, vals: torch.Tensor, end_bit: int = 64):
+    """Stand-alone entry to the onesweep radix sort: stable sort of (int64 key, int32 value) pairs on key
+    bits [0, end_bit) (keys are treated as unsigned)."""
+    assert keys.is_cuda and keys.dtype == torch.int64 and vals.dtype == torch.int32 and keys.numel() == vals.numel()
+    dev, n = keys.device, keys.numel()
+    keys, vals = keys.contiguous(), vals.contiguous()
+    ko, vo, kt, vt = torch.empty_like(keys), torch.empty_like(vals), torch.empty_like(keys), torch.empty_like(vals)
+    ws = torch.empty(N.lib().gsr_sort_workspace_bytes(n), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        N.check(N.lib().gsr_sort_pairs(N.ptr(keys), N.ptr(vals), N.ptr(ko), N.ptr(vo), N.ptr(kt), N.ptr(vt), n,
+                                       int(end_bit), N.ptr(ws), N.stream_ptr(dev)), "gsr_sort_pairs")
+    return ko, vo

@@ -1,0 +1,177 @@
+/* gsr_b200.h -- C-ABI of the B200-native 3D Gaussian Splatting rasterizer (libgsr_b200.so).
+ *
+ * This is the drop-in boundary for the rasterizer hot path of
+ * pomelyu/gaussian_splatting_lightning.  Each entry point replaces one function of the
+ * `diff_gaussian_rasterization._C` extension the reference calls (the extension's source,
+ * graphdeco-inria/diff-gaussian-rasterization @ 9c5c2028, is an un-vendored submodule:
+ * /root/reference/.gitmodules:1-4, .SUBMODULES.json:9-15), so the citations below are the
+ * reference's CALL SITES, which fix the contract:
+ *
+ *   gsr_forward       <- _C.rasterize_gaussians            gs_lightning/lightning/gs_lightning_module.py:337-348
+ *                                                            scripts/render_trained_image.py:113-124
+ *   gsr_backward      <- _C.rasterize_gaussians_backward    autograd of the call above; the dummy
+ *                                                            means2D leaf at gs_lightning_module.py:316-317,177
+ *   gsr_mark_visible  <- _C.mark_visible                    tests/rasterizer_python/test_mark_visible.py:13-14
+ *                                                            (python twin gs_lightning/rasterize/rasterize.py:23-26)
+ *   gsr_alloc_fn      <- the resizeFunctional buffer lambda notes/rasterizer_note.h:27-40
+ *
+ * Conventions
+ *   - every pointer marked "device" is a CUDA device pointer on the CURRENT device; the
+ *     caller selects the device (cudaSetDevice / torch.cuda.device) before the call.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - all entry points return GSR_OK (0) or a negative GSR_E* code; gsr_last_error() gives
+ *     the message of the last failure on the calling thread.
+ *   - matrices use the reference's row-vector convention: p_view = [p,1] @ viewmatrix,
+ *     element (r,c) at flat index 4r+c (tests/rasterizer_python/test_cases.py:23-28).
+ *   - nothing here takes or returns a torch type.
+ */
+#ifndef GSR_B200_H
+#define GSR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSR_OK 0
+#define GSR_EINVAL (-1)  /* bad argument (shape, NULL, alignment)        */
+#define GSR_ECUDA (-2)   /* a CUDA runtime call or kernel failed         */
+#define GSR_EALLOC (-3)  /* the allocation callback returned NULL        */
+#define GSR_ELIMIT (-4)  /* a size exceeds what the kernels index (2^30) */
+
+#define GSR_BUF_GEOM 0
+#define GSR_BUF_BINNING 1
+#define GSR_BUF_IMG 2
+
+/* Grows buffer `which` (GSR_BUF_*) to at least `bytes` and returns its device pointer
+ * (128-byte aligned).  May be called more than once per buffer in one gsr_forward; the
+ * last returned pointer is the live one.  notes/rasterizer_note.h:27-40. */
+typedef void* (*gsr_alloc_fn)(void* user, int which, size_t bytes);
+
+/* The 13 fields of GaussianRasterizationSettings (tests/rasterizer_python/test_cases.py:7-18,
+ * gs_lightning_module.py:322-336).  Tensor-valued fields stay on the device so that a call
+ * never forces a device-to-host copy. */
+typedef struct GsrSettings {
+  int32_t image_height;
+  int32_t image_width;
+  float tanfovx;
+  float tanfovy;
+  float scale_modifier;
+  int32_t sh_degree;
+  int32_t prefiltered;       /* accepted, no effect (reference always passes False) */
+  int32_t debug;             /* synchronise + check after every kernel             */
+  int32_t antialiasing;
+  const float* bg;           /* device (3)  */
+  const float* viewmatrix;   /* device (16) */
+  const float* projmatrix;   /* device (16) */
+  const float* campos;       /* device (3)  */
+} GsrSettings;
+
+/* Borrowed, read-only Gaussian parameters exactly as GaussianModel.get_* returns them
+ * (gs_lightning/modules/gaussian_model.py:317-330): contiguous fp32, AoS. */
+typedef struct GsrGaussians {
+  int32_t P;                    /* number of Gaussians                                  */
+  int32_t M;                    /* SH coefficients stored per Gaussian (shs is P x M x 3) */
+  const float* means3D;         /* device (P,3)                                          */
+  const float* opacities;       /* device (P,1)                                          */
+  const float* shs;             /* device (P,M,3) or NULL when colors_precomp is given   */
+  const float* colors_precomp;  /* device (P,3) or NULL                                  */
+  const float* scales;          /* device (P,3) or NULL when cov3D_precomp is given      */
+  const float* rotations;       /* device (P,4) (w,x,y,z) or NULL                        */
+  const float* cov3D_precomp;   /* device (P,6) or NULL                                  */
+} GsrGaussians;
+
+/* Gradients produced by gsr_backward; same order and shapes as the tuple
+ * _C.rasterize_gaussians_backward returns.  All device, all fully written. */
+typedef struct GsrGrads {
+  float* dL_dmeans2D;   /* (P,3)  z = 0; consumer takes [:, :2] (gaussian_model.py:180) */
+  float* dL_dcolors;    /* (P,3)                                                         */
+  float* dL_dopacity;   /* (P,1)                                                         */
+  float* dL_dmeans3D;   /* (P,3)                                                         */
+  float* dL_dcov3D;     /* (P,6)                                                         */
+  float* dL_dsh;        /* (P,M,3) or NULL                                               */
+  float* dL_dscales;    /* (P,3)                                                         */
+  float* dL_drotations; /* (P,4)                                                         */
+} GsrGrads;
+
+/* Canonical-layout export of the opaque scratch buffers for the
+ * bit-exact parity checks.  Any pointer may be NULL (skipped). All device. */
+typedef struct GsrStateExport {
+  float* depths;            /* (P)    0 where culled */
+  float* means2D;           /* (P,2)                 */
+  float* cov3D;             /* (P,6)                 */
+  float* conic_opacity;     /* (P,4)                 */
+  float* rgb;               /* (P,3)                 */
+  uint8_t* clamped;         /* (P,3)                 */
+  uint32_t* tiles_touched;  /* (P)                   */
+  uint32_t* point_offsets;  /* (P) inclusive scan    */
+  uint64_t* keys_unsorted;  /* (R)                   */
+  uint32_t* vals_unsorted;  /* (R)                   */
+  uint64_t* keys_sorted;    /* (R)                   */
+  uint32_t* vals_sorted;    /* (R) = point_list      */
+  uint32_t* ranges;         /* (T,2)                 */
+  float* final_T;           /* (H,W)                 */
+  uint32_t* n_contrib;      /* (H,W)                 */
+} GsrStateExport;
+
+/* Library / build identification: "gsr_b200 <version> sm_100a". */
+const char* gsr_version(void);
+const char* gsr_last_error(void);
+
+/* Scratch sizes (bytes).  binning is a function of the instance capacity, not of P. */
+size_t gsr_geom_bytes(int32_t P);
+size_t gsr_img_bytes(int32_t image_width, int32_t image_height);
+size_t gsr_binning_bytes(int64_t capacity, int32_t image_width, int32_t image_height);
+size_t gsr_backward_scratch_bytes(int32_t P);
+
+/* Forward: preprocess -> scan -> duplicate keys -> onesweep radix sort -> tile ranges ->
+ * compositing.  Writes out_color (3,H,W), radii (P) int32, out_invdepth (1,H,W).
+ *
+ * binning_hint = 0 reproduces upstream's behaviour: one blocking read of num_rendered
+ * after the scan, then the binning buffer is sized exactly.  binning_hint > 0 sizes the
+ * binning buffer to that many instances up front and enqueues the whole frame without a
+ * host round trip; num_rendered is read afterwards and, if it exceeded the hint, the
+ * binning + compositing stages are re-run with a large enough buffer (results are always
+ * exact).  *num_rendered receives R = sum(tiles_touched); *binning_capacity (may be NULL)
+ * the instance capacity the live binning buffer was laid out for. */
+int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, float* out_color,
+                int32_t* radii, float* out_invdepth, gsr_alloc_fn alloc, void* alloc_user,
+                int64_t binning_hint, int64_t* num_rendered, int64_t* binning_capacity, void* stream);
+
+/* Backward from the three scratch buffers the forward left behind (read-only here).
+ * dL_dinvdepth may be NULL.  `scratch` is gsr_backward_scratch_bytes(P) of device memory. */
+int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, const int32_t* radii,
+                 const float* dL_dcolor, const float* dL_dinvdepth, const void* geom,
+                 const void* binning, const void* img, int64_t num_rendered, void* scratch,
+                 const GsrGrads* grads, void* stream);
+
+/* present[i] = ([p_i,1] @ viewmatrix).z > 0.2   (camera_tools.py:5-8). */
+int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, uint8_t* present,
+                     void* stream);
+
+/* Debug accessor over the buffers of one gsr_forward call (binning_capacity as returned by
+ * it).  keys_unsorted / vals_unsorted are regenerated by re-running the duplication kernel
+ * because the sort ping-pongs over its input. */
+int gsr_export_state(const GsrSettings* settings, int32_t P, const int32_t* radii, const void* geom,
+                     const void* binning, const void* img, int64_t num_rendered, int64_t binning_capacity,
+                     const GsrStateExport* out, void* stream);
+
+/* Stand-alone entry to the hand-written onesweep radix sort (stable, LSD, 8-bit digits)
+ * used between key duplication and tile ranges: sorts n (key,value) pairs on key bits
+ * [0, end_bit).  workspace: gsr_sort_workspace_bytes(n) bytes of device memory.
+ * keys_out/vals_out receive the result; keys_tmp/vals_tmp are ping-pong storage of n
+ * elements each. */
+size_t gsr_sort_workspace_bytes(int64_t n);
+int gsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                   uint32_t* vals_out, uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n,
+                   int32_t end_bit, void* workspace, void* stream);
+
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+int64_t gsr_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSR_B200_H */
