@@ -111,7 +111,8 @@ def test_forward_matches_reference_python_golden(results, name):
     img = out["color"].cpu().numpy()
     err = np.abs(img - d["ref_image"])
     tol = 1e-4 + 1e-4 * np.abs(d["ref_image"])
-    assert ((err > tol)[:, unsat]).mean() <= OUTLIER_FRAC
+    if unsat.any():
+        assert ((err > tol)[:, unsat]).mean() <= OUTLIER_FRAC
     assert err.max() <= 2e-2  # saturated pixels: rasterize.py:253-256 keeps one more splat (Appendix B3)
     radii = out["radii"].cpu().numpy()
     vis = radii > 0
