@@ -1,0 +1,428 @@
+#!/usr/bin/env python
+"""bench.py -- rendered frames/sec of the rasterizer hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C3]
+
+Workload (config.workload): BASELINE.json configs[2] = "C3": 1M synthetic Gaussians, SH degree 3,
+1920x1080, forward + backward training step with densification statistics.  One STEP = one batch of
+`--views-per-rank` (default 8) camera views per GPU, each view a full forward + backward of the hot
+path with gradients accumulated into one flat per-Gaussian buffer; with N > 1 ranks every rank renders
+its own views against the replicated Gaussian set and the step ends with one NCCL all-reduce of the
+flat gradient buffer and of the densification statistics (view-parallel, weak scaling).
+value = frames (views) per second over all ranks, device-timed, max over ranks.
+
+Printed JSON keys follow the driver's contract; see DESIGN.md section "Measurement".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+from gaussian_splatting_lightning_b200 import synthetic  # noqa: E402
+
+METRIC = "rendered frames/sec fwd+bwd @1M Gaussians 1080p SH3"
+UNIT = "frames/s"
+ORBIT_VIEWS = 256  # bench views orbit the scene centre in steps of 2*pi/256 around view 0
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C3", choices=list(synthetic.CONFIGS))
+    ap.add_argument("--views-per-rank", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def view_index(rank: int, j: int, vpr: int) -> int:
+    """global view g -> orbit slot: 0, +1, -1, +2, -2, ... around view 0."""
+    g = rank * vpr + j
+    return ((g + 1) // 2) * (1 if g % 2 else -1) % ORBIT_VIEWS
+
+
+def make_cameras(W, H, rank, vpr, device):
+    from gaussian_splatting_lightning_b200.rasterizer import GaussianRasterizationSettings
+    cams = []
+    bg = torch.zeros(3, device=device)
+    for j in range(vpr):
+        c = synthetic.make_camera(W, H, k=view_index(rank, j, vpr), num_views=ORBIT_VIEWS)
+        cams.append(dict(host=c, settings=GaussianRasterizationSettings(
+            image_height=H, image_width=W, tanfovx=c["tanfovx"], tanfovy=c["tanfovy"], bg=bg, scale_modifier=1.0,
+            viewmatrix=c["viewmatrix"].to(device), projmatrix=c["projmatrix"].to(device), sh_degree=3,
+            campos=c["campos"].to(device), prefiltered=False, debug=False, antialiasing=False)))
+    return cams
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.gpu), "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        rows = [l for (t, l) in self.lines if t0 <= t <= t1 + 0.2] or [l for (_, l) in self.lines]
+        for l in rows:
+            f = [x.strip() for x in l.split(",")]
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)", 1965.0
+
+
+def stage_model(P, M, Pvis, R, L, A, HW, T, passes):
+    """Algorithmic bytes / flops per frame of every stage."""
+    return {
+        "preprocess": dict(bytes=52 * P + (12 * M + 67) * Pvis),
+        "scan": dict(bytes=8 * P),
+        "duplicate": dict(bytes=8 * P + 12 * Pvis + 12 * R),
+        "sort": dict(bytes=(8 + 24 * passes) * R),
+        "tile_ranges": dict(bytes=8 * R + 8 * T),
+        "render_forward": dict(bytes=44 * L + 24 * HW, flops=24 * A, ex2=A),
+        "render_backward": dict(bytes=84 * L + 24 * HW, flops=75 * A, ex2=A),
+        "preprocess_backward": dict(bytes=(187 + 24 * M) * Pvis),
+    }
+
+
+def workload_counters(cams, scene, device):
+    """P_vis, R, L, A averaged over this rank's views, from radii / n_contrib of the CUDA forward
+    (the oracle's definitions: L = sum over tiles of the max n_contrib, A = sum over pixels)."""
+    from gaussian_splatting_lightning_b200.rasterizer import export_state, forward_raw
+    acc = dict(Pvis=0.0, R=0.0, L=0.0, A=0.0)
+    for c in cams:
+        rs = c["settings"]
+        R, color, radii, geom, binning, img, invd, cap = forward_raw(
+            rs, scene["means3D"], scene["shs"], None, scene["opacities"], scene["scales"], scene["rotations"], None,
+            binning_hint=0)
+        st = export_state(rs, scene["means3D"].shape[0], radii, geom, binning, img, R, cap)
+        nc = st["n_contrib"].to(torch.int64)
+        H, W = nc.shape
+        gy, gx = (H + 15) // 16, (W + 15) // 16
+        pad = torch.zeros((gy * 16, gx * 16), dtype=torch.int64, device=device)
+        pad[:H, :W] = nc
+        tile_max = pad.view(gy, 16, gx, 16).amax(dim=(1, 3))
+        acc["Pvis"] += float((radii > 0).sum()); acc["R"] += float(R)
+        acc["L"] += float(tile_max.sum()); acc["A"] += float(nc.sum())
+        del st
+    return {k: v / len(cams) for k, v in acc.items()}
+
+
+def run_ours(args):
+    from gaussian_splatting_lightning_b200 import _native as N
+    from gaussian_splatting_lightning_b200.rasterizer import GaussianRasterizer, backward_raw, forward_raw
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    P, deg, W, H = synthetic.config(args.workload)
+    M = (deg + 1) ** 2
+    vpr = args.views_per_rank
+    scene_cpu = synthetic.make_scene(P, deg, W, H, seed=0)
+    scene = {k: v.to(device) for k, v in scene_cpu.items()}
+    cams = make_cameras(W, H, rank, vpr, device)
+    for c in cams:
+        c["settings"] = c["settings"]._replace(sh_degree=deg)
+    g = torch.Generator(device="cpu").manual_seed(1234 + rank)
+    dL_dcolor = torch.randn(3, H, W, generator=g).to(device)
+    dL_dinv = torch.randn(1, H, W, generator=g).to(device)
+
+    # flat per-Gaussian gradient buffer [means3D 3 | sh 3M | opacity 1 | scales 3 | rot 4] = 59 floats at M=16
+    widths = [3, 3 * M, 1, 3, 4]
+    flat = torch.zeros(P * sum(widths), device=device)
+    views_flat, o = [], 0
+    for w_ in widths:
+        views_flat.append(flat[o:o + P * w_].view(P, w_)); o += P * w_
+    stats = torch.zeros(2, P, device=device)      # xyz_grad_accum, xyz_grad_count (gaussian_model.py:174-181)
+    max_radii = torch.zeros(P, device=device)
+
+    def one_view(c, fwd_only=False):
+        rs = c["settings"]
+        R, color, radii, geom, binning, img, invd, cap = forward_raw(
+            rs, scene["means3D"], scene["shs"], None, scene["opacities"], scene["scales"], scene["rotations"], None)
+        if fwd_only:
+            return color
+        (d2, dcol, dop, d3, dcov, dsh, dsc, drot) = backward_raw(
+            rs, scene["means3D"], radii, scene["shs"], None, scene["opacities"], scene["scales"], scene["rotations"],
+            None, dL_dcolor, dL_dinv, geom, binning, img, R)
+        for dst, src in zip(views_flat, (d3, dsh.view(P, -1), dop, dsc, drot)):
+            dst.add_(src)
+        vis = radii > 0                                           # densification statistics of this view
+        torch.maximum(max_radii, radii.to(torch.float32), out=max_radii)
+        stats[0].add_(d2[:, :2].norm(dim=-1) * vis)
+        stats[1].add_(vis)
+        return color
+
+    def step(fwd_only=False):
+        if not fwd_only:
+            flat.zero_()
+        for c in cams:
+            one_view(c, fwd_only)
+        if world > 1 and not fwd_only:
+            dist.all_reduce(flat)
+            dist.all_reduce(stats)
+            dist.all_reduce(max_radii, op=dist.ReduceOp.MAX)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.time()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t1 = time.time()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=device)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), t0, t1
+
+    counters = workload_counters(cams, scene, device)
+    K, Wm = args.steps, max(args.warmup, 3)
+
+    # ---- headline: fwd+bwd, inputs resident in HBM, per-stage events on -------------------------
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    for _ in range(Wm):
+        step()
+    torch.cuda.synchronize()
+    N.profile_reset(); N.profile_enable(True)
+    l0 = N.launch_count()
+    ms_total, t0, t1 = timed(step, K, 0)
+    launches = N.launch_count() - l0
+    prof = N.profile_read(); N.profile_enable(False)
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    ms_fwd, _, _ = timed(lambda: step(True), K, 2)
+
+    frames = K * vpr * world
+    value = frames / (ms_total / 1e3)
+    fwd_value = frames / (ms_fwd / 1e3)
+
+    # ---- e2e: public API, host buffers (pinned GT image + camera) -> loss on the host -------------
+    e2e = None
+    if not args.no_e2e:
+        params = {k: scene[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+        gt_host = [torch.rand(3, H, W).pin_memory() for _ in cams]
+        cam_host = [torch.cat([c["host"]["viewmatrix"].reshape(-1), c["host"]["projmatrix"].reshape(-1),
+                               c["host"]["campos"].reshape(-1), torch.zeros(3)]).pin_memory() for c in cams]
+        loss_host = torch.zeros(vpr).pin_memory()
+
+        def e2e_step():
+            for p_ in params.values():
+                p_.grad = None
+            for j, c in enumerate(cams):
+                cam_d = cam_host[j].to(device, non_blocking=True)
+                gt = gt_host[j].to(device, non_blocking=True)
+                rs = c["settings"]._replace(viewmatrix=cam_d[0:16].view(4, 4), projmatrix=cam_d[16:32].view(4, 4),
+                                            campos=cam_d[32:35], bg=cam_d[35:38])
+                sp = torch.zeros_like(params["means3D"], requires_grad=True)
+                color, radii, invd = GaussianRasterizer(rs)(
+                    means3D=params["means3D"], means2D=sp, shs=params["shs"], colors_precomp=None,
+                    opacities=params["opacities"], scales=params["scales"], rotations=params["rotations"],
+                    cov3D_precomp=None)
+                loss = (color - gt).abs().mean()
+                loss.backward()
+                loss_host[j].copy_(loss.detach(), non_blocking=True)
+            if world > 1:
+                for p_ in params.values():
+                    dist.all_reduce(p_.grad)
+            torch.cuda.current_stream().synchronize()   # the step's result (losses) is on the host
+            return float(loss_host.sum())
+
+        ms_e2e, _, _ = timed(e2e_step, K, 2)
+        h2d = vpr * (3 * H * W * 4 + 38 * 4)
+        e2e = {"value": frames / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": vpr * 4,
+               "what": "GaussianRasterizer autograd API + L1 loss; per view: pinned GT image and camera H2D, loss D2H"}
+        del params
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- per-stage roofline ------------------------------------------------------------------------
+    hbm_peak, peak_src, sm_max = peaks()
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    passes = (32 + max(1, (T - 1).bit_length()) + 7) // 8
+    model = stage_model(P, M, counters["Pvis"], counters["R"], counters["L"], counters["A"], H * W, T, passes)
+    stages, stage_sum = [], 0.0
+    for name, (tot_ms, calls) in prof.items():
+        if calls == 0:
+            continue
+        avg_ms = tot_ms / calls
+        stage_sum += tot_ms
+        m = model[name]
+        s = {"stage": name, "ms_per_frame": avg_ms, "calls": calls, "algorithmic_bytes": m["bytes"],
+             "GBps": m["bytes"] / (avg_ms * 1e6), "hbm_frac": m["bytes"] / (avg_ms * 1e6) / hbm_peak}
+        if "flops" in m:
+            s["TFLOPs_fp32"] = m["flops"] / (avg_ms * 1e9)
+            s["Gex2_per_s"] = m["ex2"] / (avg_ms * 1e6)
+        stages.append(s)
+    for s in stages:
+        s["share_of_kernel_time"] = s["ms_per_frame"] * s["calls"] / stage_sum
+    dom = max(stages, key=lambda s: s["ms_per_frame"] * s["calls"])
+    roofline = {"kernel": dom["stage"], "bound": "hbm", "achieved": dom["GBps"], "peak": hbm_peak, "unit": "GB/s",
+                "frac": dom["hbm_frac"], "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": dom["algorithmic_bytes"], "ms_per_launch": dom["ms_per_frame"],
+                "note": "the compositing kernels are FP32-issue bound, not HBM bound: see stages[].TFLOPs_fp32"}
+    fp32_peak = 148 * 128 * 2 * (clocks["sm_mhz"] or sm_max) * 1e6 / 1e12 if clocks else None
+    if "TFLOPs_fp32" in dom and fp32_peak:
+        roofline["fp32"] = {"achieved_TFLOPs": dom["TFLOPs_fp32"], "peak_TFLOPs_at_observed_clock": fp32_peak,
+                            "frac": dom["TFLOPs_fp32"] / fp32_peak}
+
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        cpu_baseline = cpu_oracle_frames_per_s(args.workload, scene_cpu, cams[0]["host"], 1)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {P} Gaussians, SH degree {deg}, {W}x{H}, fwd+bwd + densification "
+                               f"stats, {vpr} views per GPU per step" + (", NCCL all-reduce of 59 floats/Gaussian + stats" if world > 1 else ""),
+                   "views_per_rank": vpr, "frames_per_step": vpr * world, "parallelism": f"view-parallel x{world}",
+                   "l2": "inputs (236 MB of Gaussian parameters + 49 MB records) exceed the 126 MB L2; no flush",
+                   "num_rendered_mean": counters["R"], "visible_mean": counters["Pvis"],
+                   "pairs_A_mean": counters["A"], "list_entries_L_mean": counters["L"]},
+        "forward_only": {"value": fwd_value, "unit": UNIT, "ms_per_step": ms_fwd / K},
+        "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "stages": stages,
+        "cpu_baseline": cpu_baseline,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_oracle_frames_per_s(workload, scene_cpu, cam_host, repeats):
+    """The CPU restatement (oracle/, C++/OpenMP, 'port') timed on the host cores: full frames of the
+    same workload, forward + backward.  This is the one place bench.py executes oracle/."""
+    import oracle
+    oracle.build()
+    P, deg, W, H = synthetic.config(workload)
+    cam = oracle.Camera(H, W, cam_host["tanfovx"], cam_host["tanfovy"], cam_host["viewmatrix"].numpy(),
+                        cam_host["projmatrix"].numpy(), cam_host["campos"].numpy(), sh_degree=deg)
+    a = {k: v.numpy() for k, v in scene_cpu.items()}
+    rng = np.random.default_rng(0)
+    dC = rng.standard_normal((3, H, W)).astype(np.float32)
+    dD = rng.standard_normal((H, W)).astype(np.float32)
+    cores = oracle.num_threads()
+    times = []
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        st = oracle.forward(cam, a["means3D"], a["scales"], a["rotations"], a["opacities"], shs=a["shs"])
+        t1 = time.perf_counter()
+        oracle.backward(st, dC, dD)
+        t2 = time.perf_counter()
+        times.append((t2 - t0, t1 - t0))
+    tot = float(np.median([t[0] for t in times]))
+    fwd = float(np.median([t[1] for t in times]))
+    return {"value": 1.0 / tot, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{repeats} full frame(s) of {workload} (view 0), forward + backward, oracle/gsr_oracle.cpp with OpenMP "
+                      f"on {cores} threads; forward alone {fwd:.2f} s, forward+backward {tot:.2f} s per frame",
+            "forward_only_value": 1.0 / fwd}
+
+
+def run_reference(args):
+    """Reference arm: the reference's CPU implementation of the path.  Its CUDA rasterizer source is
+    absent (un-vendored submodule) and its Python rasterizer is forward-only and cannot hold this
+    workload (O(tiles x P) mask), so the arm times the CPU restatement under oracle/ ('port')."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    P, deg, W, H = synthetic.config(args.workload)
+    scene_cpu = synthetic.make_scene(P, deg, W, H, seed=0)
+    cam = synthetic.make_camera(W, H, k=0, num_views=ORBIT_VIEWS)
+    K = max(1, min(args.steps, 3))
+    for _ in range(min(args.warmup, 1)):
+        cpu_oracle_frames_per_s(args.workload, scene_cpu, cam, 1)
+    t0 = time.perf_counter()
+    cb = cpu_oracle_frames_per_s(args.workload, scene_cpu, cam, K)
+    wall = time.perf_counter() - t0
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": min(args.warmup, 1), "ms_per_step": 1e3 / cb["value"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {P} Gaussians, SH degree {deg}, {W}x{H}, fwd+bwd; one frame per step",
+                       "note": "steps capped at 3 frames so the run ends within minutes; wall %.1f s" % wall},
+            "cpu_baseline": cb, "gpu_launches": 0,
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

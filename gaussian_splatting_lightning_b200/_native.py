@@ -53,7 +53,9 @@ class GsrStateExport(C.Structure):
 EXPORTED_SYMBOLS = [
     "gsr_version", "gsr_last_error", "gsr_geom_bytes", "gsr_img_bytes", "gsr_binning_bytes",
     "gsr_backward_scratch_bytes", "gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_export_state",
-    "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count",
+    "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count", "gsr_profile_enable", "gsr_profile_reset",
+    "gsr_profile_collect", "gsr_profile_stage_count", "gsr_profile_stage_name", "gsr_profile_stage_ms",
+    "gsr_profile_stage_calls",
 ]
 
 _lib = None
@@ -101,8 +103,28 @@ def lib():
     L.gsr_sort_pairs.restype = C.c_int
     L.gsr_sort_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                  C.c_int32, C.c_void_p, C.c_void_p]
+    L.gsr_profile_stage_name.restype = C.c_char_p
+    L.gsr_profile_stage_ms.restype = C.c_double
+    L.gsr_profile_stage_calls.restype = C.c_int64
+    L.gsr_profile_reset.restype = None
     _lib = L
     return L
+
+
+def profile_enable(on: bool) -> None:
+    lib().gsr_profile_enable(int(on))
+
+
+def profile_reset() -> None:
+    lib().gsr_profile_reset()
+
+
+def profile_read() -> dict:
+    """{stage: (total_ms, calls)} after waiting for the recorded events."""
+    L = lib()
+    check(L.gsr_profile_collect(), "gsr_profile_collect")
+    return {L.gsr_profile_stage_name(i).decode(): (float(L.gsr_profile_stage_ms(i)), int(L.gsr_profile_stage_calls(i)))
+            for i in range(L.gsr_profile_stage_count())}
 
 
 def check(rc: int, what: str) -> None:

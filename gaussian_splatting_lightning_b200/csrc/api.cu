@@ -6,7 +6,9 @@
 #include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
+#include <vector>
 
 #include "../../include/gsr_b200.h"
 #include "gsr_common.cuh"
@@ -31,11 +33,50 @@ int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
     if (e_ != cudaSuccess) return fail(GSR_ECUDA, what, e_);   \
   } while (0)
 
+// Optional per-stage timing (bench.py's roofline): CUDA events on the launching stream around
+// every stage, folded into per-stage totals by gsr_profile_collect().
+enum Stage { ST_PREPROCESS, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_RANGES, ST_RENDER_FWD, ST_RENDER_BWD, ST_PREPROCESS_BWD,
+             ST_COUNT };
+const char* const kStageNames[ST_COUNT] = {"preprocess", "scan", "duplicate", "sort", "tile_ranges", "render_forward",
+                                           "render_backward", "preprocess_backward"};
+struct ProfRec { int stage; cudaEvent_t a, b; };
+std::mutex g_prof_mu;
+bool g_prof_on = false;
+std::vector<ProfRec> g_prof_pending;
+std::vector<cudaEvent_t> g_prof_free;
+double g_prof_ms[ST_COUNT] = {0};
+long long g_prof_n[ST_COUNT] = {0};
+
+cudaEvent_t prof_event() {
+  if (!g_prof_free.empty()) { cudaEvent_t e = g_prof_free.back(); g_prof_free.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+struct ProfScope {
+  bool on; int stage; cudaStream_t s; cudaEvent_t a;
+  ProfScope(int stage_, cudaStream_t s_) : on(g_prof_on), stage(stage_), s(s_), a(nullptr) {
+    if (on) { std::lock_guard<std::mutex> l(g_prof_mu); a = prof_event(); cudaEventRecord(a, s); }
+  }
+  ~ProfScope() {
+    if (on) {
+      std::lock_guard<std::mutex> l(g_prof_mu);
+      cudaEvent_t b = prof_event();
+      cudaEventRecord(b, s);
+      g_prof_pending.push_back({stage, a, b});
+    }
+  }
+};
+
 // With settings->debug every stage is followed by a synchronise + error check that names
 // the stage (the CHECK_CUDA behaviour of notes/rasterizer_note.h:44-53).
-#define GSR_STAGE(expr, what, debug, stream)                                  \
+#define GSR_STAGE(id, expr, what, debug, stream)                              \
   do {                                                                        \
-    cudaError_t e_ = (expr);                                                  \
+    cudaError_t e_;                                                           \
+    {                                                                         \
+      ProfScope prof_(id, stream);                                            \
+      e_ = (expr);                                                            \
+    }                                                                         \
     if (e_ != cudaSuccess) return fail(GSR_ECUDA, what, e_);                  \
     if (debug) {                                                              \
       e_ = cudaStreamSynchronize(stream);                                     \
@@ -155,8 +196,8 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
   GSR_CUDA(cudaMemsetAsync(img_ptr + img.ranges_off, 0, img.bytes - img.ranges_off, stream), "memset(ranges)");
   GSR_CUDA(cudaMemsetAsync(geom.scan_state, 0, geom.scan_state_bytes(P), stream), "memset(scan state)");
 
-  GSR_STAGE(gsr::launch_preprocess(v, g, radii, geom, stream), "preprocess kernel", debug, stream);
-  GSR_STAGE(gsr::launch_scan(P, geom, img.ctrl, stream), "scan kernel", debug, stream);
+  GSR_STAGE(ST_PREPROCESS, gsr::launch_preprocess(v, g, radii, geom, stream), "preprocess kernel", debug, stream);
+  GSR_STAGE(ST_SCAN, gsr::launch_scan(P, geom, img.ctrl, stream), "scan kernel", debug, stream);
 
   Mailbox* mail = nullptr;
   rc = get_mailbox(&mail);
@@ -184,15 +225,15 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
       uint32_t* v0 = (npass % 2 == 0) ? bin.vals_a : bin.vals_b;
       unsigned long long* k1 = (npass % 2 == 0) ? bin.keys_b : bin.keys_a;
       uint32_t* v1 = (npass % 2 == 0) ? bin.vals_b : bin.vals_a;
-      GSR_STAGE(gsr::launch_duplicate(v, P, radii, geom, k0, v0, (uint32_t)cap, img.ctrl, stream), "duplicate kernel",
+      GSR_STAGE(ST_DUPLICATE, gsr::launch_duplicate(v, P, radii, geom, k0, v0, (uint32_t)cap, img.ctrl, stream), "duplicate kernel",
                 debug, stream);
-      GSR_STAGE(gsr::launch_onesweep(k0, v0, k1, v1, &img.ctrl->num_rendered, (uint32_t)cap, end_bit, bin.sort_ws,
+      GSR_STAGE(ST_SORT, gsr::launch_onesweep(k0, v0, k1, v1, &img.ctrl->num_rendered, (uint32_t)cap, end_bit, bin.sort_ws,
                                      stream),
                 "onesweep radix sort", debug, stream);
-      GSR_STAGE(gsr::launch_tile_ranges(bin.keys_a, &img.ctrl->num_rendered, (uint32_t)cap, img.ranges, stream),
+      GSR_STAGE(ST_RANGES, gsr::launch_tile_ranges(bin.keys_a, &img.ctrl->num_rendered, (uint32_t)cap, img.ranges, stream),
                 "tile ranges kernel", debug, stream);
     }
-    GSR_STAGE(gsr::launch_render_forward(v, img.ranges, bin.vals_a, geom.recs, out_color, out_invdepth, img.final_T,
+    GSR_STAGE(ST_RENDER_FWD, gsr::launch_render_forward(v, img.ranges, bin.vals_a, geom.recs, out_color, out_invdepth, img.final_T,
                                          img.n_contrib, stream),
               "render forward kernel", debug, stream);
     if (R < 0) {
@@ -237,10 +278,10 @@ int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, con
 
   GSR_CUDA(cudaMemsetAsync(grad_acc, 0, (size_t)P * 12 * sizeof(float), stream), "memset(grad accumulators)");
   if (num_rendered > 0)
-    GSR_STAGE(gsr::launch_render_backward(v, img.ranges, point_list, geom.recs, img.final_T, img.n_contrib, dL_dcolor,
+    GSR_STAGE(ST_RENDER_BWD, gsr::launch_render_backward(v, img.ranges, point_list, geom.recs, img.final_T, img.n_contrib, dL_dcolor,
                                           dL_dinvdepth, grad_acc, stream),
               "render backward kernel", debug, stream);
-  GSR_STAGE(gsr::launch_preprocess_backward(v, g, radii, geom, grad_acc, grads->dL_dmeans2D, grads->dL_dcolors,
+  GSR_STAGE(ST_PREPROCESS_BWD, gsr::launch_preprocess_backward(v, g, radii, geom, grad_acc, grads->dL_dmeans2D, grads->dL_dcolors,
                                             grads->dL_dopacity, grads->dL_dmeans3D, grads->dL_dcov3D, grads->dL_dsh,
                                             grads->dL_dscales, grads->dL_drotations, stream),
             "preprocess backward kernel", debug, stream);
@@ -314,5 +355,36 @@ int gsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
   GSR_CUDA(gsr::launch_onesweep(ka, va, kb, vb, d_n, (uint32_t)n, end_bit, ws, stream), "onesweep radix sort");
   return GSR_OK;
 }
+
+int gsr_profile_enable(int on) {
+  std::lock_guard<std::mutex> l(g_prof_mu);
+  g_prof_on = on != 0;
+  return GSR_OK;
+}
+
+void gsr_profile_reset(void) {
+  std::lock_guard<std::mutex> l(g_prof_mu);
+  for (int i = 0; i < ST_COUNT; ++i) { g_prof_ms[i] = 0.0; g_prof_n[i] = 0; }
+}
+
+int gsr_profile_collect(void) {
+  std::lock_guard<std::mutex> l(g_prof_mu);
+  for (const ProfRec& r : g_prof_pending) {
+    GSR_CUDA(cudaEventSynchronize(r.b), "profile: event synchronize");
+    float ms = 0.f;
+    GSR_CUDA(cudaEventElapsedTime(&ms, r.a, r.b), "profile: elapsed time");
+    g_prof_ms[r.stage] += ms;
+    g_prof_n[r.stage] += 1;
+    g_prof_free.push_back(r.a);
+    g_prof_free.push_back(r.b);
+  }
+  g_prof_pending.clear();
+  return GSR_OK;
+}
+
+int gsr_profile_stage_count(void) { return ST_COUNT; }
+const char* gsr_profile_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? kStageNames[i] : ""; }
+double gsr_profile_stage_ms(int i) { return (i >= 0 && i < ST_COUNT) ? g_prof_ms[i] : 0.0; }
+int64_t gsr_profile_stage_calls(int i) { return (i >= 0 && i < ST_COUNT) ? (int64_t)g_prof_n[i] : 0; }
 
 }  // extern "C"

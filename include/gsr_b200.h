@@ -171,6 +171,19 @@ int gsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 int64_t gsr_launch_count(void);
 
+/* Optional per-stage device timing (CUDA events on the launching stream around every stage of
+ * gsr_forward / gsr_backward); used by bench.py for the per-kernel roofline.  Stages:
+ * preprocess, scan, duplicate, sort, tile_ranges, render_forward, render_backward,
+ * preprocess_backward.  gsr_profile_collect() waits for the recorded events and folds them into
+ * the per-stage totals read by gsr_profile_stage_ms / _calls. */
+int gsr_profile_enable(int on);
+void gsr_profile_reset(void);
+int gsr_profile_collect(void);
+int gsr_profile_stage_count(void);
+const char* gsr_profile_stage_name(int i);
+double gsr_profile_stage_ms(int i);
+int64_t gsr_profile_stage_calls(int i);
+
 #ifdef __cplusplus
 }
 #endif
