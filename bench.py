@@ -70,48 +70,109 @@ def make_cameras(W, H, rank, vpr, device):
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    """SM clock + throttle reasons during the timed region (B200_PROFILING.md clocks line).
+
+    Default: one `nvidia-smi -lms 200` child process (the recipe's query list).  start() BLOCKS until the
+    first sample arrives: on a fresh box the child's driver/NVML initialisation takes seconds and, when it
+    overlapped the timed region, stalled this process's launches (measured: 90.7 ms per step instead of
+    24.4 ms).  An in-process NVML polling thread (GSR_BENCH_SAMPLER=nvml) was measured slower still
+    (254-304 vs 328 frames/s: it competes with the launching thread for the GIL), so it is not the default.
+    """
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+               ("sw_power_cap", 0x4))
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index):
+    def __init__(self, gpu_index, mode=None, period=0.25):
         self.gpu = gpu_index
+        self.mode = mode or os.environ.get("GSR_BENCH_SAMPLER", "smi")
+        self.period = period
+        self.samples = []      # (time, sm_mhz, sm_max_mhz, reasons bitmask)
         self.proc = None
-        self.lines = []
+        self._stop = threading.Event()
+        self.t = None
+
+    def _physical_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [x.strip() for x in vis.split(",") if x.strip()]
+            if self.gpu < len(ids) and ids[self.gpu].isdigit():
+                return int(ids[self.gpu])
+        return self.gpu
 
     def start(self):
+        if self.mode == "none":
+            return
+        if self.mode == "nvml":
+            try:
+                import pynvml
+                pynvml.nvmlInit()
+                self.nv = pynvml
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index())
+                self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+                self.t = threading.Thread(target=self._poll_nvml, daemon=True)
+                self.t.start()
+                return
+            except Exception:
+                self.mode = "smi"
         try:
+            ms = int(os.environ.get("GSR_BENCH_SMI_MS", "200"))
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.gpu), "-lms", "100"], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
+                                          "-i", str(self._physical_index()), "-lms", str(ms)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read_smi, daemon=True)
             self.t.start()
+            t_end = time.time() + 30.0
+            while not self.samples and time.time() < t_end and self.proc.poll() is None:
+                time.sleep(0.05)
         except Exception:
             self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append((time.time(), line.strip()))
-
-    def stop(self, t0, t1):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm, mx, reasons = [], [], set()
-        rows = [l for (t, l) in self.lines if t0 <= t <= t1 + 0.2] or [l for (_, l) in self.lines]
-        for l in rows:
-            f = [x.strip() for x in l.split(",")]
+    def _poll_nvml(self):
+        nv = self.nv
+        while not self._stop.is_set():
             try:
-                sm.append(float(f[1])); mx.append(float(f[2]))
+                sm = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    rs = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    rs = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.samples.append((time.time(), sm, self.sm_max, rs))
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def _read_smi(self):
+        for line in self.proc.stdout:
+            f = [x.strip() for x in line.strip().split(",")]
+            try:
+                rs = 0
+                for (name, bit), v in zip(self.REASONS, f[5:9]):
+                    if v.lower().startswith("active"):
+                        rs |= bit
+                self.samples.append((time.time(), float(f[1]), float(f[2]), rs))
             except Exception:
                 continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+
+    def stop(self, t0, t1):
+        if self.mode == "none":
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["sampler disabled"]}
+        self._stop.set()
+        if self.proc is not None:
+            time.sleep(0.1)
+            self.proc.terminate()
+        if self.t is not None:
+            self.t.join(timeout=1.0)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock sampling unavailable"]}
+        rows = [s for s in self.samples if t0 <= s[0] <= t1] or self.samples
+        bits = 0
+        for s in rows:
+            bits |= s[3]
+        return {"sm_mhz": float(np.median([s[1] for s in rows])), "sm_max_mhz": max(s[2] for s in rows),
+                "reasons": sorted(n for n, b in self.REASONS if bits & b), "samples": len(rows),
+                "sampler": self.mode}
 
 
 def peaks():
@@ -253,12 +314,14 @@ def run_ours(args):
     for _ in range(Wm):
         step()
     torch.cuda.synchronize()
-    N.profile_reset(); N.profile_enable(True)
     l0 = N.launch_count()
     ms_total, t0, t1 = timed(step, K, 0)
     launches = N.launch_count() - l0
-    prof = N.profile_read(); N.profile_enable(False)
     clocks = sampler.stop(t0, t1) if rank == 0 else None
+    # per-stage CUDA events (on the launching stream, inside the C library) in a second pass of the same steps
+    N.profile_reset(); N.profile_enable(True)
+    timed(step, K, 0)
+    prof = N.profile_read(); N.profile_enable(False)
     ms_fwd, _, _ = timed(lambda: step(True), K, 2)
 
     frames = K * vpr * world

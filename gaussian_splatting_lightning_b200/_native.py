@@ -40,6 +40,12 @@ class GsrGrads(C.Structure):
                 ("dL_dscales", C.c_void_p), ("dL_drotations", C.c_void_p)]
 
 
+class GsrDensifyStats(C.Structure):
+    _fields_ = [("max_radii2D", C.c_void_p), ("xyz_grad_accum", C.c_void_p), ("xyz_grad_count", C.c_void_p)]
+
+
+GSR_GRADS_ACCUMULATE = 1
+
 _EXPORT_FIELDS = ["depths", "means2D", "cov3D", "conic_opacity", "rgb", "clamped", "tiles_touched",
                   "point_offsets", "keys_unsorted", "vals_unsorted", "keys_sorted", "vals_sorted", "ranges",
                   "final_T", "n_contrib"]
@@ -94,7 +100,7 @@ def lib():
     L.gsr_backward.restype = C.c_int
     L.gsr_backward.argtypes = [C.POINTER(GsrSettings), C.POINTER(GsrGaussians), C.c_void_p, C.c_void_p, C.c_void_p,
                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(GsrGrads),
-                               C.c_void_p]
+                               C.c_int32, C.POINTER(GsrDensifyStats), C.c_void_p]
     L.gsr_mark_visible.restype = C.c_int
     L.gsr_mark_visible.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.gsr_export_state.restype = C.c_int

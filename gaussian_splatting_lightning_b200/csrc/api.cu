@@ -160,7 +160,10 @@ int64_t gsr_launch_count(void) { return (int64_t)g_launches.load(); }
 
 size_t gsr_geom_bytes(int32_t P) { return GeomState::carve(nullptr, P).bytes; }
 size_t gsr_img_bytes(int32_t W, int32_t H) { return ImgState::carve(nullptr, W, H).bytes; }
-size_t gsr_binning_bytes(int64_t capacity, int32_t, int32_t) { return BinningState::carve(nullptr, capacity).bytes; }
+size_t gsr_binning_bytes(int64_t capacity, int32_t W, int32_t H) {
+  const int T = ((W + GSR_TILE - 1) / GSR_TILE) * ((H + GSR_TILE - 1) / GSR_TILE);
+  return BinningState::carve(nullptr, capacity, T).bytes;
+}
 size_t gsr_backward_scratch_bytes(int32_t P) { return gsr_align_up((size_t)(P > 0 ? P : 1) * 12 * sizeof(float)); }
 
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, uint8_t* present, void* stream) {
@@ -215,9 +218,9 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
   }
   for (int attempt = 0; attempt < 2; ++attempt) {
     if (cap >= (1ll << 30)) return fail(GSR_ELIMIT, "more than 2^30 tile instances");
-    char* bin_ptr = (char*)alloc(alloc_user, GSR_BUF_BINNING, BinningState::carve(nullptr, cap).bytes);
+    char* bin_ptr = (char*)alloc(alloc_user, GSR_BUF_BINNING, BinningState::carve(nullptr, cap, num_tiles).bytes);
     if (!bin_ptr) return fail(GSR_EALLOC, "allocator returned NULL");
-    BinningState bin = BinningState::carve(bin_ptr, cap);
+    BinningState bin = BinningState::carve(bin_ptr, cap, num_tiles);
     if (cap > 0 && P > 0) {
       GSR_CUDA(cudaMemsetAsync(bin.sort_ws_base, 0, bin.sort_ws.bytes, stream), "memset(sort workspace)");
       // start in the buffer that makes the last pass land in (keys_a, vals_a)
@@ -225,7 +228,7 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
       uint32_t* v0 = (npass % 2 == 0) ? bin.vals_a : bin.vals_b;
       unsigned long long* k1 = (npass % 2 == 0) ? bin.keys_b : bin.keys_a;
       uint32_t* v1 = (npass % 2 == 0) ? bin.vals_b : bin.vals_a;
-      GSR_STAGE(ST_DUPLICATE, gsr::launch_duplicate(v, P, radii, geom, k0, v0, (uint32_t)cap, img.ctrl, stream), "duplicate kernel",
+      GSR_STAGE(ST_DUPLICATE, gsr::launch_duplicate(v, P, radii, geom, k0, v0, (uint32_t)cap, img.ctrl, bin.header, stream), "duplicate kernel",
                 debug, stream);
       GSR_STAGE(ST_SORT, gsr::launch_onesweep(k0, v0, k1, v1, &img.ctrl->num_rendered, (uint32_t)cap, end_bit, bin.sort_ws,
                                      stream),
@@ -234,7 +237,7 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
                 "tile ranges kernel", debug, stream);
     }
     GSR_STAGE(ST_RENDER_FWD, gsr::launch_render_forward(v, img.ranges, bin.vals_a, geom.recs, out_color, out_invdepth, img.final_T,
-                                         img.n_contrib, stream),
+                                         img.n_contrib, bin.hits, stream),
               "render forward kernel", debug, stream);
     if (R < 0) {
       GSR_CUDA(cudaEventSynchronize(mail->ev), "read num_rendered");
@@ -253,7 +256,8 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
 
 int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, const int32_t* radii,
                  const float* dL_dcolor, const float* dL_dinvdepth, const void* geom_, const void* binning_,
-                 const void* img_, int64_t num_rendered, void* scratch, const GsrGrads* grads, void* stream_) {
+                 const void* img_, int64_t num_rendered, void* scratch, const GsrGrads* grads, int32_t flags,
+                 const GsrDensifyStats* stats, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   GsrView v;
   GsrGaussiansDev g;
@@ -266,24 +270,28 @@ int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, con
   if (P == 0) return GSR_OK;
   if (!radii || !dL_dcolor || !geom_ || !binning_ || !img_ || !scratch)
     return fail(GSR_EINVAL, "backward: NULL buffer");
-  if (!grads->dL_dmeans2D || !grads->dL_dcolors || !grads->dL_dopacity || !grads->dL_dmeans3D || !grads->dL_dcov3D ||
-      !grads->dL_dscales || !grads->dL_drotations || (g.shs && !grads->dL_dsh))
-    return fail(GSR_EINVAL, "backward: NULL gradient output");
-  if (reinterpret_cast<uintptr_t>(grads->dL_drotations) & 15) return fail(GSR_EINVAL, "dL_drotations must be 16-byte aligned");
+  if (grads->dL_drotations && (reinterpret_cast<uintptr_t>(grads->dL_drotations) & 15))
+    return fail(GSR_EINVAL, "dL_drotations must be 16-byte aligned");
+  if (flags & ~GSR_GRADS_ACCUMULATE) return fail(GSR_EINVAL, "backward: unknown flag");
   const bool debug = settings->debug != 0;
   GeomState geom = GeomState::carve((char*)geom_, P);
   ImgState img = ImgState::carve((char*)img_, v.W, v.H);
-  const uint32_t* point_list = (const uint32_t*)binning_;  // vals_a sits at offset 0 (BinningState)
   float* grad_acc = (float*)scratch;
+  gsr::PreBwdOut out;
+  out.dL_dmeans2D = grads->dL_dmeans2D; out.dL_dcolors = grads->dL_dcolors; out.dL_dopacity = grads->dL_dopacity;
+  out.dL_dmeans3D = grads->dL_dmeans3D; out.dL_dcov3D = grads->dL_dcov3D; out.dL_dsh = grads->dL_dsh;
+  out.dL_dscales = grads->dL_dscales; out.dL_drot = grads->dL_drotations;
+  out.accumulate = (flags & GSR_GRADS_ACCUMULATE) ? 1 : 0;
+  out.max_radii2D = stats ? stats->max_radii2D : nullptr;
+  out.xyz_grad_accum = stats ? stats->xyz_grad_accum : nullptr;
+  out.xyz_grad_count = stats ? stats->xyz_grad_count : nullptr;
 
   GSR_CUDA(cudaMemsetAsync(grad_acc, 0, (size_t)P * 12 * sizeof(float), stream), "memset(grad accumulators)");
   if (num_rendered > 0)
-    GSR_STAGE(ST_RENDER_BWD, gsr::launch_render_backward(v, img.ranges, point_list, geom.recs, img.final_T, img.n_contrib, dL_dcolor,
+    GSR_STAGE(ST_RENDER_BWD, gsr::launch_render_backward(v, img.ranges, binning_, geom.recs, img.final_T, img.n_contrib, dL_dcolor,
                                           dL_dinvdepth, grad_acc, stream),
               "render backward kernel", debug, stream);
-  GSR_STAGE(ST_PREPROCESS_BWD, gsr::launch_preprocess_backward(v, g, radii, geom, grad_acc, grads->dL_dmeans2D, grads->dL_dcolors,
-                                            grads->dL_dopacity, grads->dL_dmeans3D, grads->dL_dcov3D, grads->dL_dsh,
-                                            grads->dL_dscales, grads->dL_drotations, stream),
+  GSR_STAGE(ST_PREPROCESS_BWD, gsr::launch_preprocess_backward(v, g, radii, geom, grad_acc, out, stream),
             "preprocess backward kernel", debug, stream);
   return GSR_OK;
 }
@@ -304,14 +312,14 @@ int gsr_export_state(const GsrSettings* settings, int32_t P, const int32_t* radi
                                    out->clamped, out->tiles_touched, out->point_offsets, stream),
            "export kernel");
   if (R > 0 && binning_) {
-    BinningState bin = BinningState::carve((char*)binning_, cap);
+    BinningState bin = BinningState::carve((char*)binning_, cap, v.gx * v.gy);
     if (out->keys_sorted)
       GSR_CUDA(cudaMemcpyAsync(out->keys_sorted, bin.keys_a, R * 8, cudaMemcpyDeviceToDevice, stream), "export keys");
     if (out->vals_sorted)
       GSR_CUDA(cudaMemcpyAsync(out->vals_sorted, bin.vals_a, R * 4, cudaMemcpyDeviceToDevice, stream), "export vals");
     if (out->keys_unsorted && out->vals_unsorted)
       GSR_CUDA(gsr::launch_duplicate(v, P, radii, geom, (unsigned long long*)out->keys_unsorted, out->vals_unsorted,
-                                     (uint32_t)R, img.ctrl, stream),
+                                     (uint32_t)R, img.ctrl, nullptr, stream),
                "export duplicate kernel");
   }
   const size_t HW = (size_t)v.W * v.H;

@@ -108,8 +108,9 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, int gx, int gy, c
                                                         const uint32_t* __restrict__ offsets,
                                                         unsigned long long* __restrict__ keys,
                                                         uint32_t* __restrict__ vals, uint32_t capacity,
-                                                        GsrControl* ctrl) {
+                                                        GsrControl* ctrl, BinningHeader* header) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0 && header) { header->capacity = capacity; header->num_tiles = (uint32_t)(gx * gy); }
   if (i >= P) return;
   const int r = radii[i];
   if (r <= 0) return;
@@ -135,10 +136,10 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, int gx, int gy, c
 
 cudaError_t launch_duplicate(const GsrView& v, int P, const int32_t* radii, const GeomState& geom,
                              unsigned long long* keys, uint32_t* vals, uint32_t capacity, GsrControl* ctrl,
-                             cudaStream_t s) {
+                             BinningHeader* header, cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
   duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, v.gx, v.gy, radii, geom.recs, geom.point_offsets, keys, vals,
-                                                   capacity, ctrl);
+                                                   capacity, ctrl, header);
   count_launch();
   return cudaGetLastError();
 }

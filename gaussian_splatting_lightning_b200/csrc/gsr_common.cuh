@@ -9,7 +9,10 @@
 //                              u32    tiles_touched[P]   4 B
 //                              u32    point_offsets[P]   4 B  inclusive scan of tiles_touched
 //                              u64    scan_state[...]         decoupled look-back words of the scan
-//   binning (per instance, R)  u32 vals_a[cap] (sorted point list ends here), vals_b[cap], u64 keys_a[cap], keys_b[cap]
+//   binning (per instance, R)  128-byte header {u32 capacity, u32 num_tiles} (written on the device; the backward
+//                              locates everything else from it), u32 vals_a[cap] (sorted point list ends here),
+//                              u32 hits[(cap/32 + T + 2) * 8] (per-warp hit words of the forward compositing),
+//                              vals_b[cap], u64 keys_a[cap], keys_b[cap],
 //                              sort control (digit histograms, tile counters, look-back words)
 //   img                        float final_T[HW], u32 n_contrib[HW], uint2 ranges[T], GsrControl
 #pragma once
@@ -136,22 +139,40 @@ struct Workspace {
 }  // namespace gsr_sort
 
 // ---- binning buffer carving ----------------------------------------------------------
+struct BinningHeader {
+  uint32_t capacity;   // instance capacity the buffer was laid out for
+  uint32_t num_tiles;
+  uint32_t pad[30];
+};
+static_assert(sizeof(BinningHeader) == 128, "binning header is one 128-byte line");
+
+// Offsets of the two arrays the backward needs; a pure function of (capacity, num_tiles) so that
+// device code can locate them from the header alone.
+__host__ __device__ inline size_t gsr_bin_align(size_t x) { return (x + 127) / 128 * 128; }
+__host__ __device__ inline size_t gsr_bin_vals_off() { return sizeof(BinningHeader); }
+__host__ __device__ inline size_t gsr_bin_hit_words(size_t cap, size_t num_tiles) { return (cap / 32 + num_tiles + 2) * 8; }
+__host__ __device__ inline size_t gsr_bin_hits_off(size_t cap) { return gsr_bin_vals_off() + gsr_bin_align(cap * 4); }
+
 struct BinningState {
+  BinningHeader* header;
   unsigned long long* keys_a;
   unsigned long long* keys_b;
   uint32_t* vals_a;
   uint32_t* vals_b;
+  uint32_t* hits;
   gsr_sort::Workspace sort_ws;
   char* sort_ws_base;
   size_t bytes;
-  static BinningState carve(char* base, int64_t capacity) {
+  static BinningState carve(char* base, int64_t capacity, int num_tiles) {
     BinningState b;
     size_t off = 0;
     auto take = [&](size_t n) { size_t o = off; off = gsr_align_up(off + n); return base ? base + o : (char*)nullptr; };
     const size_t cap = (size_t)(capacity > 0 ? capacity : 1);
-    // vals_a first: the sorted point list always ends in vals_a (offset 0, independent of the
-    // capacity), which is all the backward needs from this buffer.
+    const size_t T = (size_t)(num_tiles > 0 ? num_tiles : 1);
+    b.header = (BinningHeader*)take(sizeof(BinningHeader));
+    // vals_a right behind the header: the sorted point list always ends in vals_a.
     b.vals_a = (uint32_t*)take(cap * 4);
+    b.hits = (uint32_t*)take(gsr_bin_hit_words(cap, T) * 4);
     b.vals_b = (uint32_t*)take(cap * 4);
     b.keys_a = (unsigned long long*)take(cap * 8);
     b.keys_b = (unsigned long long*)take(cap * 8);
@@ -195,7 +216,7 @@ cudaError_t launch_preprocess(const GsrView& v, const GsrGaussiansDev& g, int32_
 cudaError_t launch_scan(int P, const GeomState& geom, GsrControl* ctrl, cudaStream_t s);
 cudaError_t launch_duplicate(const GsrView& v, int P, const int32_t* radii, const GeomState& geom,
                              unsigned long long* keys, uint32_t* vals, uint32_t capacity, GsrControl* ctrl,
-                             cudaStream_t s);
+                             BinningHeader* header, cudaStream_t s);
 // Sorts min(*d_n, capacity) pairs; the result lands in (keys_a, vals_a) when the pass
 // count is even, else in (keys_b, vals_b).  The workspace must be zeroed.
 cudaError_t launch_onesweep(unsigned long long* keys_a, uint32_t* vals_a, unsigned long long* keys_b,
@@ -205,16 +226,20 @@ cudaError_t launch_tile_ranges(const unsigned long long* keys_sorted, const unsi
                                uint2* ranges, cudaStream_t s);
 cudaError_t launch_render_forward(const GsrView& v, const uint2* ranges, const uint32_t* point_list,
                                   const GsrRec* recs, float* out_color, float* out_invdepth, float* final_T,
-                                  uint32_t* n_contrib, cudaStream_t s);
-cudaError_t launch_render_backward(const GsrView& v, const uint2* ranges, const uint32_t* point_list,
-                                   const GsrRec* recs, const float* final_T, const uint32_t* n_contrib,
-                                   const float* dL_dpix, const float* dL_dinvdepth, float* grad_acc,
-                                   cudaStream_t s);
-// grad_acc: (P,12) floats {dmean2D.x, .y, dconic.A, .B | .C, dopacity, dcolor.r, .g | .b, dinvz, -, -}
+                                  uint32_t* n_contrib, uint32_t* hits, cudaStream_t s);
+// binning: the forward's binning buffer (header + sorted point list + hit words).
+// grad_acc: (P,12) floats, ten raw pixel sums per Gaussian (render_backward.cu) + 2 pad.
+cudaError_t launch_render_backward(const GsrView& v, const uint2* ranges, const void* binning, const GsrRec* recs,
+                                   const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
+                                   const float* dL_dinvdepth, float* grad_acc, cudaStream_t s);
+struct PreBwdOut {
+  float* dL_dmeans2D; float* dL_dcolors; float* dL_dopacity; float* dL_dmeans3D; float* dL_dcov3D; float* dL_dsh;
+  float* dL_dscales; float* dL_drot;
+  int accumulate;
+  float* max_radii2D; float* xyz_grad_accum; float* xyz_grad_count;
+};
 cudaError_t launch_preprocess_backward(const GsrView& v, const GsrGaussiansDev& g, const int32_t* radii,
-                                       const GeomState& geom, const float* grad_acc, float* dL_dmeans2D,
-                                       float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
-                                       float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drot,
+                                       const GeomState& geom, const float* grad_acc, const PreBwdOut& out,
                                        cudaStream_t s);
 cudaError_t launch_export_geom(int P, const int32_t* radii, const GeomState& geom, float* depths, float* means2D,
                                float* cov3D, float* conic_opacity, float* rgb, uint8_t* clamped,

@@ -8,6 +8,16 @@
 // the reference has no backward for any of it, so the derivative is the one stated in
 // oracle/gsr_oracle.cpp (gsro_preprocess_backward) and pinned there by float64 autograd.
 //
+// Input is the accumulator row the compositing backward left per Gaussian: ten RAW sums over the
+// Gaussian's pixels (render_backward.cu); the per-Gaussian factors that turn them into
+// dL/d{mean2D, conic, opacity} (conic entries, W/2, H/2, -1/2) are applied here, once per Gaussian.
+//
+// Fused epilogues: with GSR_GRADS_ACCUMULATE the outputs are += so that the
+// views of one optimiser step sum straight into the flat buffer the all-reduce sends, and the
+// densification statistics of the view (max radius, || dL_dmean2D.xy ||, count --
+// gs_lightning/modules/gaussian_model.py:174-181) are updated from the per-view gradient before
+// it is summed.  Outputs whose pointer is NULL are not produced.
+//
 // HBM-bound: (131 + 12M) B read, (56 + 12M) B written per visible Gaussian.  One thread per
 // Gaussian; the thread's dL_dsh row is written with 128-bit stores.
 #include "gsr_math.cuh"
@@ -29,9 +39,27 @@ struct PreBwdArgs {
   float* dL_dsh;
   float* dL_dscales;
   float* dL_drot;
+  int accumulate;
+  float* max_radii2D;
+  float* xyz_grad_accum;
+  float* xyz_grad_count;
 };
 
-template <int DEG>
+// store or accumulate one float / float4
+template <bool ACC>
+__device__ __forceinline__ void put(float* p, float v) {
+  if (ACC) *p += v; else *p = v;
+}
+template <bool ACC>
+__device__ __forceinline__ void put4(float4* p, float4 v) {
+  if (ACC) {
+    const float4 o = *p;
+    v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+  }
+  *p = v;
+}
+
+template <int DEG, bool ACC>
 __device__ __forceinline__ void sh_backward(const float* __restrict__ sh, float* __restrict__ dsh, int M, bool vec4,
                                             float x, float y, float z, const float* g3, float* ddir) {
   constexpr int N = (DEG + 1) * (DEG + 1);
@@ -51,7 +79,8 @@ __device__ __forceinline__ void sh_backward(const float* __restrict__ sh, float*
       }
     }
   }
-  // row = 3*M floats; entries past 3*N are zero
+  if (!dsh) return;
+  // row = 3*M floats; entries past 3*N are zero (left untouched when accumulating)
   const int total = 3 * M;
   if (vec4) {
     float4* d4 = reinterpret_cast<float4*>(dsh);
@@ -59,28 +88,37 @@ __device__ __forceinline__ void sh_backward(const float* __restrict__ sh, float*
 #pragma unroll
     for (int k = 3 * N; k < NV * 4; ++k) out[k] = 0.f;
 #pragma unroll
-    for (int k = 0; k < NV; ++k) d4[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
-    for (int k = NV; k < total / 4; ++k) d4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int k = 0; k < NV; ++k) put4<ACC>(d4 + k, make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]));
+    if (!ACC)
+      for (int k = NV; k < total / 4; ++k) d4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
   } else {
 #pragma unroll
-    for (int k = 0; k < 3 * N; ++k) dsh[k] = out[k];
-    for (int k = 3 * N; k < total; ++k) dsh[k] = 0.f;
+    for (int k = 0; k < 3 * N; ++k) put<ACC>(dsh + k, out[k]);
+    if (!ACC)
+      for (int k = 3 * N; k < total; ++k) dsh[k] = 0.f;
   }
 }
 
+template <bool ACC>
 __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int P = a.g.P, M = a.g.M;
   if (i >= P) return;
   const bool sh_vec4 = a.dL_dsh && ((M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0);
+  const int radius = a.radii[i];
 
-  if (!(a.radii[i] > 0)) {
-    a.dL_dmeans2D[3 * (size_t)i] = 0.f; a.dL_dmeans2D[3 * (size_t)i + 1] = 0.f; a.dL_dmeans2D[3 * (size_t)i + 2] = 0.f;
-    a.dL_dcolors[3 * (size_t)i] = 0.f; a.dL_dcolors[3 * (size_t)i + 1] = 0.f; a.dL_dcolors[3 * (size_t)i + 2] = 0.f;
-    a.dL_dopacity[i] = 0.f;
-    for (int k = 0; k < 3; ++k) { a.dL_dmeans3D[3 * (size_t)i + k] = 0.f; a.dL_dscales[3 * (size_t)i + k] = 0.f; }
-    for (int k = 0; k < 4; ++k) a.dL_drot[4 * (size_t)i + k] = 0.f;
-    for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * (size_t)i + k] = 0.f;
+  if (!(radius > 0)) {
+    if (ACC) return;  // accumulating: rows of culled Gaussians keep their value
+    if (a.dL_dmeans2D) { a.dL_dmeans2D[3 * (size_t)i] = 0.f; a.dL_dmeans2D[3 * (size_t)i + 1] = 0.f; a.dL_dmeans2D[3 * (size_t)i + 2] = 0.f; }
+    if (a.dL_dcolors) { a.dL_dcolors[3 * (size_t)i] = 0.f; a.dL_dcolors[3 * (size_t)i + 1] = 0.f; a.dL_dcolors[3 * (size_t)i + 2] = 0.f; }
+    if (a.dL_dopacity) a.dL_dopacity[i] = 0.f;
+    for (int k = 0; k < 3; ++k) {
+      if (a.dL_dmeans3D) a.dL_dmeans3D[3 * (size_t)i + k] = 0.f;
+      if (a.dL_dscales) a.dL_dscales[3 * (size_t)i + k] = 0.f;
+    }
+    if (a.dL_drot) reinterpret_cast<float4*>(a.dL_drot)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.dL_dcov3D)
+      for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * (size_t)i + k] = 0.f;
     if (a.dL_dsh) {
       float* dsh = a.dL_dsh + (size_t)i * M * 3;
       if (sh_vec4) for (int k = 0; k < 3 * M / 4; ++k) reinterpret_cast<float4*>(dsh)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -89,8 +127,8 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
     return;
   }
 
-  const float4 g0 = reinterpret_cast<const float4*>(a.grad_acc)[3 * (size_t)i];      // dmx dmy dA dB
-  const float4 g1 = reinterpret_cast<const float4*>(a.grad_acc)[3 * (size_t)i + 1];  // dC dop dr dg
+  const float4 g0 = reinterpret_cast<const float4*>(a.grad_acc)[3 * (size_t)i];      // S0 S1 S2 S3
+  const float4 g1 = reinterpret_cast<const float4*>(a.grad_acc)[3 * (size_t)i + 1];  // S4 S5 dr dg
   const float4 g2 = reinterpret_cast<const float4*>(a.grad_acc)[3 * (size_t)i + 2];  // db dinvz - -
   const float* __restrict__ view = a.v.view;
   const float* __restrict__ proj = a.v.proj;
@@ -104,10 +142,16 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
   build_jacobian(view, px, py, pz, fx, fy, a.v.tanfovx, a.v.tanfovy, jc);
   const Cov2D c0 = project_cov(s6, jc);
   const float ca = c0.a + 0.3f, cc = c0.c + 0.3f, cb = c0.b;
-  const float det = ca * cc - cb * cb;
+  const float det = fmaf(ca, cc, -(cb * cb));  // same chain as the forward (preprocess.cu)
+  const float det_inv = 1.f / det;
+  const float cA = cc * det_inv, cB = -cb * det_inv, cC = ca * det_inv;  // the conic the compositing used
+
+  // raw pixel sums -> dL/d{mean2D, conic, opacity}  (render_backward.cu header)
+  const float dmx = -(cA * g0.x + cB * g0.y) * (0.5f * (float)a.v.W);
+  const float dmy = -(cC * g0.y + cB * g0.x) * (0.5f * (float)a.v.H);
+  const float dA = -0.5f * g0.z, dB = -g0.w, dC = -0.5f * g1.x;
 
   // conic -> dilated cov2D
-  const float dA = g0.z, dB = g0.w, dC = g1.x;
   const float d2inv = 1.f / (det * det + 0.0000001f);
   float da = d2inv * (-cc * cc * dA + cb * cc * dB - cb * cb * dC);
   float dc = d2inv * (-cb * cb * dA + ca * cb * dB - ca * ca * dC);
@@ -128,7 +172,7 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
       db += dL_dratio * (-2.f * cb * inv + r2 * 2.f * cb);
     }
   }
-  a.dL_dopacity[i] = dop;
+  if (a.dL_dopacity) put<ACC>(a.dL_dopacity + i, dop);
 
   // cov2D -> cov3D
   const float* m0 = jc.m0;
@@ -140,8 +184,10 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
   dS[1] = 2.f * m0[0] * m0[1] * da + (m0[0] * m1[1] + m0[1] * m1[0]) * db + 2.f * m1[0] * m1[1] * dc;
   dS[2] = 2.f * m0[0] * m0[2] * da + (m0[0] * m1[2] + m0[2] * m1[0]) * db + 2.f * m1[0] * m1[2] * dc;
   dS[4] = 2.f * m0[1] * m0[2] * da + (m0[1] * m1[2] + m0[2] * m1[1]) * db + 2.f * m1[1] * m1[2] * dc;
+  if (a.dL_dcov3D) {
 #pragma unroll
-  for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * (size_t)i + k] = dS[k];
+    for (int k = 0; k < 6; ++k) put<ACC>(a.dL_dcov3D + 6 * (size_t)i + k, dS[k]);
+  }
 
   // cov2D -> J*R_cw -> view-space point
   const float S[3][3] = {{s6[0], s6[1], s6[2]}, {s6[1], s6[3], s6[4]}, {s6[2], s6[4], s6[5]}};
@@ -172,14 +218,26 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
     const float mul1 = hx * mw * mw, mul2 = hy * mw * mw;
 #pragma unroll
     for (int j = 0; j < 3; ++j)
-      dmean[j] += (proj[4 * j + 0] * mw - proj[4 * j + 3] * mul1) * g0.x +
-                  (proj[4 * j + 1] * mw - proj[4 * j + 3] * mul2) * g0.y;
+      dmean[j] += (proj[4 * j + 0] * mw - proj[4 * j + 3] * mul1) * dmx +
+                  (proj[4 * j + 1] * mw - proj[4 * j + 3] * mul2) * dmy;
   }
-  a.dL_dmeans2D[3 * (size_t)i] = g0.x; a.dL_dmeans2D[3 * (size_t)i + 1] = g0.y; a.dL_dmeans2D[3 * (size_t)i + 2] = 0.f;
-  a.dL_dcolors[3 * (size_t)i] = g1.z; a.dL_dcolors[3 * (size_t)i + 1] = g1.w; a.dL_dcolors[3 * (size_t)i + 2] = g2.x;
+  if (a.dL_dmeans2D) {
+    put<ACC>(a.dL_dmeans2D + 3 * (size_t)i, dmx);
+    put<ACC>(a.dL_dmeans2D + 3 * (size_t)i + 1, dmy);
+    if (!ACC) a.dL_dmeans2D[3 * (size_t)i + 2] = 0.f;
+  }
+  if (a.dL_dcolors) {
+    put<ACC>(a.dL_dcolors + 3 * (size_t)i, g1.z);
+    put<ACC>(a.dL_dcolors + 3 * (size_t)i + 1, g1.w);
+    put<ACC>(a.dL_dcolors + 3 * (size_t)i + 2, g2.x);
+  }
+  // densification statistics of this view (gaussian_model.py:174-181, visible_mask = radii > 0)
+  if (a.max_radii2D) a.max_radii2D[i] = fmaxf(a.max_radii2D[i], (float)radius);
+  if (a.xyz_grad_accum) a.xyz_grad_accum[i] += sqrtf(dmx * dmx + dmy * dmy);
+  if (a.xyz_grad_count) a.xyz_grad_count[i] += 1.f;
 
   // SH
-  if (a.dL_dsh) {
+  if (a.g.shs && (a.dL_dsh || a.dL_dmeans3D)) {
     const float* __restrict__ cam = a.v.campos;
     const float dirx = px - cam[0], diry = py - cam[1], dirz = pz - cam[2];
     const float len = sqrtf(dirx * dirx + diry * diry + dirz * dirz);
@@ -187,24 +245,27 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
     const unsigned cl = a.clamped[i];
     const float g3[3] = {(cl & 1u) ? 0.f : g1.z, (cl & 2u) ? 0.f : g1.w, (cl & 4u) ? 0.f : g2.x};
     const float* sh = a.g.shs + (size_t)i * M * 3;
-    float* dsh = a.dL_dsh + (size_t)i * M * 3;
+    float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)i * M * 3 : nullptr;
     float ddir[3];
     switch (a.v.deg) {
-      case 0: sh_backward<0>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
-      case 1: sh_backward<1>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
-      case 2: sh_backward<2>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
-      default: sh_backward<3>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
+      case 0: sh_backward<0, ACC>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
+      case 1: sh_backward<1, ACC>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
+      case 2: sh_backward<2, ACC>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
+      default: sh_backward<3, ACC>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
     }
     const float ng = x * ddir[0] + y * ddir[1] + z * ddir[2];
     dmean[0] += (ddir[0] - x * ng) / len;
     dmean[1] += (ddir[1] - y * ng) / len;
     dmean[2] += (ddir[2] - z * ng) / len;
   }
+  if (a.dL_dmeans3D) {
 #pragma unroll
-  for (int j = 0; j < 3; ++j) a.dL_dmeans3D[3 * (size_t)i + j] = dmean[j];
+    for (int j = 0; j < 3; ++j) put<ACC>(a.dL_dmeans3D + 3 * (size_t)i + j, dmean[j]);
+  }
 
   // cov3D -> scale, rotation
   if (!a.g.cov3D_precomp) {
+    if (!a.dL_dscales && !a.dL_drot) return;
     const float4 q = reinterpret_cast<const float4*>(a.g.rotations)[i];
     float R[3][3];
     quat_to_R(q, R);
@@ -224,7 +285,7 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
         dsk += dLrk * R[r][k];
         dR[r][k] = dLrk * s[k];
       }
-      a.dL_dscales[3 * (size_t)i + k] = mod * dsk;
+      if (a.dL_dscales) put<ACC>(a.dL_dscales + 3 * (size_t)i + k, mod * dsk);
     }
     const float r = q.x, x = q.y, y = q.z, z = q.w;
     float4 dq;
@@ -235,25 +296,27 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
                   z * dR[2][1] - 2.f * y * dR[2][2]);
     dq.w = 2.f * (-2.f * z * dR[0][0] - r * dR[0][1] + x * dR[0][2] + r * dR[1][0] - 2.f * z * dR[1][1] +
                   y * dR[1][2] + x * dR[2][0] + y * dR[2][1]);
-    reinterpret_cast<float4*>(a.dL_drot)[i] = dq;
-  } else {
-    for (int k = 0; k < 3; ++k) a.dL_dscales[3 * (size_t)i + k] = 0.f;
-    reinterpret_cast<float4*>(a.dL_drot)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.dL_drot) put4<ACC>(reinterpret_cast<float4*>(a.dL_drot) + i, dq);
+  } else if (!ACC) {
+    if (a.dL_dscales)
+      for (int k = 0; k < 3; ++k) a.dL_dscales[3 * (size_t)i + k] = 0.f;
+    if (a.dL_drot) reinterpret_cast<float4*>(a.dL_drot)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
 }
 
 cudaError_t launch_preprocess_backward(const GsrView& v, const GsrGaussiansDev& g, const int32_t* radii,
-                                       const GeomState& geom, const float* grad_acc, float* dL_dmeans2D,
-                                       float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
-                                       float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drot,
+                                       const GeomState& geom, const float* grad_acc, const PreBwdOut& o,
                                        cudaStream_t s) {
   if (g.P <= 0) return cudaSuccess;
   PreBwdArgs a;
   a.v = v; a.g = g; a.radii = radii; a.cov3D = geom.cov3D; a.clamped = geom.clamped; a.grad_acc = grad_acc;
-  a.dL_dmeans2D = dL_dmeans2D; a.dL_dcolors = dL_dcolors; a.dL_dopacity = dL_dopacity;
-  a.dL_dmeans3D = dL_dmeans3D; a.dL_dcov3D = dL_dcov3D; a.dL_dsh = (g.shs ? dL_dsh : nullptr);
-  a.dL_dscales = dL_dscales; a.dL_drot = dL_drot;
-  preprocess_backward_kernel<<<(g.P + 255) / 256, 256, 0, s>>>(a);
+  a.dL_dmeans2D = o.dL_dmeans2D; a.dL_dcolors = o.dL_dcolors; a.dL_dopacity = o.dL_dopacity;
+  a.dL_dmeans3D = o.dL_dmeans3D; a.dL_dcov3D = o.dL_dcov3D; a.dL_dsh = (g.shs ? o.dL_dsh : nullptr);
+  a.dL_dscales = o.dL_dscales; a.dL_drot = o.dL_drot;
+  a.accumulate = o.accumulate;
+  a.max_radii2D = o.max_radii2D; a.xyz_grad_accum = o.xyz_grad_accum; a.xyz_grad_count = o.xyz_grad_count;
+  if (o.accumulate) preprocess_backward_kernel<true><<<(g.P + 255) / 256, 256, 0, s>>>(a);
+  else preprocess_backward_kernel<false><<<(g.P + 255) / 256, 256, 0, s>>>(a);
   count_launch();
   return cudaGetLastError();
 }

@@ -24,48 +24,125 @@ __host__ __device__ __forceinline__ float gsr_clampf(float v, float lo, float hi
   return fminf(fmaxf(v, lo), hi);
 }
 
+// ---- staged record: what the compositing kernels keep in shared memory -----------------
+// The quadratic form is pre-scaled into the log2 domain when a batch is staged, so that the
+// per-(pixel, splat) evaluation is  e = hA dx^2 + hB dx dy + hC dy^2  (= -power * log2 e),
+// G = ex2(-e):  hA = A * (log2e / 2), hB = B * log2e, hC = C * (log2e / 2), tau2 = tau * log2e.
+#define GSR_LOG2E 1.4426950408889634f
+#define GSR_HALF_LOG2E 0.7213475204444817f
+
+#ifdef __CUDACC__
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// Shared-memory accesses through explicit 32-bit shared addresses with an immediate byte offset
+// (keeps the address arithmetic of the hit loop to one IMAD per splat).
+template <int OFF>
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4+%5];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(addr), "n"(OFF));
+  return v;
+}
+template <int OFF>
+__device__ __forceinline__ float2 lds64(uint32_t addr) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0,%1}, [%2+%3];" : "=f"(v.x), "=f"(v.y) : "r"(addr), "n"(OFF));
+  return v;
+}
+template <int OFF>
+__device__ __forceinline__ uint32_t lds32u(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFF));
+  return v;
+}
+// index of the most significant set bit (x != 0)
+__device__ __forceinline__ int msb_index(uint32_t x) {
+  int r;
+  asm("bfind.u32 %0, %1;" : "=r"(r) : "r"(x));
+  return r;
+}
+
+// Staged batch: three planes of 256 float4, plane p of entry j at byte offset p*4096 + j*16.
+//   plane 0 {mean.x, mean.y, hA, hB}   plane 1 {hC, opacity, r, g}   plane 2 {b, 1/z, tau2, bits(gaussian id)}
+#define GSR_PLANE 4096
+
+// e = hA dx^2 + hC dy^2 + hB dx dy with a FIXED rounding sequence: the forward and the backward
+// kernel must agree bit for bit on alpha (the backward replays the forward's accept/reject
+// decisions), so the chain is spelled out with intrinsics the compiler cannot re-associate.
+__device__ __forceinline__ float quad_form(float hA, float hB, float hC, float dx, float dy) {
+  const float t = __fmul_rn(hA, dx);
+  const float u = __fmul_rn(hC, dy);
+  const float v = __fmul_rn(hB, dx);
+  float e = __fmul_rn(t, dx);
+  e = __fmaf_rn(u, dy, e);
+  e = __fmaf_rn(v, dy, e);
+  return e;
+}
+__device__ __forceinline__ float splat_alpha(float opacity, float G) {
+  return fminf(0.99f, __fmul_rn(opacity, G));
+}
+#endif  // __CUDACC__
+
 // Conservative test "can this splat reach alpha >= 1/255 on ANY pixel of the sub-tile?".
 //
-// alpha = min(.99, o * exp(power)) >= 1/255  <=>  power >= -tau, tau = ln(255 o), where
-// power(d) = -q(d), q(d) = 1/2 (A dx^2 + C dy^2) + B dx dy >= 0 for a positive-definite conic.
-// The minimum of the convex q over the rectangle is 0 if the centre lies inside it, else it is
-// attained on an edge that faces the centre; on such an edge q is a 1-D parabola whose clamped
+// alpha = min(.99, o * 2^-e) >= 1/255  <=>  e <= tau2, tau2 = log2(255 o), where
+// e(d) = hA dx^2 + hB dx dy + hC dy^2 >= 0 for a positive-definite conic.
+// The minimum of the convex e over the rectangle is 0 if the centre lies inside it, else it is
+// attained on an edge that faces the centre; on such an edge e is a 1-D parabola whose clamped
 // vertex gives the minimum in closed form.  The splat is rejected only if that minimum exceeds
-// tau by more than a margin that covers the FP32 evaluation error of `power` in the per-pixel
-// loop, of this test, of logf and of the ex2.approx path (bounded by a few 1e-7 * S, S = the
-// sum of the absolute terms of q at the farthest corner).  Returns true when in doubt.
-//   a = {mean.x, mean.y, conic.A, conic.B}, C = conic.C
-__host__ __device__ __forceinline__ bool subtile_may_contribute(const float4 a, const float C, const float tau,
+// tau2 by more than a margin that covers the FP32 evaluation error of e in the per-pixel
+// loop, of this test, of logf and of ex2.approx (bounded by a few 1e-7 * S, S = the sum of the
+// absolute terms of e at the farthest corner).  Returns true when in doubt.
+//   a = {mean.x, mean.y, hA, hB}
+__host__ __device__ __forceinline__ bool subtile_may_contribute(const float4 a, const float hC, const float tau2,
                                                                 const SubTile st) {
-  const float mx = a.x, my = a.y, A = a.z, B = a.w;
-  if (!(tau >= -1e-4f)) return false;  // opacity < 1/255: alpha can never reach the floor
-  if (!(A > 0.f && C > 0.f && A * C - B * B > 0.f)) return true;  // not provably convex: keep
+  const float mx = a.x, my = a.y, hA = a.z, hB = a.w;
+  if (!(tau2 >= -1.5e-4f)) return false;  // opacity < 1/255: alpha can never reach the floor
+  if (!(hA > 0.f && hC > 0.f && 4.f * hA * hC - hB * hB > 0.f)) return true;  // not provably convex: keep
   const float dxn = mx - gsr_clampf(mx, st.x0, st.x1);  // dx at the nearest column (0 if inside)
   const float dyn = my - gsr_clampf(my, st.y0, st.y1);
   if (dxn == 0.f && dyn == 0.f) return true;
   const float dx_lo = mx - st.x1, dx_hi = mx - st.x0;  // range of dx over the rectangle
   const float dy_lo = my - st.y1, dy_hi = my - st.y0;
-  float minq = 3.0e38f;
-  if (dxn != 0.f) {  // facing vertical edge: dx fixed, vertex dy* = -B dx / C
+  float mine = 3.0e38f;
+  if (dxn != 0.f) {  // facing vertical edge: dx fixed, vertex dy* = -hB dx / (2 hC)
 #ifdef __CUDA_ARCH__
-    const float dys = gsr_clampf(__fdividef(-B * dxn, C), dy_lo, dy_hi);
+    const float dys = gsr_clampf(__fdividef(-0.5f * hB * dxn, hC), dy_lo, dy_hi);
 #else
-    const float dys = gsr_clampf(-B * dxn / C, dy_lo, dy_hi);
+    const float dys = gsr_clampf(-0.5f * hB * dxn / hC, dy_lo, dy_hi);
 #endif
-    minq = 0.5f * (A * dxn * dxn + C * dys * dys) + B * dxn * dys;
+    mine = hA * dxn * dxn + hC * dys * dys + hB * dxn * dys;
   }
-  if (dyn != 0.f) {  // facing horizontal edge: dy fixed, vertex dx* = -B dy / A
+  if (dyn != 0.f) {  // facing horizontal edge: dy fixed, vertex dx* = -hB dy / (2 hA)
 #ifdef __CUDA_ARCH__
-    const float dxs = gsr_clampf(__fdividef(-B * dyn, A), dx_lo, dx_hi);
+    const float dxs = gsr_clampf(__fdividef(-0.5f * hB * dyn, hA), dx_lo, dx_hi);
 #else
-    const float dxs = gsr_clampf(-B * dyn / A, dx_lo, dx_hi);
+    const float dxs = gsr_clampf(-0.5f * hB * dyn / hA, dx_lo, dx_hi);
 #endif
-    minq = fminf(minq, 0.5f * (A * dxs * dxs + C * dyn * dyn) + B * dxs * dyn);
+    mine = fminf(mine, hA * dxs * dxs + hC * dyn * dyn + hB * dxs * dyn);
   }
   const float DX = fmaxf(fabsf(dx_lo), fabsf(dx_hi));
   const float DY = fmaxf(fabsf(dy_lo), fabsf(dy_hi));
-  const float S = 0.5f * (A * DX * DX + C * DY * DY) + fabsf(B) * DX * DY;
-  return minq <= tau + (4e-6f * S + 2e-5f);
+  const float S = hA * DX * DX + hC * DY * DY + fabsf(hB) * DX * DY;
+  return mine <= tau2 + (4e-6f * S + 3e-5f);
+}
+
+// ---- per-(warp, 32-splat chunk) hit words -------------------------------------------------
+// The forward records, for every chunk of 32 list entries a warp visited, which of them
+// contributed to at least one of the warp's 32 pixels.  The backward replays exactly those.
+// Tile t's chunk k lives in slot (range.x >> 5) + t + k (unique and monotonic over tiles);
+// a slot holds 8 words, one per warp.
+__host__ __device__ __forceinline__ size_t hit_slot(uint32_t range_x, uint32_t tile, uint32_t chunk) {
+  return (size_t)(range_x >> 5) + tile + chunk;
 }
 
 }  // namespace gsr

@@ -13,13 +13,19 @@
 //   * one CTA per tile, 8 warps; warp w owns the 8x4 pixel sub-tile (w&1, w>>1) so that a warp's
 //     pixels are spatially compact;
 //   * the tile's list is consumed in batches of 256: each thread gathers one packed 48-byte
-//     GsrRec (three 128-bit loads, L2-resident at 1M Gaussians) into shared memory;
+//     GsrRec (three 128-bit loads, L2-resident at 1M Gaussians) and stages it in shared memory
+//     with the quadratic form pre-scaled into the log2 domain (render_common.cuh), so that the
+//     inner loop is 6 FP32 ops + one MUFU.EX2 per (pixel, splat);
 //   * sub-tile culling: before touching a batch, each lane tests ONE splat of the batch
 //     against the warp's 8x4 pixel rectangle (exact minimum of the quadratic form over the
-//     rectangle vs. tau = ln(255 * opacity), conservative margin) and a ballot turns the 32
+//     rectangle vs. tau2 = log2(255 * opacity), conservative margin) and a ballot turns the 32
 //     answers into a bit mask; the warp then iterates only over set bits.  A splat rejected
 //     here has alpha < 1/255 on every pixel of the sub-tile, so results are identical to the
 //     unculled loop while most (pixel, splat) pairs are never evaluated;
+//   * the hit loop is branch-free per lane (predicated updates);
+//   * for every chunk of 32 list entries the warp records which entries contributed to at
+//     least one of its pixels (one 32-bit "hit word" per warp and chunk, 1 byte per list entry
+//     in total): the backward kernel replays exactly those and needs no culling test;
 //   * warp ballots retire a warp as soon as its 32 pixels are saturated; the CTA leaves the
 //     list when __syncthreads_and says every pixel is done.
 #include "gsr_common.cuh"
@@ -33,10 +39,9 @@ __global__ void __launch_bounds__(256) render_forward_kernel(const GsrView v, co
                                                              float* __restrict__ out_color,
                                                              float* __restrict__ out_invdepth,
                                                              float* __restrict__ final_T,
-                                                             uint32_t* __restrict__ n_contrib) {
-  __shared__ float4 sA[256];
-  __shared__ float4 sB[256];
-  __shared__ float4 sC[256];
+                                                             uint32_t* __restrict__ n_contrib,
+                                                             uint32_t* __restrict__ hits) {
+  __shared__ float4 sRec[3][256];  // staged batch, planes as described in render_common.cuh
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
@@ -47,9 +52,11 @@ __global__ void __launch_bounds__(256) render_forward_kernel(const GsrView v, co
   const bool inside = pxi < v.W && pyi < v.H;
   const float pxf = (float)pxi, pyf = (float)pyi;
   const SubTile st = make_subtile(sx0, sy0, v.W, v.H);
+  const uint32_t aRec = (uint32_t)__cvta_generic_to_shared(sRec);
 
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
+  uint32_t* __restrict__ hit_row = hits + hit_slot(range.x, (uint32_t)tile, 0) * 8 + warp;
 
   float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
   uint32_t last = 0;
@@ -61,7 +68,9 @@ __global__ void __launch_bounds__(256) render_forward_kernel(const GsrView v, co
     if (tid < cnt) {
       const uint32_t g = point_list[range.x + base + tid];
       const GsrRec* r = recs + g;
-      sA[tid] = r->a; sB[tid] = r->b; sC[tid] = r->c;
+      float4 a = r->a, b = r->b, c = r->c;
+      a.z *= GSR_HALF_LOG2E; a.w *= GSR_LOG2E; b.x *= GSR_HALF_LOG2E; c.z *= GSR_LOG2E;
+      sRec[0][tid] = a; sRec[1][tid] = b; sRec[2][tid] = c;
     }
     __syncthreads();
     if (__all_sync(0xffffffffu, done)) continue;  // whole warp saturated: only keep the barriers
@@ -69,29 +78,33 @@ __global__ void __launch_bounds__(256) render_forward_kernel(const GsrView v, co
     for (int c0 = 0; c0 < cnt; c0 += 32) {
       // one splat per lane against the warp's sub-tile
       bool hit = false;
-      if (c0 + lane < cnt) hit = subtile_may_contribute(sA[c0 + lane], sB[c0 + lane].x, sC[c0 + lane].z, st);
+      if (c0 + lane < cnt) hit = subtile_may_contribute(sRec[0][c0 + lane], sRec[1][c0 + lane].x, sRec[2][c0 + lane].z, st);
       uint32_t mask = __ballot_sync(0xffffffffu, hit);
+      uint32_t used = 0;
       while (mask) {
-        const int j = c0 + __ffs(mask) - 1;
+        const int bit = __ffs(mask) - 1;
         mask &= mask - 1;
-        const float4 a = sA[j];
-        const float4 b = sB[j];
+        const uint32_t addr = aRec + (uint32_t)(c0 + bit) * 16u;
+        const float4 a = lds128<0>(addr);
+        const float4 b = lds128<GSR_PLANE>(addr);
+        const float2 c = lds64<2 * GSR_PLANE>(addr);
         const float dx = a.x - pxf, dy = a.y - pyf;
-        const float power = -0.5f * (a.z * dx * dx + b.x * dy * dy) - a.w * dx * dy;
-        if (power > 0.f) continue;
-        const float alpha = fminf(0.99f, b.y * __expf(power));
-        if (alpha < 1.f / 255.f || done) continue;
-        const float test_T = T * (1.f - alpha);
-        if (test_T < 0.0001f) { done = true; continue; }
-        const float4 c = sC[j];
-        const float w = alpha * T;
+        const float e = quad_form(a.z, a.w, b.x, dx, dy);
+        const float alpha = splat_alpha(b.y, ex2_approx(-e));
+        const float test_T = __fmaf_rn(-T, alpha, T);
+        bool ok = !(e < 0.f) && (alpha >= 1.f / 255.f) && !done;
+        done = done || (ok && test_T < 0.0001f);
+        ok = ok && !(test_T < 0.0001f);
+        const float w = ok ? alpha * T : 0.f;
         C0 = fmaf(b.z, w, C0);
         C1 = fmaf(b.w, w, C1);
         C2 = fmaf(c.x, w, C2);
         D = fmaf(c.y, w, D);
-        T = test_T;
-        last = (uint32_t)(base + j + 1);
+        T = ok ? test_T : T;
+        last = ok ? (uint32_t)(base + c0 + bit + 1) : last;
+        if (__any_sync(0xffffffffu, ok)) used |= 1u << bit;
       }
+      if (lane == 0) hit_row[(size_t)((base + c0) >> 5) * 8] = used;
       if (__all_sync(0xffffffffu, done)) break;
     }
   }
@@ -111,11 +124,11 @@ __global__ void __launch_bounds__(256) render_forward_kernel(const GsrView v, co
 
 cudaError_t launch_render_forward(const GsrView& v, const uint2* ranges, const uint32_t* point_list,
                                   const GsrRec* recs, float* out_color, float* out_invdepth, float* final_T,
-                                  uint32_t* n_contrib, cudaStream_t s) {
+                                  uint32_t* n_contrib, uint32_t* hits, cudaStream_t s) {
   const int tiles = v.gx * v.gy;
   if (tiles <= 0) return cudaSuccess;
   render_forward_kernel<<<tiles, 256, 0, s>>>(v, ranges, point_list, recs, out_color, out_invdepth, final_T,
-                                              n_contrib);
+                                              n_contrib, hits);
   count_launch();
   return cudaGetLastError();
 }

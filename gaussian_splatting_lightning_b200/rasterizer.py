@@ -11,6 +11,7 @@ The compute is libgsr_b200.so (hand-written sm_100a CUDA) reached through _nativ
 from __future__ import annotations
 
 import ctypes as C
+import math
 import os
 from typing import NamedTuple, Optional
 
@@ -106,17 +107,38 @@ def forward_raw(rs: GaussianRasterizationSettings, means3D, sh, colors_precomp, 
             alloc.buffers[N.GSR_BUF_IMG], invdepth, int(cap.value))
 
 
+_GRAD_NAMES = ("dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales",
+               "dL_drotations")
+
+
 def backward_raw(rs: GaussianRasterizationSettings, means3D, radii, sh, colors_precomp, opacities, scales,
                  rotations, cov3Ds_precomp, dL_dcolor, dL_dinvdepth, geomBuffer, binningBuffer, imgBuffer,
-                 num_rendered: int):
+                 num_rendered: int, want=None, accumulate_into=None, stats=None):
     """_C.rasterize_gaussians_backward: returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D,
-    dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)."""
+    dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
+
+    Extensions of the C-ABI (include/gsr_b200.h), all optional:
+      want            names of the gradients to produce (others come back as None, not computed);
+      accumulate_into dict name -> tensor: those gradients are ADDED into the given tensors
+                      (GSR_GRADS_ACCUMULATE: several views into one flat gradient buffer);
+      stats           dict with any of max_radii2D / xyz_grad_accum / xyz_grad_count, (P,) float32:
+                      the view's densification statistics (gaussian_model.py:174-181), fused.
+    """
     fr = _Frame(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
     dev, P, M = fr.device, fr.P, fr.M
+    shapes = dict(dL_dmeans2D=(P, 3), dL_dcolors=(P, 3), dL_dopacity=(P, 1), dL_dmeans3D=(P, 3), dL_dcov3D=(P, 6),
+                  dL_dsh=(P, M, 3), dL_dscales=(P, 3), dL_drotations=(P, 4))
     with torch.cuda.device(dev):
-        e = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
-        g = dict(dL_dmeans2D=e(P, 3), dL_dcolors=e(P, 3), dL_dopacity=e(P, 1), dL_dmeans3D=e(P, 3),
-                 dL_dcov3D=e(P, 6), dL_dsh=e(P, M, 3), dL_dscales=e(P, 3), dL_drotations=e(P, 4))
+        if accumulate_into is not None:
+            g = {n: accumulate_into.get(n) for n in _GRAD_NAMES}
+            for n, t in g.items():
+                if t is not None and not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()
+                                          and t.numel() == math.prod(shapes[n])):
+                    raise RuntimeError(f"accumulate_into[{n!r}] must be a contiguous float32 CUDA tensor of shape {shapes[n]}")
+        else:
+            names = _GRAD_NAMES if want is None else tuple(want)
+            g = {n: (torch.empty(shapes[n], dtype=torch.float32, device=dev) if n in names else None)
+                 for n in _GRAD_NAMES}
         if P == 0:
             return tuple(g.values())
         dL_dcolor = N.f32c(dL_dcolor, dev)
@@ -125,9 +147,18 @@ def backward_raw(rs: GaussianRasterizationSettings, means3D, radii, sh, colors_p
         dL_dinvdepth = N.f32c(dL_dinvdepth, dev)
         scratch = torch.empty(N.lib().gsr_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
         grads = N.GsrGrads(*[N.ptr(t) for t in g.values()])
+        st = None
+        if stats:
+            for k, t in stats.items():
+                if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == P):
+                    raise RuntimeError(f"stats[{k!r}] must be a contiguous float32 CUDA tensor of {P} elements")
+            st = N.GsrDensifyStats(N.ptr(stats.get("max_radii2D")), N.ptr(stats.get("xyz_grad_accum")),
+                                   N.ptr(stats.get("xyz_grad_count")))
         rc = N.lib().gsr_backward(C.byref(fr.settings), C.byref(fr.gaussians), N.ptr(radii), N.ptr(dL_dcolor),
                                   N.ptr(dL_dinvdepth), N.ptr(geomBuffer), N.ptr(binningBuffer), N.ptr(imgBuffer),
-                                  int(num_rendered), N.ptr(scratch), C.byref(grads), N.stream_ptr(dev))
+                                  int(num_rendered), N.ptr(scratch), C.byref(grads),
+                                  N.GSR_GRADS_ACCUMULATE if accumulate_into is not None else 0,
+                                  C.byref(st) if st is not None else None, N.stream_ptr(dev))
         N.check(rc, "gsr_backward")
     return tuple(g.values())
 
@@ -169,11 +200,17 @@ class _RasterizeGaussians(torch.autograd.Function):
     def backward(ctx, grad_out_color, _grad_radii, grad_out_depth):
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities, geomBuffer,
          binningBuffer, imgBuffer) = ctx.saved_tensors
+        has_sh, has_col, has_scale, has_rot, has_cov = ctx.has
+        # inputs in forward order: means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp
+        need = ctx.needs_input_grad
+        want = [n for n, ok in (("dL_dmeans3D", need[0]), ("dL_dmeans2D", need[1]), ("dL_dsh", has_sh and need[2]),
+                                ("dL_dcolors", has_col and need[3]), ("dL_dopacity", need[4]),
+                                ("dL_dscales", has_scale and need[5]), ("dL_drotations", has_rot and need[6]),
+                                ("dL_dcov3D", has_cov and need[7])) if ok]
         (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
          dL_drotations) = backward_raw(ctx.raster_settings, means3D, radii, sh, colors_precomp, opacities, scales,
                                        rotations, cov3Ds_precomp, grad_out_color, grad_out_depth, geomBuffer,
-                                       binningBuffer, imgBuffer, ctx.num_rendered)
-        has_sh, has_col, has_scale, has_rot, has_cov = ctx.has
+                                       binningBuffer, imgBuffer, ctx.num_rendered, want=want)
         return (dL_dmeans3D, dL_dmeans2D, dL_dsh if has_sh else None, dL_dcolors if has_col else None, dL_dopacity,
                 dL_dscales if has_scale else None, dL_drotations if has_rot else None,
                 dL_dcov3D if has_cov else None, None)

@@ -84,7 +84,9 @@ typedef struct GsrGaussians {
 } GsrGaussians;
 
 /* Gradients produced by gsr_backward; same order and shapes as the tuple
- * _C.rasterize_gaussians_backward returns.  All device, all fully written. */
+ * _C.rasterize_gaussians_backward returns.  All device.  ANY pointer may be NULL: that
+ * gradient is then not wanted and is neither computed nor written (a training step that
+ * passes shs + scales/rotations never reads dL_dcolors / dL_dcov3D). */
 typedef struct GsrGrads {
   float* dL_dmeans2D;   /* (P,3)  z = 0; consumer takes [:, :2] (gaussian_model.py:180) */
   float* dL_dcolors;    /* (P,3)                                                         */
@@ -95,6 +97,20 @@ typedef struct GsrGrads {
   float* dL_dscales;    /* (P,3)                                                         */
   float* dL_drotations; /* (P,4)                                                         */
 } GsrGrads;
+
+/* gsr_backward flags */
+#define GSR_GRADS_ACCUMULATE 1 /* outputs are += (several views into one gradient buffer, the layout the
+                                  view-parallel all-reduce sends); rows of culled Gaussians are not touched */
+
+/* Densification statistics of one view, fused into the backward so that the per-view norm is
+ * taken BEFORE gradients of several views are summed.  Mirrors
+ * GaussianModel.update_max_radii2D / update_xyz_gradient (gs_lightning/modules/gaussian_model.py:174-181)
+ * with visible_mask = radii > 0 (gs_lightning_module.py:192-195).  Any pointer may be NULL. */
+typedef struct GsrDensifyStats {
+  float* max_radii2D;     /* (P)  = max(max_radii2D, radii)              where radii > 0 */
+  float* xyz_grad_accum;  /* (P) += || dL_dmeans2D[:, :2] ||_2           where radii > 0 */
+  float* xyz_grad_count;  /* (P) += 1                                     where radii > 0 */
+} GsrDensifyStats;
 
 /* Canonical-layout export of the opaque scratch buffers for the
  * bit-exact parity checks.  Any pointer may be NULL (skipped). All device. */
@@ -141,11 +157,12 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
                 int64_t binning_hint, int64_t* num_rendered, int64_t* binning_capacity, void* stream);
 
 /* Backward from the three scratch buffers the forward left behind (read-only here).
- * dL_dinvdepth may be NULL.  `scratch` is gsr_backward_scratch_bytes(P) of device memory. */
+ * dL_dinvdepth may be NULL.  `scratch` is gsr_backward_scratch_bytes(P) of device memory.
+ * flags: 0 or GSR_GRADS_ACCUMULATE.  stats: NULL or the densification statistics to update. */
 int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, const int32_t* radii,
                  const float* dL_dcolor, const float* dL_dinvdepth, const void* geom,
                  const void* binning, const void* img, int64_t num_rendered, void* scratch,
-                 const GsrGrads* grads, void* stream);
+                 const GsrGrads* grads, int32_t flags, const GsrDensifyStats* stats, void* stream);
 
 /* present[i] = ([p_i,1] @ viewmatrix).z > 0.2   (camera_tools.py:5-8). */
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, uint8_t* present,
