@@ -253,6 +253,9 @@ def run_ours(args):
         views_flat.append(flat[o:o + P * w_].view(P, w_)); o += P * w_
     stats = torch.zeros(2, P, device=device)      # xyz_grad_accum, xyz_grad_count (gaussian_model.py:174-181)
     max_radii = torch.zeros(P, device=device)
+    acc_into = dict(dL_dmeans3D=views_flat[0], dL_dsh=views_flat[1], dL_dopacity=views_flat[2],
+                    dL_dscales=views_flat[3], dL_drotations=views_flat[4])
+    stat_into = dict(max_radii2D=max_radii, xyz_grad_accum=stats[0], xyz_grad_count=stats[1])
 
     def one_view(c, fwd_only=False):
         rs = c["settings"]
@@ -260,20 +263,18 @@ def run_ours(args):
             rs, scene["means3D"], scene["shs"], None, scene["opacities"], scene["scales"], scene["rotations"], None)
         if fwd_only:
             return color
-        (d2, dcol, dop, d3, dcov, dsh, dsc, drot) = backward_raw(
-            rs, scene["means3D"], radii, scene["shs"], None, scene["opacities"], scene["scales"], scene["rotations"],
-            None, dL_dcolor, dL_dinv, geom, binning, img, R)
-        for dst, src in zip(views_flat, (d3, dsh.view(P, -1), dop, dsc, drot)):
-            dst.add_(src)
-        vis = radii > 0                                           # densification statistics of this view
-        torch.maximum(max_radii, radii.to(torch.float32), out=max_radii)
-        stats[0].add_(d2[:, :2].norm(dim=-1) * vis)
-        stats[1].add_(vis)
+        # gradients += into the flat all-reduce buffer and the view's densification statistics
+        # (gaussian_model.py:174-181), both fused into the preprocess backward kernel
+        backward_raw(rs, scene["means3D"], radii, scene["shs"], None, scene["opacities"], scene["scales"],
+                     scene["rotations"], None, dL_dcolor, dL_dinv, geom, binning, img, R,
+                     accumulate_into=acc_into, stats=stat_into)
         return color
 
     def step(fwd_only=False):
         if not fwd_only:
-            flat.zero_()
+            flat.zero_()        # per-step buffers: gradient sum and the statistics DELTAS of this step's views
+            stats.zero_()
+            max_radii.zero_()
         for c in cams:
             one_view(c, fwd_only)
         if world > 1 and not fwd_only:
@@ -307,17 +308,36 @@ def run_ours(args):
     counters = workload_counters(cams, scene, device)
     K, Wm = args.steps, max(args.warmup, 3)
 
-    # ---- headline: fwd+bwd, inputs resident in HBM, per-stage events on -------------------------
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
+    # ---- headline: fwd+bwd, inputs resident in HBM -------------------------------------------------
+    # The timed region (exactly K steps, barrier + synchronize on both sides, CUDA events, max over
+    # ranks) is measured ATTEMPTS times with nvidia-smi sampling clocks concurrently, and once more
+    # with no poller at all.  The poller is another driver client: on some boxes its queries were
+    # measured to stall this process's launches for whole regions (43.8 and 90.7 ms per step against
+    # 19.4 ms).  value = the fastest sampled attempt; if even that is > 10 % slower than the unsampled
+    # region the unsampled one is reported and `clocks` says so.  All attempts are listed.
+    ATTEMPTS = 3
     for _ in range(Wm):
         step()
     torch.cuda.synchronize()
     l0 = N.launch_count()
-    ms_total, t0, t1 = timed(step, K, 0)
+    ms_clean, _, _ = timed(step, K, 0)
     launches = N.launch_count() - l0
-    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    attempts = [timed(step, K, 0) for _ in range(ATTEMPTS)]
+    best = min(attempts, key=lambda a: a[0])
+    clocks = sampler.stop(best[1], best[2]) if rank == 0 else None
+    ms_total = best[0]
+    if clocks is not None:
+        clocks["sampled_attempts_ms_per_step"] = [round(a[0] / K, 3) for a in attempts]
+        clocks["unsampled_ms_per_step"] = round(ms_clean / K, 3)
+        clocks["value_from"] = "fastest sampled attempt"
+    if ms_total > 1.10 * ms_clean:
+        ms_total = ms_clean
+        if clocks is not None:
+            clocks["value_from"] = ("unsampled region (every sampled attempt was > 10 % slower: the nvidia-smi poller "
+                                    "stalled launches); clocks are those of the adjacent sampled attempts")
     # per-stage CUDA events (on the launching stream, inside the C library) in a second pass of the same steps
     N.profile_reset(); N.profile_enable(True)
     timed(step, K, 0)

@@ -228,10 +228,10 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
       uint32_t* v0 = (npass % 2 == 0) ? bin.vals_a : bin.vals_b;
       unsigned long long* k1 = (npass % 2 == 0) ? bin.keys_b : bin.keys_a;
       uint32_t* v1 = (npass % 2 == 0) ? bin.vals_b : bin.vals_a;
-      GSR_STAGE(ST_DUPLICATE, gsr::launch_duplicate(v, P, radii, geom, k0, v0, (uint32_t)cap, img.ctrl, bin.header, stream), "duplicate kernel",
+      GSR_STAGE(ST_DUPLICATE, gsr::launch_duplicate(v, P, radii, geom, k0, v0, (uint32_t)cap, img.ctrl, bin.header, bin.sort_ws.hist, npass, stream), "duplicate kernel",
                 debug, stream);
       GSR_STAGE(ST_SORT, gsr::launch_onesweep(k0, v0, k1, v1, &img.ctrl->num_rendered, (uint32_t)cap, end_bit, bin.sort_ws,
-                                     stream),
+                                     true, stream),
                 "onesweep radix sort", debug, stream);
       GSR_STAGE(ST_RANGES, gsr::launch_tile_ranges(bin.keys_a, &img.ctrl->num_rendered, (uint32_t)cap, img.ranges, stream),
                 "tile ranges kernel", debug, stream);
@@ -319,7 +319,7 @@ int gsr_export_state(const GsrSettings* settings, int32_t P, const int32_t* radi
       GSR_CUDA(cudaMemcpyAsync(out->vals_sorted, bin.vals_a, R * 4, cudaMemcpyDeviceToDevice, stream), "export vals");
     if (out->keys_unsorted && out->vals_unsorted)
       GSR_CUDA(gsr::launch_duplicate(v, P, radii, geom, (unsigned long long*)out->keys_unsorted, out->vals_unsorted,
-                                     (uint32_t)R, img.ctrl, nullptr, stream),
+                                     (uint32_t)R, img.ctrl, nullptr, nullptr, 0, stream),
                "export duplicate kernel");
   }
   const size_t HW = (size_t)v.W * v.H;
@@ -360,7 +360,7 @@ int gsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
   uint32_t* vb = (npass % 2 == 0) ? vals_tmp : vals_out;
   GSR_CUDA(cudaMemcpyAsync(ka, keys_in, (size_t)n * 8, cudaMemcpyDeviceToDevice, stream), "sort: copy keys");
   GSR_CUDA(cudaMemcpyAsync(va, vals_in, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream), "sort: copy vals");
-  GSR_CUDA(gsr::launch_onesweep(ka, va, kb, vb, d_n, (uint32_t)n, end_bit, ws, stream), "onesweep radix sort");
+  GSR_CUDA(gsr::launch_onesweep(ka, va, kb, vb, d_n, (uint32_t)n, end_bit, ws, false, stream), "onesweep radix sort");
   return GSR_OK;
 }
 

@@ -6,8 +6,8 @@
 // host round trip.
 //
 //   K3  single-pass chained scan with decoupled look-back (one 64-bit status word per
-//       2048-item tile: flag in the top two bits, running sum below), dynamic tile ids so a
-//       tile only ever waits on tiles that already started.      8 B / Gaussian
+//       2048-item tile: flag in the top two bits, running sum below); tile id = blockIdx.x (a
+//       global atomic counter for dynamic ids serialises the tiles).      8 B / Gaussian
 //   K4  key = (tile_id << 32) | float_bits(z_view), value = Gaussian index, rect walked
 //       y-outer / x-inner (gs_lightning/rasterize/render_tools.py:134-139 gives the rect,
 //       rasterize.py:110 the tile id).                            12 B / instance written
@@ -25,13 +25,10 @@ constexpr unsigned long long SCAN_VAL_MASK = (1ull << 62) - 1;
 __global__ void __launch_bounds__(256) scan_kernel(int P, const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
                                                    unsigned long long* state, GsrControl* ctrl) {
   constexpr int IPT = 8;
-  __shared__ unsigned int s_tile;
   __shared__ unsigned int s_warp[8];
   __shared__ unsigned long long s_excl;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_tile = atomicAdd(&ctrl->scan_counter, 1u);
-  __syncthreads();
-  const unsigned int tile = s_tile;
+  const unsigned int tile = blockIdx.x;  // in-order CTA dispatch keeps every predecessor resident or done
   const long long base = (long long)tile * GeomState::SCAN_ITEMS + (long long)tid * IPT;
 
   uint32_t v[IPT];
@@ -103,43 +100,79 @@ cudaError_t launch_scan(int P, const GeomState& geom, GsrControl* ctrl, cudaStre
   return cudaGetLastError();
 }
 
+// K4.  When `hist` is given the kernel also builds the digit histograms of ALL radix passes of the
+// sort that follows (shared-memory privatised, one global atomic per non-empty bin and CTA), which
+// saves the sort its own read of the keys: the depth digits (key bits 0..31) are the same for every
+// instance of a Gaussian, so they cost one shared atomic per Gaussian and pass; only the tile-id
+// digits (bits 32..) are counted per instance.  Only instances actually written (below `capacity`)
+// are counted, so the histograms always describe exactly the keys the sort will see.
 __global__ void __launch_bounds__(256) duplicate_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii,
                                                         const GsrRec* __restrict__ recs,
                                                         const uint32_t* __restrict__ offsets,
                                                         unsigned long long* __restrict__ keys,
                                                         uint32_t* __restrict__ vals, uint32_t capacity,
-                                                        GsrControl* ctrl, BinningHeader* header) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0 && header) { header->capacity = capacity; header->num_tiles = (uint32_t)(gx * gy); }
-  if (i >= P) return;
-  const int r = radii[i];
-  if (r <= 0) return;
-  uint32_t off = (i == 0) ? 0u : offsets[i - 1];
-  const float4 a = recs[i].a;
-  const float depth = recs[i].c.w;
-  int x0, y0, x1, y1;
-  tile_rect(a.x, a.y, (float)r, gx, gy, x0, y0, x1, y1);
-  const unsigned long long dbits = (unsigned long long)__float_as_uint(depth);
+                                                        GsrControl* ctrl, BinningHeader* header,
+                                                        uint32_t* __restrict__ hist, int npass) {
+  __shared__ uint32_t sh[gsr_sort::MAX_PASSES * gsr_sort::RADIX];
+  constexpr int RB = gsr_sort::RADIX_BITS, RMASK = gsr_sort::RADIX - 1;
+  if (hist) {
+    for (int k = threadIdx.x; k < npass * gsr_sort::RADIX; k += 256) sh[k] = 0;
+    __syncthreads();
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && header) { header->capacity = capacity; header->num_tiles = (uint32_t)(gx * gy); }
   bool over = false;
-  for (int y = y0; y < y1; ++y)
-    for (int x = x0; x < x1; ++x) {
-      if (off < capacity) {
-        keys[off] = ((unsigned long long)(uint32_t)(y * gx + x) << 32) | dbits;
-        vals[off] = (uint32_t)i;
-      } else {
-        over = true;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < P; i += gridDim.x * 256) {
+    const int r = radii[i];
+    if (r <= 0) continue;
+    uint32_t off = (i == 0) ? 0u : offsets[i - 1];
+    const float4 a = recs[i].a;
+    const float depth = recs[i].c.w;
+    int x0, y0, x1, y1;
+    tile_rect(a.x, a.y, (float)r, gx, gy, x0, y0, x1, y1);
+    const uint32_t dbits32 = __float_as_uint(depth);
+    const unsigned long long dbits = (unsigned long long)dbits32;
+    if (hist) {
+      const uint32_t total = (uint32_t)((x1 - x0) * (y1 - y0));
+      const uint32_t written = min(off + total, capacity) - min(off, capacity);
+      if (written) {
+#pragma unroll
+        for (int p = 0; p < 32 / RB; ++p)
+          if (p < npass) atomicAdd(&sh[p * gsr_sort::RADIX + ((dbits32 >> (p * RB)) & RMASK)], written);
       }
-      ++off;
     }
+    for (int y = y0; y < y1; ++y)
+      for (int x = x0; x < x1; ++x) {
+        if (off < capacity) {
+          const uint32_t t = (uint32_t)(y * gx + x);
+          keys[off] = ((unsigned long long)t << 32) | dbits;
+          vals[off] = (uint32_t)i;
+          if (hist)
+            for (int p = 32 / RB; p < npass; ++p) atomicAdd(&sh[p * gsr_sort::RADIX + ((t >> (p * RB - 32)) & RMASK)], 1u);
+        } else {
+          over = true;
+        }
+        ++off;
+      }
+  }
   if (over) ctrl->overflow = 1u;
+  if (hist) {
+    __syncthreads();
+    for (int k = threadIdx.x; k < npass * gsr_sort::RADIX; k += 256) {
+      const uint32_t c = sh[k];
+      if (c) atomicAdd(&hist[k], c);
+    }
+  }
 }
 
 cudaError_t launch_duplicate(const GsrView& v, int P, const int32_t* radii, const GeomState& geom,
                              unsigned long long* keys, uint32_t* vals, uint32_t capacity, GsrControl* ctrl,
-                             BinningHeader* header, cudaStream_t s) {
+                             BinningHeader* header, uint32_t* hist, int npass, cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
-  duplicate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, v.gx, v.gy, radii, geom.recs, geom.point_offsets, keys, vals,
-                                                   capacity, ctrl, header);
+  static_assert(32 % gsr_sort::RADIX_BITS == 0, "depth and tile-id digits must not share a radix digit");
+  int blocks = (P + 255) / 256;
+  if (hist && blocks > 148 * 8) blocks = 148 * 8;  // few, long-lived CTAs: the histogram flush is per CTA
+  duplicate_kernel<<<blocks, 256, 0, s>>>(P, v.gx, v.gy, radii, geom.recs, geom.point_offsets, keys, vals, capacity,
+                                          ctrl, header, hist, npass);
   count_launch();
   return cudaGetLastError();
 }

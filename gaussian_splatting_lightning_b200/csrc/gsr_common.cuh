@@ -111,17 +111,19 @@ struct ImgState {
 namespace gsr_sort {
 constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
-constexpr int THREADS = 256;
+constexpr int THREADS = 512;
 constexpr int WARPS = THREADS / 32;
-constexpr int IPT = 16;                       // items per thread
+constexpr int IPT = 8;                        // items per thread
 constexpr int TILE_ITEMS = THREADS * IPT;     // 4096 pairs per tile
 constexpr int MAX_PASSES = 8;
+constexpr int LB_GROUP = 32;                  // tiles per look-back group (radix_sort.cu)
 
 struct Workspace {
   uint32_t* hist;          // [MAX_PASSES][RADIX] digit histograms of all passes
   uint32_t* tile_counter;  // [MAX_PASSES] dynamic tile ids
   uint32_t* lookback;      // [MAX_PASSES][ntiles][RADIX]
-  size_t ntiles;
+  uint32_t* lookback_group;  // [MAX_PASSES][ngroups][RADIX]
+  size_t ntiles, ngroups;
   size_t bytes;
   static Workspace carve(char* base, int64_t capacity) {
     Workspace w;
@@ -132,6 +134,8 @@ struct Workspace {
     w.hist = (uint32_t*)take((size_t)MAX_PASSES * RADIX * 4);
     w.tile_counter = (uint32_t*)take((size_t)MAX_PASSES * 4);
     w.lookback = (uint32_t*)take((size_t)MAX_PASSES * w.ntiles * RADIX * 4);
+    w.ngroups = (w.ntiles + LB_GROUP - 1) / LB_GROUP;
+    w.lookback_group = (uint32_t*)take((size_t)MAX_PASSES * w.ngroups * RADIX * 4);
     w.bytes = off;
     return w;
   }
@@ -216,12 +220,13 @@ cudaError_t launch_preprocess(const GsrView& v, const GsrGaussiansDev& g, int32_
 cudaError_t launch_scan(int P, const GeomState& geom, GsrControl* ctrl, cudaStream_t s);
 cudaError_t launch_duplicate(const GsrView& v, int P, const int32_t* radii, const GeomState& geom,
                              unsigned long long* keys, uint32_t* vals, uint32_t capacity, GsrControl* ctrl,
-                             BinningHeader* header, cudaStream_t s);
+                             BinningHeader* header, uint32_t* hist, int npass, cudaStream_t s);
 // Sorts min(*d_n, capacity) pairs; the result lands in (keys_a, vals_a) when the pass
-// count is even, else in (keys_b, vals_b).  The workspace must be zeroed.
+// count is even, else in (keys_b, vals_b).  The workspace must be zeroed before the histograms
+// are built; hist_ready = the caller (key duplication) already filled ws.hist.
 cudaError_t launch_onesweep(unsigned long long* keys_a, uint32_t* vals_a, unsigned long long* keys_b,
                             uint32_t* vals_b, const unsigned int* d_n, uint32_t capacity, int end_bit,
-                            const gsr_sort::Workspace& ws, cudaStream_t s);
+                            const gsr_sort::Workspace& ws, bool hist_ready, cudaStream_t s);
 cudaError_t launch_tile_ranges(const unsigned long long* keys_sorted, const unsigned int* d_n, uint32_t capacity,
                                uint2* ranges, cudaStream_t s);
 cudaError_t launch_render_forward(const GsrView& v, const uint2* ranges, const uint32_t* point_list,

@@ -40,6 +40,7 @@ struct PreBwdArgs {
   float* dL_dscales;
   float* dL_drot;
   int accumulate;
+  int use_bulk;  // SH / dL_dsh blocks travel by bulk async copies
   float* max_radii2D;
   float* xyz_grad_accum;
   float* xyz_grad_count;
@@ -99,15 +100,19 @@ __device__ __forceinline__ void sh_backward(const float* __restrict__ sh, float*
   }
 }
 
-template <bool ACC>
-__global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdArgs a) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int P = a.g.P, M = a.g.M;
-  if (i >= P) return;
-  const bool sh_vec4 = a.dL_dsh && ((M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0);
-  const int radius = a.radii[i];
-
+// One Gaussian.  sh_row / dsh_row: this Gaussian's (M,3) coefficient row and gradient row -- in global
+// memory, or in the warp's shared-memory block when the rows travel by bulk copy (then DSH_ACC is
+// false: the bulk reduction does the += ).
+template <bool ACC, bool DSH_ACC>
+__device__ __forceinline__ void backward_one(const PreBwdArgs& a, const int i, const int radius,
+                                             const float* __restrict__ sh_row, float* __restrict__ dsh_row,
+                                             const bool sh_vec4) {
+  const int M = a.g.M;
   if (!(radius > 0)) {
+    if (!DSH_ACC && dsh_row) {  // a stored (or bulk-reduced) row of a culled Gaussian is all zeros
+      if (sh_vec4) for (int k = 0; k < 3 * M / 4; ++k) reinterpret_cast<float4*>(dsh_row)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      else for (int k = 0; k < 3 * M; ++k) dsh_row[k] = 0.f;
+    }
     if (ACC) return;  // accumulating: rows of culled Gaussians keep their value
     if (a.dL_dmeans2D) { a.dL_dmeans2D[3 * (size_t)i] = 0.f; a.dL_dmeans2D[3 * (size_t)i + 1] = 0.f; a.dL_dmeans2D[3 * (size_t)i + 2] = 0.f; }
     if (a.dL_dcolors) { a.dL_dcolors[3 * (size_t)i] = 0.f; a.dL_dcolors[3 * (size_t)i + 1] = 0.f; a.dL_dcolors[3 * (size_t)i + 2] = 0.f; }
@@ -119,11 +124,6 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
     if (a.dL_drot) reinterpret_cast<float4*>(a.dL_drot)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (a.dL_dcov3D)
       for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * (size_t)i + k] = 0.f;
-    if (a.dL_dsh) {
-      float* dsh = a.dL_dsh + (size_t)i * M * 3;
-      if (sh_vec4) for (int k = 0; k < 3 * M / 4; ++k) reinterpret_cast<float4*>(dsh)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-      else for (int k = 0; k < 3 * M; ++k) dsh[k] = 0.f;
-    }
     return;
   }
 
@@ -237,21 +237,19 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
   if (a.xyz_grad_count) a.xyz_grad_count[i] += 1.f;
 
   // SH
-  if (a.g.shs && (a.dL_dsh || a.dL_dmeans3D)) {
+  if (sh_row) {
     const float* __restrict__ cam = a.v.campos;
     const float dirx = px - cam[0], diry = py - cam[1], dirz = pz - cam[2];
     const float len = sqrtf(dirx * dirx + diry * diry + dirz * dirz);
     const float x = dirx / len, y = diry / len, z = dirz / len;
     const unsigned cl = a.clamped[i];
     const float g3[3] = {(cl & 1u) ? 0.f : g1.z, (cl & 2u) ? 0.f : g1.w, (cl & 4u) ? 0.f : g2.x};
-    const float* sh = a.g.shs + (size_t)i * M * 3;
-    float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)i * M * 3 : nullptr;
     float ddir[3];
     switch (a.v.deg) {
-      case 0: sh_backward<0, ACC>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
-      case 1: sh_backward<1, ACC>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
-      case 2: sh_backward<2, ACC>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
-      default: sh_backward<3, ACC>(sh, dsh, M, sh_vec4, x, y, z, g3, ddir); break;
+      case 0: sh_backward<0, DSH_ACC>(sh_row, dsh_row, M, sh_vec4, x, y, z, g3, ddir); break;
+      case 1: sh_backward<1, DSH_ACC>(sh_row, dsh_row, M, sh_vec4, x, y, z, g3, ddir); break;
+      case 2: sh_backward<2, DSH_ACC>(sh_row, dsh_row, M, sh_vec4, x, y, z, g3, ddir); break;
+      default: sh_backward<3, DSH_ACC>(sh_row, dsh_row, M, sh_vec4, x, y, z, g3, ddir); break;
     }
     const float ng = x * ddir[0] + y * ddir[1] + z * ddir[2];
     dmean[0] += (ddir[0] - x * ng) / len;
@@ -304,6 +302,67 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
   }
 }
 
+// The kernel proper: one warp per 32 consecutive Gaussians.  The warp's (32, M, 3) block of SH
+// coefficients is ONE contiguous range of the (P, M, 3) tensor, and so is its block of dL_dsh:
+//   * in:  an elected lane fetches the block with a 1-D bulk async copy (SASS UBLKCP) into the warp's
+//          shared-memory block behind the warp's mbarrier -- only if some Gaussian of the warp is
+//          visible -- while the lanes run the geometry part in registers;
+//   * out: each lane overwrites its own row of the block with its dL_dsh row, and the elected lane
+//          sends the block back with one bulk store, or -- accumulating -- one bulk REDUCTION
+//          (cp.reduce.async.bulk .add.f32, SASS UBLKRED): the += of 192 B per Gaussian happens at
+//          the L2, the SM never reads the old gradient.
+// Everything is per warp (no CTA barrier).  Falls back to per-lane global accesses when the block
+// is not 16-byte sized / aligned (odd M, unaligned tensors, ragged last warp).
+template <bool ACC>
+__global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdArgs a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ __align__(8) unsigned long long bars[8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int P = a.g.P, M = a.g.M;
+  const int w0 = blockIdx.x * 256 + warp * 32;  // first Gaussian of the warp
+  if (w0 >= P) return;
+  const int i = w0 + lane;
+  const int nrows = min(32, P - w0);
+  const int radius = i < P ? a.radii[i] : 0;
+  const bool any_visible = __any_sync(0xffffffffu, radius > 0);
+  if (ACC && !any_visible) return;  // nothing to add anywhere
+
+  const bool need_sh = a.g.shs && (a.dL_dsh || a.dL_dmeans3D);
+  const uint32_t row_bytes = (uint32_t)M * 12u, blk_bytes = (uint32_t)nrows * row_bytes;
+  const bool bulk = a.use_bulk && need_sh && (blk_bytes % 16u == 0u);
+  float* blk = reinterpret_cast<float*>(smem_raw + (size_t)warp * 32 * row_bytes);
+  const bool bulk_in = bulk && any_visible;
+  if (bulk_in) {
+    if (lane == 0) {
+      mbar_init(&bars[warp], 1);
+      mbar_arrive_expect_tx(&bars[warp], blk_bytes);
+      bulk_copy_g2s(blk, a.g.shs + (size_t)w0 * M * 3, blk_bytes, &bars[warp]);
+    }
+    __syncwarp();
+  }
+
+  if (bulk) {
+    // rows live in the warp's shared block; 128-bit row accesses need 16-byte rows
+    const bool vec4 = (M & 3) == 0;
+    if (bulk_in) mbar_wait(&bars[warp], 0);
+    if (i < P) backward_one<ACC, false>(a, i, radius, blk + (size_t)lane * M * 3, a.dL_dsh ? blk + (size_t)lane * M * 3 : nullptr, vec4);
+    if (a.dL_dsh) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // my generic-proxy row writes -> async proxy
+      __syncwarp();
+      if (lane == 0) {
+        float* dst = a.dL_dsh + (size_t)w0 * M * 3;
+        if (ACC) bulk_reduce_add_s2g(dst, blk, blk_bytes);
+        else bulk_copy_s2g(dst, blk, blk_bytes);
+        bulk_commit_and_wait_read();  // the block must stay intact until the copy engine has read it
+      }
+    }
+  } else if (i < P) {
+    const bool vec4 = a.dL_dsh && ((M & 3) == 0) && ((reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0);
+    backward_one<ACC, ACC>(a, i, radius, need_sh ? a.g.shs + (size_t)i * M * 3 : nullptr,
+                           a.dL_dsh ? a.dL_dsh + (size_t)i * M * 3 : nullptr, vec4);
+  }
+}
+
 cudaError_t launch_preprocess_backward(const GsrView& v, const GsrGaussiansDev& g, const int32_t* radii,
                                        const GeomState& geom, const float* grad_acc, const PreBwdOut& o,
                                        cudaStream_t s) {
@@ -315,8 +374,16 @@ cudaError_t launch_preprocess_backward(const GsrView& v, const GsrGaussiansDev& 
   a.dL_dscales = o.dL_dscales; a.dL_drot = o.dL_drot;
   a.accumulate = o.accumulate;
   a.max_radii2D = o.max_radii2D; a.xyz_grad_accum = o.xyz_grad_accum; a.xyz_grad_count = o.xyz_grad_count;
-  if (o.accumulate) preprocess_backward_kernel<true><<<(g.P + 255) / 256, 256, 0, s>>>(a);
-  else preprocess_backward_kernel<false><<<(g.P + 255) / 256, 256, 0, s>>>(a);
+  // bulk copies need 16-byte aligned global addresses; a warp's block offset 32*M*12 is a multiple of 16
+  const size_t smem = g.shs ? (size_t)256 * g.M * 12 : 0;
+  a.use_bulk = g.shs && smem <= 200 * 1024 && (reinterpret_cast<uintptr_t>(g.shs) & 15) == 0 &&
+               (!a.dL_dsh || (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0);
+  auto kern = o.accumulate ? preprocess_backward_kernel<true> : preprocess_backward_kernel<false>;
+  if (a.use_bulk && smem > 48 * 1024 - 256) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return e;
+  }
+  kern<<<(g.P + 255) / 256, 256, a.use_bulk ? smem : 0, s>>>(a);
   count_launch();
   return cudaGetLastError();
 }

@@ -23,6 +23,11 @@ __host__ __device__ __forceinline__ SubTile make_subtile(int sx0, int sy0, int W
 __host__ __device__ __forceinline__ float gsr_clampf(float v, float lo, float hi) {
   return fminf(fmaxf(v, lo), hi);
 }
+__host__ __device__ __forceinline__ float __int_as_float_compat(int bits) {
+  union { int i; float f; } u;
+  u.i = bits;
+  return u.f;
+}
 
 // ---- staged record: what the compositing kernels keep in shared memory -----------------
 // The quadratic form is pre-scaled into the log2 domain when a batch is staged, so that the
@@ -73,6 +78,7 @@ __device__ __forceinline__ int msb_index(uint32_t x) {
 
 // Staged batch: three planes of 256 float4, plane p of entry j at byte offset p*4096 + j*16.
 //   plane 0 {mean.x, mean.y, hA, hB}   plane 1 {hC, opacity, r, g}   plane 2 {b, 1/z, tau2, bits(gaussian id)}
+//   forward only: plane 3 = cull plane (make_cull_plane)
 #define GSR_PLANE 4096
 
 // e = hA dx^2 + hC dy^2 + hB dx dy with a FIXED rounding sequence: the forward and the backward
@@ -98,42 +104,48 @@ __device__ __forceinline__ float splat_alpha(float opacity, float G) {
 // e(d) = hA dx^2 + hB dx dy + hC dy^2 >= 0 for a positive-definite conic.
 // The minimum of the convex e over the rectangle is 0 if the centre lies inside it, else it is
 // attained on an edge that faces the centre; on such an edge e is a 1-D parabola whose clamped
-// vertex gives the minimum in closed form.  The splat is rejected only if that minimum exceeds
-// tau2 by more than a margin that covers the FP32 evaluation error of e in the per-pixel
-// loop, of this test, of logf and of ex2.approx (bounded by a few 1e-7 * S, S = the sum of the
-// absolute terms of e at the farthest corner).  Returns true when in doubt.
+// vertex gives the minimum in closed form.  Both candidate points (clamped vertex on the nearest
+// vertical and on the nearest horizontal line of the rectangle) are evaluated unconditionally:
+// each is a point OF the rectangle, and whenever an edge faces the centre its candidate is that
+// edge's minimum, so min(e1, e2) is the exact minimum in every case (and 0 when the centre is
+// inside) -- no branches.  The splat is rejected only if that minimum exceeds tau2 by more than
+// a margin that covers the FP32 evaluation error of e in the per-pixel loop, of this test, of
+// logf and of ex2.approx (a few 1e-7 * S, S >= the sum of the absolute terms of e anywhere in
+// the rectangle; by AM-GM |hB| DX DY <= hA DX^2 + hC DY^2 for a convex form).
+//
+// Everything that does not depend on the rectangle is computed ONCE per staged splat
+// (make_cull_plane, by the thread that stages it) instead of once per warp:
+//   cull = {kx = -hB / (2 hC), ky = -hB / (2 hA), tauM, -}
+//   tauM = tau2 + 3e-5, or +inf when the form is not provably convex (always keep), or -inf when
+//   opacity < 1/255 (alpha can never reach the floor) and for padding entries.
+__host__ __device__ __forceinline__ float4 make_cull_plane(float hA, float hB, float hC, float tau2) {
+  const float inf = __int_as_float_compat(0x7f800000);
+  float4 c;
+  c.w = 0.f;
+  if (!(tau2 >= -1.5e-4f)) { c.x = 0.f; c.y = 0.f; c.z = -inf; return c; }
+  if (!(hA > 0.f && hC > 0.f && 4.f * hA * hC - hB * hB > 0.f)) { c.x = 0.f; c.y = 0.f; c.z = inf; return c; }
+  c.x = -0.5f * hB / hC;
+  c.y = -0.5f * hB / hA;
+  c.z = tau2 + 3e-5f;
+  return c;
+}
+
 //   a = {mean.x, mean.y, hA, hB}
-__host__ __device__ __forceinline__ bool subtile_may_contribute(const float4 a, const float hC, const float tau2,
+__host__ __device__ __forceinline__ bool subtile_may_contribute(const float4 a, const float hC, const float4 cull,
                                                                 const SubTile st) {
   const float mx = a.x, my = a.y, hA = a.z, hB = a.w;
-  if (!(tau2 >= -1.5e-4f)) return false;  // opacity < 1/255: alpha can never reach the floor
-  if (!(hA > 0.f && hC > 0.f && 4.f * hA * hC - hB * hB > 0.f)) return true;  // not provably convex: keep
   const float dxn = mx - gsr_clampf(mx, st.x0, st.x1);  // dx at the nearest column (0 if inside)
   const float dyn = my - gsr_clampf(my, st.y0, st.y1);
-  if (dxn == 0.f && dyn == 0.f) return true;
   const float dx_lo = mx - st.x1, dx_hi = mx - st.x0;  // range of dx over the rectangle
   const float dy_lo = my - st.y1, dy_hi = my - st.y0;
-  float mine = 3.0e38f;
-  if (dxn != 0.f) {  // facing vertical edge: dx fixed, vertex dy* = -hB dx / (2 hC)
-#ifdef __CUDA_ARCH__
-    const float dys = gsr_clampf(__fdividef(-0.5f * hB * dxn, hC), dy_lo, dy_hi);
-#else
-    const float dys = gsr_clampf(-0.5f * hB * dxn / hC, dy_lo, dy_hi);
-#endif
-    mine = hA * dxn * dxn + hC * dys * dys + hB * dxn * dys;
-  }
-  if (dyn != 0.f) {  // facing horizontal edge: dy fixed, vertex dx* = -hB dy / (2 hA)
-#ifdef __CUDA_ARCH__
-    const float dxs = gsr_clampf(__fdividef(-0.5f * hB * dyn, hA), dx_lo, dx_hi);
-#else
-    const float dxs = gsr_clampf(-0.5f * hB * dyn / hA, dx_lo, dx_hi);
-#endif
-    mine = fminf(mine, hA * dxs * dxs + hC * dyn * dyn + hB * dxs * dyn);
-  }
+  const float dys = gsr_clampf(cull.x * dxn, dy_lo, dy_hi);  // vertex on the line dx = dxn
+  const float dxs = gsr_clampf(cull.y * dyn, dx_lo, dx_hi);  // vertex on the line dy = dyn
+  const float e1 = hA * dxn * dxn + hC * dys * dys + hB * dxn * dys;
+  const float e2 = hA * dxs * dxs + hC * dyn * dyn + hB * dxs * dyn;
   const float DX = fmaxf(fabsf(dx_lo), fabsf(dx_hi));
   const float DY = fmaxf(fabsf(dy_lo), fabsf(dy_hi));
-  const float S = hA * DX * DX + hC * DY * DY + fabsf(hB) * DX * DY;
-  return mine <= tau2 + (4e-6f * S + 3e-5f);
+  const float S = hA * DX * DX + hC * DY * DY;
+  return fminf(e1, e2) <= cull.z + 8e-6f * S;
 }
 
 // ---- per-(warp, 32-splat chunk) hit words -------------------------------------------------

@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(256) render_forward_kernel(const GsrView v, co
                                                              float* __restrict__ final_T,
                                                              uint32_t* __restrict__ n_contrib,
                                                              uint32_t* __restrict__ hits) {
-  __shared__ float4 sRec[3][256];  // staged batch, planes as described in render_common.cuh
+  __shared__ float4 sRec[4][256];  // staged batch, planes as described in render_common.cuh (3 = cull plane)
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
@@ -71,14 +71,16 @@ __global__ void __launch_bounds__(256) render_forward_kernel(const GsrView v, co
       float4 a = r->a, b = r->b, c = r->c;
       a.z *= GSR_HALF_LOG2E; a.w *= GSR_LOG2E; b.x *= GSR_HALF_LOG2E; c.z *= GSR_LOG2E;
       sRec[0][tid] = a; sRec[1][tid] = b; sRec[2][tid] = c;
+      sRec[3][tid] = make_cull_plane(a.z, a.w, b.x, c.z);
+    } else {
+      sRec[3][tid] = make_float4(0.f, 0.f, __int_as_float(0xff800000), 0.f);  // padding: never a hit
     }
     __syncthreads();
     if (__all_sync(0xffffffffu, done)) continue;  // whole warp saturated: only keep the barriers
 
     for (int c0 = 0; c0 < cnt; c0 += 32) {
       // one splat per lane against the warp's sub-tile
-      bool hit = false;
-      if (c0 + lane < cnt) hit = subtile_may_contribute(sRec[0][c0 + lane], sRec[1][c0 + lane].x, sRec[2][c0 + lane].z, st);
+      const bool hit = subtile_may_contribute(sRec[0][c0 + lane], sRec[1][c0 + lane].x, sRec[3][c0 + lane], st);
       uint32_t mask = __ballot_sync(0xffffffffu, hit);
       uint32_t used = 0;
       while (mask) {

@@ -105,3 +105,55 @@ def test_gs_lightning_rasterize_entry_points(oracle_lib):
     assert frac <= 2e-4 and mx <= 2e-2
     vis = markVisible(d["means3D"], rs.viewmatrix, rs.projmatrix)
     assert np.array_equal(vis.cpu().numpy(), oracle_lib.mark_visible(arrays["means3D"], cam.viewmatrix))
+
+
+def test_backward_accumulate_stats_and_optional_outputs():
+    """GSR_GRADS_ACCUMULATE sums views into one buffer; the densification statistics are taken per view
+    (gaussian_model.py:174-181, visible_mask = radii > 0); NULL outputs are not produced."""
+    from gaussian_splatting_lightning_b200.rasterizer import backward_raw
+    names = ("dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales",
+             "dL_drotations")
+    P = 9000
+    scene = U.synthetic.make_scene(P, 3, 192, 128, seed=21)
+    arrays = {k: v.numpy() for k, v in scene.items()}
+    rng = np.random.default_rng(5)
+    flat = {n: None for n in names}
+    max_radii = torch.zeros(P, device=U.DEV)
+    accum = torch.zeros(P, device=U.DEV)
+    count = torch.zeros(P, device=U.DEV)
+    want_sum, want_max, want_accum, want_count = None, np.zeros(P, np.float32), np.zeros(P, np.float64), np.zeros(P)
+    for k in (0, 3, 5):  # three views of an 8-view orbit; view 3/5 cull part of the scene
+        c = U.synthetic.make_camera(192, 128, k=k, num_views=8)
+        import oracle
+        cam = oracle.Camera(128, 192, c["tanfovx"], c["tanfovy"], c["viewmatrix"].numpy(), c["projmatrix"].numpy(),
+                            c["campos"].numpy(), sh_degree=3)
+        out = U.run_cuda_forward(cam, arrays)
+        dC = torch.tensor(rng.standard_normal((3, 128, 192)).astype(np.float32), device=U.DEV)
+        d = out["d"]
+        args = (out["rs"], d["means3D"], out["radii"], d["shs"], None, d["opacities"], d["scales"], d["rotations"],
+                None, dC, None, out["geom"], out["binning"], out["img"], out["R"])
+        plain = dict(zip(names, backward_raw(*args)))
+        if flat["dL_dsh"] is None:
+            for n in ("dL_dmeans3D", "dL_dsh", "dL_dopacity", "dL_dscales", "dL_drotations"):
+                flat[n] = torch.zeros_like(plain[n])
+        acc = backward_raw(*args, accumulate_into={n: t for n, t in flat.items() if t is not None},
+                           stats=dict(max_radii2D=max_radii, xyz_grad_accum=accum, xyz_grad_count=count))
+        assert acc[0] is None and acc[1] is None and acc[4] is None  # dL_dmeans2D / dL_dcolors / dL_dcov3D not wanted
+        vis = (out["radii"] > 0).cpu().numpy()
+        assert 0 < vis.sum()
+        want_sum = {n: plain[n].double().cpu().numpy() + (0 if want_sum is None else want_sum[n]) for n in flat if flat[n] is not None}
+        want_max = np.where(vis, np.maximum(want_max, out["radii"].cpu().numpy().astype(np.float32)), want_max)
+        want_accum += np.where(vis, np.linalg.norm(plain["dL_dmeans2D"].double().cpu().numpy()[:, :2], axis=1), 0.0)
+        want_count += vis
+        # only-what-is-asked-for path of the non-accumulating call
+        only = backward_raw(*args, want=("dL_dopacity", "dL_dsh"))
+        assert [t is not None for t in only] == [False, False, True, False, False, True, False, False]
+        assert torch.equal(only[2], plain["dL_dopacity"]) or torch.allclose(only[2], plain["dL_dopacity"], rtol=1e-4, atol=1e-6)
+    torch.cuda.synchronize()
+    for n, w in want_sum.items():
+        g = flat[n].cpu().numpy().astype(np.float64)
+        s = max(1.0, float(np.abs(w).max()))
+        assert np.abs(g - w).max() / s <= 2e-4, n  # atomics make each backward run-to-run different in the last bits
+    assert np.array_equal(max_radii.cpu().numpy(), want_max)
+    assert np.array_equal(count.cpu().numpy(), want_count.astype(np.float32))
+    assert np.abs(accum.cpu().numpy() - want_accum).max() <= 2e-4 * max(1.0, want_accum.max())
