@@ -245,17 +245,11 @@ def run_ours(args):
     dL_dcolor = torch.randn(3, H, W, generator=g).to(device)
     dL_dinv = torch.randn(1, H, W, generator=g).to(device)
 
-    # flat per-Gaussian gradient buffer [means3D 3 | sh 3M | opacity 1 | scales 3 | rot 4] = 59 floats at M=16
-    widths = [3, 3 * M, 1, 3, 4]
-    flat = torch.zeros(P * sum(widths), device=device)
-    views_flat, o = [], 0
-    for w_ in widths:
-        views_flat.append(flat[o:o + P * w_].view(P, w_)); o += P * w_
-    stats = torch.zeros(2, P, device=device)      # xyz_grad_accum, xyz_grad_count (gaussian_model.py:174-181)
-    max_radii = torch.zeros(P, device=device)
-    acc_into = dict(dL_dmeans3D=views_flat[0], dL_dsh=views_flat[1], dL_dopacity=views_flat[2],
-                    dL_dscales=views_flat[3], dL_drotations=views_flat[4])
-    stat_into = dict(max_radii2D=max_radii, xyz_grad_accum=stats[0], xyz_grad_count=stats[1])
+    # per-step exchange buffers: flat gradient buffer [means3D 3 | sh 3M | opacity 1 | scales 3 | rot 4]
+    # (59 floats per Gaussian at M = 16) + densification-statistics deltas (view_parallel.py)
+    from gaussian_splatting_lightning_b200.view_parallel import StepBuffers
+    bufs = StepBuffers(P, M, device)
+    acc_into, stat_into = bufs.grads(), bufs.densify_stats()
 
     def one_view(c, fwd_only=False):
         rs = c["settings"]
@@ -272,15 +266,11 @@ def run_ours(args):
 
     def step(fwd_only=False):
         if not fwd_only:
-            flat.zero_()        # per-step buffers: gradient sum and the statistics DELTAS of this step's views
-            stats.zero_()
-            max_radii.zero_()
+            bufs.zero_()        # per-step buffers: gradient sum and the statistics DELTAS of this step's views
         for c in cams:
             one_view(c, fwd_only)
         if world > 1 and not fwd_only:
-            dist.all_reduce(flat)
-            dist.all_reduce(stats)
-            dist.all_reduce(max_radii, op=dist.ReduceOp.MAX)
+            bufs.all_reduce()   # sum(flat), sum(stats), max(max_radii) over the ranks
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -357,12 +347,33 @@ def run_ours(args):
                                c["host"]["campos"].reshape(-1), torch.zeros(3)]).pin_memory() for c in cams]
         loss_host = torch.zeros(vpr).pin_memory()
 
+        copy_stream = torch.cuda.Stream(device)
+        slots = [dict(cam=torch.empty(38, device=device), gt=torch.empty(3, H, W, device=device),
+                      ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
+
+        def upload(j):
+            """this step's host inputs of view j -> device, on the copy stream (double-buffered, the way a
+            prefetching data loader hands batches over); every byte is copied inside the timed region"""
+            sl = slots[j % 2]
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(sl["free"])           # the view that used this slot last is done with it
+                sl["cam"].copy_(cam_host[j], non_blocking=True)
+                sl["gt"].copy_(gt_host[j], non_blocking=True)
+                sl["ready"].record(copy_stream)
+
         def e2e_step():
+            main = torch.cuda.current_stream()
             for p_ in params.values():
                 p_.grad = None
+            for sl in slots:
+                sl["free"].record(main)
+            upload(0)
             for j, c in enumerate(cams):
-                cam_d = cam_host[j].to(device, non_blocking=True)
-                gt = gt_host[j].to(device, non_blocking=True)
+                if j + 1 < vpr:
+                    upload(j + 1)                            # overlaps the rendering of view j
+                sl = slots[j % 2]
+                main.wait_event(sl["ready"])
+                cam_d, gt = sl["cam"], sl["gt"]
                 rs = c["settings"]._replace(viewmatrix=cam_d[0:16].view(4, 4), projmatrix=cam_d[16:32].view(4, 4),
                                             campos=cam_d[32:35], bg=cam_d[35:38])
                 sp = torch.zeros_like(params["means3D"], requires_grad=True)
@@ -373,16 +384,18 @@ def run_ours(args):
                 loss = (color - gt).abs().mean()
                 loss.backward()
                 loss_host[j].copy_(loss.detach(), non_blocking=True)
+                sl["free"].record(main)
             if world > 1:
                 for p_ in params.values():
                     dist.all_reduce(p_.grad)
-            torch.cuda.current_stream().synchronize()   # the step's result (losses) is on the host
+            main.synchronize()                               # the step's result (losses) is on the host
             return float(loss_host.sum())
 
         ms_e2e, _, _ = timed(e2e_step, K, 2)
         h2d = vpr * (3 * H * W * 4 + 38 * 4)
         e2e = {"value": frames / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": vpr * 4,
-               "what": "GaussianRasterizer autograd API + L1 loss; per view: pinned GT image and camera H2D, loss D2H"}
+               "what": "GaussianRasterizer autograd API + L1 loss; per view: pinned GT image and camera H2D (copy stream, "
+                       "double-buffered, inside the timed region), loss D2H"}
         del params
 
     if rank != 0:

@@ -1,0 +1,119 @@
+"""View-parallel training step of the rasterizer hot path.
+
+The path shards by camera view: every rank holds the full (replicated) Gaussian set, renders its own
+views of the optimiser step and accumulates their gradients -- straight from the preprocess-backward
+kernel, GSR_GRADS_ACCUMULATE -- into ONE flat fp32 buffer laid out for a single all-reduce:
+
+    flat = [ dL_dmeans3D (P,3) | dL_dsh (P,M,3) | dL_dopacity (P,1) | dL_dscales (P,3) | dL_drotations (P,4) ]
+           = 59 floats per Gaussian at SH degree 3
+
+plus the step's densification-statistics deltas, taken per view BEFORE the views are summed
+(gs_lightning/modules/gaussian_model.py:174-181, gs_lightning/lightning/gs_lightning_module.py:192-195):
+
+    stats[0] = sum over views of || dL_dmeans2D[:, :2] ||  where radii > 0     (xyz_grad_accum delta)
+    stats[1] = number of views with radii > 0                                   (xyz_grad_count delta)
+    max_radii = max over views of radii                                         (max_radii2D candidate)
+
+One exchange per step: all_reduce(sum) of `flat`, all_reduce(sum) of `stats`, all_reduce(max) of
+`max_radii`.  Every rank then applies the identical optimiser / densification update, so the
+replicas stay bit-identical.  There is no collective inside the render path.
+
+Only torch + torch.distributed here (works on any device and backend: NCCL on the GPUs, gloo in the
+CPU tests of the exchange); rendering itself is CUDA-only (rasterizer.py).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+GRAD_FIELDS = ("dL_dmeans3D", "dL_dsh", "dL_dopacity", "dL_dscales", "dL_drotations")
+
+
+def partition_views(num_views: int, world_size: int, rank: int) -> List[int]:
+    """Views of one optimiser step owned by `rank`: {k : k mod world_size == rank}."""
+    if not (0 <= rank < world_size):
+        raise ValueError(f"rank {rank} outside world of size {world_size}")
+    return list(range(rank, num_views, world_size))
+
+
+class StepBuffers:
+    """The per-step exchange buffers of one rank."""
+
+    def __init__(self, num_gaussians: int, sh_coeffs: int, device, dtype=torch.float32):
+        P, M = int(num_gaussians), int(sh_coeffs)
+        self.P, self.M = P, M
+        self.widths = dict(dL_dmeans3D=3, dL_dsh=3 * M, dL_dopacity=1, dL_dscales=3, dL_drotations=4)
+        self.floats_per_gaussian = sum(self.widths.values())
+        self.flat = torch.zeros(P * self.floats_per_gaussian, device=device, dtype=dtype)
+        self.stats = torch.zeros(2, P, device=device, dtype=dtype)
+        self.max_radii = torch.zeros(P, device=device, dtype=dtype)
+        self._views: Dict[str, torch.Tensor] = {}
+        o = 0
+        for name, w in self.widths.items():
+            shape = (P, M, 3) if name == "dL_dsh" else (P, w)
+            self._views[name] = self.flat[o:o + P * w].view(shape)
+            o += P * w
+
+    # -- what the rasterizer backward writes into -------------------------------------------------
+    def grads(self) -> Dict[str, torch.Tensor]:
+        """name -> view into `flat`; pass as backward_raw(..., accumulate_into=...)."""
+        return dict(self._views)
+
+    def densify_stats(self) -> Dict[str, torch.Tensor]:
+        """pass as backward_raw(..., stats=...)."""
+        return dict(max_radii2D=self.max_radii, xyz_grad_accum=self.stats[0], xyz_grad_count=self.stats[1])
+
+    def zero_(self) -> None:
+        self.flat.zero_()
+        self.stats.zero_()
+        self.max_radii.zero_()
+
+    # -- the one exchange step --------------------------------------------------------------------
+    def all_reduce(self, group=None, async_op: bool = False):
+        """Sum gradients and statistics deltas, max the radii, over the ranks of `group`."""
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return []
+        works = [dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op),
+                 dist.all_reduce(self.stats, op=dist.ReduceOp.SUM, group=group, async_op=async_op),
+                 dist.all_reduce(self.max_radii, op=dist.ReduceOp.MAX, group=group, async_op=async_op)]
+        return [w for w in works if w is not None]
+
+    def exchanged_bytes(self) -> int:
+        return (self.flat.numel() + self.stats.numel() + self.max_radii.numel()) * self.flat.element_size()
+
+    # -- consumers ----------------------------------------------------------------------------------
+    def apply_densify_stats(self, max_radii2D: torch.Tensor, xyz_grad_accum: torch.Tensor,
+                            xyz_grad_count: torch.Tensor) -> None:
+        """Fold the (all-reduced) deltas of this step into the model's running statistics, the way
+        GaussianModel.update_max_radii2D / update_xyz_gradient do view by view."""
+        seen = self.stats[1] > 0
+        max_radii2D[seen] = torch.maximum(max_radii2D[seen], self.max_radii[seen].to(max_radii2D.dtype))
+        xyz_grad_accum.add_(self.stats[0].to(xyz_grad_accum.dtype).view_as(xyz_grad_accum))
+        xyz_grad_count.add_(self.stats[1].to(xyz_grad_count.dtype).view_as(xyz_grad_count))
+
+
+def render_step(settings_per_view: Sequence, scene: Dict[str, torch.Tensor], dL_dcolor, dL_dinvdepth,
+                buffers: StepBuffers, group=None, exchange: bool = True) -> List[torch.Tensor]:
+    """Forward + backward of this rank's views into `buffers`, then the exchange.
+
+    settings_per_view: GaussianRasterizationSettings of the views this rank owns;
+    dL_dcolor / dL_dinvdepth: callables view_index, color, invdepth -> gradient tensors (or fixed tensors).
+    Returns the rendered colour images.
+    """
+    from .rasterizer import backward_raw, forward_raw
+    buffers.zero_()
+    images = []
+    for k, rs in enumerate(settings_per_view):
+        R, color, radii, geom, binning, img, invd, _cap = forward_raw(
+            rs, scene["means3D"], scene["shs"], None, scene["opacities"], scene["scales"], scene["rotations"], None)
+        gC = dL_dcolor(k, color, invd) if callable(dL_dcolor) else dL_dcolor
+        gD = dL_dinvdepth(k, color, invd) if callable(dL_dinvdepth) else dL_dinvdepth
+        backward_raw(rs, scene["means3D"], radii, scene["shs"], None, scene["opacities"], scene["scales"],
+                     scene["rotations"], None, gC, gD, geom, binning, img, R,
+                     accumulate_into=buffers.grads(), stats=buffers.densify_stats())
+        images.append(color)
+    if exchange:
+        buffers.all_reduce(group)
+    return images

@@ -1,0 +1,108 @@
+"""World-size-2 gloo test (CPU) of the view-parallel exchange step: view partition,
+flat gradient-buffer layout, sum / sum / max all-reduce and the per-view densification statistics.
+The per-view gradients are synthetic here -- rendering is CUDA-only; the GPU tests cover the kernels
+that write these buffers (tests/test_gpu_api.py::test_backward_accumulate_stats_and_optional_outputs)."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from gaussian_splatting_lightning_b200.view_parallel import GRAD_FIELDS, StepBuffers, partition_views
+
+P, M, VIEWS, WORLD = 257, 16, 7, 2
+
+
+def _view_contribution(k: int):
+    """Deterministic fake result of rendering view k: gradients, radii, screen-space gradient norm."""
+    g = torch.Generator().manual_seed(1000 + k)
+    shapes = dict(dL_dmeans3D=(P, 3), dL_dsh=(P, M, 3), dL_dopacity=(P, 1), dL_dscales=(P, 3), dL_drotations=(P, 4))
+    grads = {n: torch.randn(s, generator=g) for n, s in shapes.items()}
+    radii = torch.randint(0, 40, (P,), generator=g)
+    radii[torch.rand(P, generator=g) < 0.3] = 0          # culled in this view
+    norm = torch.rand(P, generator=g)
+    return grads, radii, norm
+
+
+def _accumulate_like_the_kernel(buf: StepBuffers, k: int):
+    grads, radii, norm = _view_contribution(k)
+    vis = radii > 0
+    for n, t in buf.grads().items():
+        t[vis] += grads[n][vis]                            # GSR_GRADS_ACCUMULATE leaves culled rows alone
+    st = buf.densify_stats()
+    st["max_radii2D"][vis] = torch.maximum(st["max_radii2D"][vis], radii[vis].float())
+    st["xyz_grad_accum"][vis] += norm[vis]
+    st["xyz_grad_count"][vis] += 1
+
+
+def _worker(rank: int, port: int, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=WORLD)
+    try:
+        buf = StepBuffers(P, M, "cpu")
+        buf.zero_()
+        mine = partition_views(VIEWS, WORLD, rank)
+        for k in mine:
+            _accumulate_like_the_kernel(buf, k)
+        buf.all_reduce()
+        out[rank] = dict(flat=buf.flat.clone(), stats=buf.stats.clone(), max_radii=buf.max_radii.clone(), views=mine)
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def test_partition_covers_every_view_once():
+    for world in (1, 2, 3, 8):
+        for views in (0, 1, 7, 64):
+            got = sorted(k for r in range(world) for k in partition_views(views, world, r))
+            assert got == list(range(views))
+    assert partition_views(64, 8, 3) == list(range(3, 64, 8))
+
+
+def test_flat_layout_is_one_contiguous_buffer():
+    buf = StepBuffers(10, 16, "cpu")
+    assert buf.floats_per_gaussian == 59 and buf.flat.numel() == 590
+    off = 0
+    for n in GRAD_FIELDS:
+        v = buf.grads()[n]
+        assert v.is_contiguous() and v.data_ptr() == buf.flat.data_ptr() + 4 * off
+        off += v.numel()
+    assert off == buf.flat.numel()
+    assert buf.exchanged_bytes() == (590 + 20 + 10) * 4
+
+
+def test_world2_exchange_matches_single_process_sum():
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(_free_port(), out), nprocs=WORLD, join=True)
+    ref = StepBuffers(P, M, "cpu")
+    for k in range(VIEWS):
+        _accumulate_like_the_kernel(ref, k)
+    assert sorted(out[0]["views"] + out[1]["views"]) == list(range(VIEWS))
+    for r in range(WORLD):
+        assert torch.allclose(out[r]["flat"], ref.flat, rtol=1e-6, atol=1e-6)
+        assert torch.allclose(out[r]["stats"][0], ref.stats[0], rtol=1e-6, atol=1e-6)
+        assert torch.equal(out[r]["stats"][1], ref.stats[1])
+        assert torch.equal(out[r]["max_radii"], ref.max_radii)
+    assert torch.equal(out[0]["flat"], out[1]["flat"])      # replicas stay bit-identical
+
+    # folding the deltas into the model's running statistics == the reference's view-by-view update
+    max_r, acc, cnt = torch.zeros(P), torch.zeros(P, 1), torch.zeros(P, 1)
+    ref.apply_densify_stats(max_r, acc, cnt)
+    w_max, w_acc, w_cnt = torch.zeros(P), torch.zeros(P, 1), torch.zeros(P, 1)
+    for k in range(VIEWS):
+        _, radii, norm = _view_contribution(k)
+        vis = radii > 0
+        w_max[vis] = torch.max(w_max[vis], radii[vis].float())      # gaussian_model.py:174-176
+        w_acc[vis] += norm[vis, None]                                # gaussian_model.py:178-181
+        w_cnt[vis] += 1
+    assert torch.equal(max_r, w_max) and torch.allclose(acc, w_acc, atol=1e-6) and torch.equal(cnt, w_cnt)
