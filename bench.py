@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3", choices=list(synthetic.CONFIGS))
     ap.add_argument("--views-per-rank", type=int, default=8)
+    ap.add_argument("--streams", type=int, default=3, help="CUDA streams the views of a step are spread over")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -264,11 +265,13 @@ def run_ours(args):
                      accumulate_into=acc_into, stats=stat_into)
         return color
 
+    from gaussian_splatting_lightning_b200.view_parallel import ViewStreams
+    vstreams = ViewStreams(device, args.streams)   # independent views of a step round-robin over CUDA streams
+
     def step(fwd_only=False):
         if not fwd_only:
             bufs.zero_()        # per-step buffers: gradient sum and the statistics DELTAS of this step's views
-        for c in cams:
-            one_view(c, fwd_only)
+        vstreams.run(len(cams), lambda j: one_view(cams[j], fwd_only))
         if world > 1 and not fwd_only:
             bufs.all_reduce()   # sum(flat), sum(stats), max(max_radii) over the ranks
 
@@ -329,9 +332,12 @@ def run_ours(args):
             clocks["value_from"] = ("unsampled region (every sampled attempt was > 10 % slower: the nvidia-smi poller "
                                     "stalled launches); clocks are those of the adjacent sampled attempts")
     # per-stage CUDA events (on the launching stream, inside the C library) in a second pass of the same steps
+    # (views one after another on ONE stream here, so that a stage's events bracket that stage alone)
+    vstreams_timed, vstreams = vstreams, ViewStreams(device, 1)
     N.profile_reset(); N.profile_enable(True)
     timed(step, K, 0)
     prof = N.profile_read(); N.profile_enable(False)
+    vstreams = vstreams_timed
     ms_fwd, _, _ = timed(lambda: step(True), K, 2)
 
     frames = K * vpr * world
@@ -443,7 +449,7 @@ def run_ours(args):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {P} Gaussians, SH degree {deg}, {W}x{H}, fwd+bwd + densification "
                                f"stats, {vpr} views per GPU per step" + (", NCCL all-reduce of 59 floats/Gaussian + stats" if world > 1 else ""),
-                   "views_per_rank": vpr, "frames_per_step": vpr * world, "parallelism": f"view-parallel x{world}",
+                   "views_per_rank": vpr, "frames_per_step": vpr * world, "streams_per_rank": args.streams, "parallelism": f"view-parallel x{world}",
                    "l2": "inputs (236 MB of Gaussian parameters + 49 MB records) exceed the 126 MB L2; no flush",
                    "num_rendered_mean": counters["R"], "visible_mean": counters["Pvis"],
                    "pairs_A_mean": counters["A"], "list_entries_L_mean": counters["L"]},

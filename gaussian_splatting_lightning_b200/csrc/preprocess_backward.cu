@@ -46,20 +46,21 @@ struct PreBwdArgs {
   float* xyz_grad_count;
 };
 
-// store or accumulate one float / float4
+// store or accumulate one float / float4.  Accumulation is an L2 reduction (red.global.add.f32), so
+// views rendered concurrently on different streams may accumulate into the same buffers.
 template <bool ACC>
 __device__ __forceinline__ void put(float* p, float v) {
-  if (ACC) *p += v; else *p = v;
+  if (ACC) atomicAdd(p, v); else *p = v;
 }
 template <bool ACC>
 __device__ __forceinline__ void put4(float4* p, float4 v) {
   if (ACC) {
-    const float4 o = *p;
-    v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+    float* f = reinterpret_cast<float*>(p);
+    atomicAdd(f, v.x); atomicAdd(f + 1, v.y); atomicAdd(f + 2, v.z); atomicAdd(f + 3, v.w);
+  } else {
+    *p = v;
   }
-  *p = v;
 }
-
 template <int DEG, bool ACC>
 __device__ __forceinline__ void sh_backward(const float* __restrict__ sh, float* __restrict__ dsh, int M, bool vec4,
                                             float x, float y, float z, const float* g3, float* ddir) {
@@ -232,9 +233,10 @@ __device__ __forceinline__ void backward_one(const PreBwdArgs& a, const int i, c
     put<ACC>(a.dL_dcolors + 3 * (size_t)i + 2, g2.x);
   }
   // densification statistics of this view (gaussian_model.py:174-181, visible_mask = radii > 0)
-  if (a.max_radii2D) a.max_radii2D[i] = fmaxf(a.max_radii2D[i], (float)radius);
-  if (a.xyz_grad_accum) a.xyz_grad_accum[i] += sqrtf(dmx * dmx + dmy * dmy);
-  if (a.xyz_grad_count) a.xyz_grad_count[i] += 1.f;
+  // (atomics: concurrent views may update the same statistics; non-negative floats order like ints)
+  if (a.max_radii2D) atomicMax(reinterpret_cast<int*>(a.max_radii2D + i), __float_as_int((float)radius));
+  if (a.xyz_grad_accum) atomicAdd(a.xyz_grad_accum + i, sqrtf(dmx * dmx + dmy * dmy));
+  if (a.xyz_grad_count) atomicAdd(a.xyz_grad_count + i, 1.f);
 
   // SH
   if (sh_row) {
