@@ -430,8 +430,15 @@ def run_ours(args):
     for s in stages:
         s["share_of_kernel_time"] = s["ms_per_frame"] * s["calls"] / stage_sum
     dom = max(stages, key=lambda s: s["ms_per_frame"] * s["calls"])
+    traffic, traffic_src = None, None
+    tp = os.path.join(ROOT, "profiles", "r1_v3_traffic.json")      # dram bytes per launch from the ncu --set full capture
+    if os.path.exists(tp):
+        tj = json.load(open(tp))
+        ent = tj.get(dom["stage"] + "_kernel") or tj.get({"sort": "onesweep_pass_kernel"}.get(dom["stage"], ""))
+        if ent:
+            traffic, traffic_src = ent["dram_bytes_per_launch"], "profiles/r1_v3_traffic.json: " + tj.get("_source", "")
     roofline = {"kernel": dom["stage"], "bound": "hbm", "achieved": dom["GBps"], "peak": hbm_peak, "unit": "GB/s",
-                "frac": dom["hbm_frac"], "traffic": None, "peak_source": peak_src,
+                "frac": dom["hbm_frac"], "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": dom["algorithmic_bytes"], "ms_per_launch": dom["ms_per_frame"],
                 "note": "the compositing kernels are FP32-issue bound, not HBM bound: see stages[].TFLOPs_fp32"}
     fp32_peak = 148 * 128 * 2 * (clocks["sm_mhz"] or sm_max) * 1e6 / 1e12 if clocks else None
