@@ -1,0 +1,94 @@
+"""BASELINE.json sizes.  C2 (100k Gaussians, SH3, 800x800) is compared with the CPU oracle directly;
+C3 (1M Gaussians, SH3, 1920x1080) is checked through size-independent properties: sortedness and
+stability of the (key, value) list, ranges consistent with the keys, sum(tiles_touched) = R,
+n_contrib inside the tile's list, 0 <= final_T <= 1, and LINEARITY of the backward in the upstream
+gradient (the forward state is fixed, so grad(a g1 + b g2) = a grad(g1) + b grad(g2))."""
+import numpy as np
+import pytest
+import torch
+
+import gpu_utils as U
+from gaussian_splatting_lightning_b200 import synthetic
+
+pytestmark = pytest.mark.gpu
+
+
+def test_c2_matches_oracle(oracle_lib):
+    P, deg, W, H = synthetic.config("C2")
+    cam, arrays = U.synthetic_case(P, deg, W, H, seed=0)
+    ref = U.run_oracle_forward(cam, arrays)
+    out = U.run_cuda_forward(cam, arrays)
+    st = U.export(out)
+    assert np.array_equal(out["radii"].cpu().numpy(), ref["radii"])
+    assert np.array_equal(st["keys_sorted"].view(np.uint64), ref["keys"])
+    assert np.array_equal(st["vals_sorted"].view(np.uint32), ref["point_list"])
+    assert np.array_equal(st["ranges"].view(np.uint32), ref["ranges"])
+    frac, mx = U.close_fraction(out["color"].cpu().numpy(), ref["color"], 1e-4, 1e-4)
+    assert frac <= 2e-4 and mx <= 2e-2, (frac, mx)
+    rng = np.random.default_rng(3)
+    dC = rng.standard_normal((3, H, W)).astype(np.float32)
+    dD = rng.standard_normal((1, H, W)).astype(np.float32)
+    want = oracle_lib.backward(ref, dC, dD[0])
+    got = U.run_cuda_backward(out, dC, dD)
+    for k in ("dL_dmeans2D", "dL_dopacity", "dL_dmeans3D", "dL_dsh", "dL_dscales", "dL_drotations"):
+        w = want[k]
+        s = max(1.0, float(np.abs(w).max()))
+        frac, mx = U.close_fraction(got[k].reshape(w.shape) / s, w / s, 1e-4, 1e-3)
+        assert frac <= 2e-3 and mx <= 5e-2, (k, frac, mx)
+
+
+def test_c3_properties():
+    P, deg, W, H = synthetic.config("C3")
+    scene = synthetic.make_scene(P, deg, W, H, seed=0)
+    c = synthetic.make_camera(W, H, k=1, num_views=256)
+    import oracle
+    cam = oracle.Camera(H, W, c["tanfovx"], c["tanfovy"], c["viewmatrix"].numpy(), c["projmatrix"].numpy(),
+                        c["campos"].numpy(), sh_degree=deg, bg=np.array([0.2, 0.3, 0.4], np.float32))
+    arrays = {k: v.numpy() for k, v in scene.items()}
+    out = U.run_cuda_forward(cam, arrays)
+    from gaussian_splatting_lightning_b200.rasterizer import export_state
+    st = export_state(out["rs"], P, out["radii"], out["geom"], out["binning"], out["img"], out["R"], out["cap"])
+    R = out["R"]
+    keys, vals = st["keys_sorted"], st["vals_sorted"].long()
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    assert int(st["tiles_touched"].long().sum()) == R and int(st["point_offsets"][-1]) == R
+    assert bool(((st["tiles_touched"] > 0) == (out["radii"] > 0)).all())
+    assert bool((keys[1:] >= keys[:-1]).all())                               # sorted
+    same = keys[1:] == keys[:-1]
+    assert bool((vals[1:][same] > vals[:-1][same]).all())                     # stable: ties in Gaussian order
+    # every sorted instance is one of the Gaussian's own keys: depth bits = its z_view, tile inside the grid
+    assert bool(((keys & 0xFFFFFFFF) == st["depths"].view(torch.int32).long()[vals]).all())
+    tiles = keys >> 32
+    assert int(tiles.min()) >= 0 and int(tiles.max()) < T
+    # a permutation of the unsorted list (checksum of checksums)
+    ku = st["keys_unsorted"]
+    assert int(ku.sum()) == int(keys.sum()) and int((ku ^ (ku >> 7)).sum()) == int((keys ^ (keys >> 7)).sum())
+    assert int(st["vals_unsorted"].long().sum()) == int(vals.sum())
+    # ranges = boundaries of the tile ids
+    rg = st["ranges"].long()
+    counts = torch.bincount(tiles, minlength=T)
+    assert bool(((rg[:, 1] - rg[:, 0]) == counts).all())
+    nz = counts > 0
+    assert bool((rg[nz, 0] == (torch.cumsum(counts, 0) - counts)[nz]).all())
+    # per pixel: last contributor inside the tile's list, transmittance in [0, 1]
+    gy, gx = (H + 15) // 16, (W + 15) // 16
+    ys, xs = torch.meshgrid(torch.arange(H, device=U.DEV), torch.arange(W, device=U.DEV), indexing="ij")
+    per_pixel_len = counts[(ys // 16) * gx + xs // 16]
+    assert bool((st["n_contrib"].long() <= per_pixel_len).all())
+    fT = st["final_T"]
+    assert bool(((fT >= 0) & (fT <= 1)).all()) and bool(torch.isfinite(out["color"]).all())
+    assert bool((out["color"] >= -1e-6).all())
+
+    # linearity of the backward in (dL_dcolor, dL_dinvdepth)
+    g = torch.Generator(device="cpu").manual_seed(5)
+    g1c, g2c = torch.randn(3, H, W, generator=g).numpy(), torch.randn(3, H, W, generator=g).numpy()
+    g1d, g2d = torch.randn(1, H, W, generator=g).numpy(), torch.randn(1, H, W, generator=g).numpy()
+    a, b = 0.75, -1.5
+    G1 = U.run_cuda_backward(out, g1c, g1d)
+    G2 = U.run_cuda_backward(out, g2c, g2d)
+    G3 = U.run_cuda_backward(out, a * g1c + b * g2c, a * g1d + b * g2d)
+    for k in ("dL_dmeans3D", "dL_dsh", "dL_dopacity", "dL_dscales", "dL_drotations", "dL_dmeans2D"):
+        want = a * G1[k].astype(np.float64) + b * G2[k].astype(np.float64)
+        s = max(1.0, float(np.abs(want).max()))
+        err = np.abs(G3[k] - want) / s
+        assert float(err.max()) <= 2e-4, (k, float(err.max()))
