@@ -353,56 +353,93 @@ def run_ours(args):
                                c["host"]["campos"].reshape(-1), torch.zeros(3)]).pin_memory() for c in cams]
         loss_host = torch.zeros(vpr).pin_memory()
 
+        # .grad of the parameters = their slices of the step's flat gradient buffer: the backward kernel adds
+        # into it (accumulate_gradients_into), the one all-reduce sends it, FusedAdam would read it
+        from gaussian_splatting_lightning_b200.rasterizer import accumulate_gradients_into
+        from gaussian_splatting_lightning_b200.training import l1_loss, parameter_groups_on
+        parameter_groups_on(bufs, params)
         copy_stream = torch.cuda.Stream(device)
+        n_slots = args.streams + 1
         slots = [dict(cam=torch.empty(38, device=device), gt=torch.empty(3, H, W, device=device),
-                      ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
+                      ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(n_slots)]
 
         def upload(j):
-            """this step's host inputs of view j -> device, on the copy stream (double-buffered, the way a
-            prefetching data loader hands batches over); every byte is copied inside the timed region"""
-            sl = slots[j % 2]
+            """this step's host inputs of view j -> device, on the copy stream (a ring of streams+1 slots, the
+            way a prefetching data loader hands batches over); every byte is copied inside the timed region"""
+            sl = slots[j % n_slots]
             with torch.cuda.stream(copy_stream):
                 copy_stream.wait_event(sl["free"])           # the view that used this slot last is done with it
                 sl["cam"].copy_(cam_host[j], non_blocking=True)
                 sl["gt"].copy_(gt_host[j], non_blocking=True)
                 sl["ready"].record(copy_stream)
 
-        def e2e_step():
-            main = torch.cuda.current_stream()
-            for p_ in params.values():
-                p_.grad = None
-            for sl in slots:
-                sl["free"].record(main)
-            upload(0)
-            for j, c in enumerate(cams):
-                if j + 1 < vpr:
-                    upload(j + 1)                            # overlaps the rendering of view j
-                sl = slots[j % 2]
-                main.wait_event(sl["ready"])
-                cam_d, gt = sl["cam"], sl["gt"]
-                rs = c["settings"]._replace(viewmatrix=cam_d[0:16].view(4, 4), projmatrix=cam_d[16:32].view(4, 4),
-                                            campos=cam_d[32:35], bg=cam_d[35:38])
-                sp = torch.zeros_like(params["means3D"], requires_grad=True)
+        def e2e_view(j):
+            st = torch.cuda.current_stream()                 # ViewStreams.run: view j on stream j mod n
+            if j + n_slots - 1 < vpr:
+                upload(j + n_slots - 1)                      # its slot was freed by view j-1; overlaps the rendering
+            sl = slots[j % n_slots]
+            st.wait_event(sl["ready"])
+            cam_d, gt = sl["cam"], sl["gt"]
+            rs = cams[j]["settings"]._replace(viewmatrix=cam_d[0:16].view(4, 4), projmatrix=cam_d[16:32].view(4, 4),
+                                              campos=cam_d[32:35], bg=cam_d[35:38])
+            sp = torch.zeros_like(params["means3D"], requires_grad=True)
+            with accumulate_gradients_into(acc_into, stat_into):
                 color, radii, invd = GaussianRasterizer(rs)(
                     means3D=params["means3D"], means2D=sp, shs=params["shs"], colors_precomp=None,
                     opacities=params["opacities"], scales=params["scales"], rotations=params["rotations"],
                     cov3D_precomp=None)
-                loss = (color - gt).abs().mean()
-                loss.backward()
-                loss_host[j].copy_(loss.detach(), non_blocking=True)
-                sl["free"].record(main)
+            loss = l1_loss(color, gt)
+            loss.backward()
+            loss_host[j].copy_(loss.detach(), non_blocking=True)
+            sl["free"].record(st)
+
+        def e2e_step():
+            main = torch.cuda.current_stream()
+            bufs.zero_()
+            for j in range(min(n_slots - 1, vpr)):
+                upload(j)
+            vstreams.run(vpr, e2e_view)
             if world > 1:
-                for p_ in params.values():
-                    dist.all_reduce(p_.grad)
+                bufs.all_reduce()
             main.synchronize()                               # the step's result (losses) is on the host
             return float(loss_host.sum())
 
         ms_e2e, _, _ = timed(e2e_step, K, 2)
         h2d = vpr * (3 * H * W * 4 + 38 * 4)
         e2e = {"value": frames / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": vpr * 4,
-               "what": "GaussianRasterizer autograd API + L1 loss; per view: pinned GT image and camera H2D (copy stream, "
-                       "double-buffered, inside the timed region), loss D2H"}
-        del params
+               "what": "GaussianRasterizer autograd API + fused L1 loss (training.l1_loss) with fused gradient accumulation "
+                       "(accumulate_gradients_into) on the same CUDA streams as `value`; per view: pinned GT image and "
+                       "camera H2D (copy stream, ring of streams+1 slots, inside the timed region), loss D2H"}
+        # ---- the training-step neighbours of the path (SURVEY 8(f) rows 1-2), each one launch, HBM bound --------
+        from gaussian_splatting_lightning_b200.training import FusedAdam, densify_fold
+
+        def ev_ms(fn, reps=20):
+            for _ in range(3):
+                fn()
+            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(); a_.record()
+            for _ in range(reps):
+                fn()
+            b_.record(); torch.cuda.synchronize()
+            return a_.elapsed_time(b_) / reps
+
+        hbm_pk = peaks()[0]
+        opt = FusedAdam([{"params": [params[k]], "lr": lr} for k, lr in
+                         (("means3D", 1.6e-4), ("shs", 2.5e-3), ("opacities", 5e-2), ("scales", 5e-3), ("rotations", 1e-3))],
+                        lr=0.0, eps=1e-15)
+        n_par = sum(p_.numel() for p_ in params.values())
+        img_a, img_b = torch.rand(3, H, W, device=device, requires_grad=True), torch.rand(3, H, W, device=device)
+        run_stats = [torch.zeros(P, device=device) for _ in range(3)]
+        neighbours = []
+        for name, fn, nbytes in (
+                ("adam (6 groups, one launch, zero_grad fused)", lambda: opt.step(zero_grad=True), 32 * n_par),
+                ("l1_loss value + unit gradient", lambda: l1_loss(img_a, img_b), 12 * 3 * H * W),
+                ("densify_fold", lambda: densify_fold(bufs.max_radii, bufs.stats[0], bufs.stats[1], *run_stats), 32 * P)):
+            ms_ = ev_ms(fn)
+            neighbours.append({"kernel": name, "ms": ms_, "algorithmic_bytes": nbytes, "GBps": nbytes / (ms_ * 1e6),
+                               "hbm_frac": nbytes / (ms_ * 1e6) / hbm_pk})
+        e2e["neighbours"] = neighbours
+        del params, opt
 
     if rank != 0:
         if world > 1:

@@ -44,7 +44,14 @@ class GsrDensifyStats(C.Structure):
     _fields_ = [("max_radii2D", C.c_void_p), ("xyz_grad_accum", C.c_void_p), ("xyz_grad_count", C.c_void_p)]
 
 
+class GsrAdamGroup(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("n", C.c_int64), ("lr", C.c_double)]
+
+
 GSR_GRADS_ACCUMULATE = 1
+GSR_ADAM_MAX_GROUPS = 8
+GSR_ADAM_ZERO_GRAD = 1
 
 _EXPORT_FIELDS = ["depths", "means2D", "cov3D", "conic_opacity", "rgb", "clamped", "tiles_touched",
                   "point_offsets", "keys_unsorted", "vals_unsorted", "keys_sorted", "vals_sorted", "ranges",
@@ -61,7 +68,7 @@ EXPORTED_SYMBOLS = [
     "gsr_backward_scratch_bytes", "gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_export_state",
     "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count", "gsr_profile_enable", "gsr_profile_reset",
     "gsr_profile_collect", "gsr_profile_stage_count", "gsr_profile_stage_name", "gsr_profile_stage_ms",
-    "gsr_profile_stage_calls",
+    "gsr_profile_stage_calls", "gsr_l1_loss_scratch_bytes", "gsr_l1_loss", "gsr_adam_step", "gsr_densify_fold",
 ]
 
 _lib = None
@@ -109,6 +116,15 @@ def lib():
     L.gsr_sort_pairs.restype = C.c_int
     L.gsr_sort_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                  C.c_int32, C.c_void_p, C.c_void_p]
+    L.gsr_l1_loss_scratch_bytes.restype = C.c_size_t
+    L.gsr_l1_loss_scratch_bytes.argtypes = []
+    L.gsr_l1_loss.restype = C.c_int
+    L.gsr_l1_loss.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gsr_adam_step.restype = C.c_int
+    L.gsr_adam_step.argtypes = [C.POINTER(GsrAdamGroup), C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double,
+                                C.c_int32, C.c_void_p]
+    L.gsr_densify_fold.restype = C.c_int
+    L.gsr_densify_fold.argtypes = [C.c_int32] + [C.c_void_p] * 7
     L.gsr_profile_stage_name.restype = C.c_char_p
     L.gsr_profile_stage_ms.restype = C.c_double
     L.gsr_profile_stage_calls.restype = C.c_int64

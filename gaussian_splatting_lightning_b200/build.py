@@ -30,6 +30,8 @@ SOURCES = {
     "render_forward.cu": [],
     "render_backward.cu": [],
     "preprocess_backward.cu": ["-fmad=false"],
+    "loss.cu": [],
+    "optimizer.cu": ["-fmad=false"],
 }
 HEADERS = ["gsr_common.cuh", "gsr_math.cuh", "render_common.cuh", os.path.join("..", "..", "include", "gsr_b200.h")]
 

@@ -334,6 +334,42 @@ int gsr_export_state(const GsrSettings* settings, int32_t P, const int32_t* radi
   return GSR_OK;
 }
 
+size_t gsr_l1_loss_scratch_bytes(void) { return gsr::l1_scratch_bytes(); }
+
+int gsr_l1_loss(const float* image, const float* target, int64_t n, float* dL_dimage, float* out_loss, void* scratch,
+                void* stream) {
+  if (n <= 0 || !image || !target || !out_loss || !scratch) return fail(GSR_EINVAL, "l1_loss: bad arguments");
+  if ((((uintptr_t)image) | ((uintptr_t)target) | ((uintptr_t)dL_dimage) | ((uintptr_t)scratch)) & 15)
+    return fail(GSR_EINVAL, "l1_loss: image, target, dL_dimage and scratch must be 16-byte aligned");
+  GSR_CUDA(gsr::launch_l1_loss(image, target, (long long)n, dL_dimage, out_loss, scratch, (cudaStream_t)stream),
+           "l1_loss kernel");
+  return GSR_OK;
+}
+
+int gsr_adam_step(const GsrAdamGroup* groups, int32_t num_groups, int32_t step, double beta1, double beta2, double eps,
+                  int32_t flags, void* stream) {
+  if (!groups || num_groups < 0 || num_groups > GSR_ADAM_MAX_GROUPS || step < 1)
+    return fail(GSR_EINVAL, "adam_step: bad arguments (1..8 groups, step >= 1)");
+  if (!(beta1 >= 0.0 && beta1 < 1.0 && beta2 >= 0.0 && beta2 < 1.0)) return fail(GSR_EINVAL, "adam_step: betas outside [0,1)");
+  for (int i = 0; i < num_groups; ++i) {
+    const GsrAdamGroup& g = groups[i];
+    if (g.n < 0 || (g.n > 0 && (!g.param || !g.grad || !g.exp_avg || !g.exp_avg_sq)))
+      return fail(GSR_EINVAL, "adam_step: NULL pointer in a non-empty group");
+  }
+  GSR_CUDA(gsr::launch_adam(groups, num_groups, step, beta1, beta2, eps, (flags & GSR_ADAM_ZERO_GRAD) ? 1 : 0,
+                            (cudaStream_t)stream), "adam kernel");
+  return GSR_OK;
+}
+
+int gsr_densify_fold(int32_t P, const float* d_max_radii, const float* d_accum, const float* d_count,
+                     float* max_radii2D, float* xyz_grad_accum, float* xyz_grad_count, void* stream) {
+  if (P < 0 || (P > 0 && (!d_count || (max_radii2D && !d_max_radii) || (xyz_grad_accum && !d_accum))))
+    return fail(GSR_EINVAL, "densify_fold: bad arguments");
+  GSR_CUDA(gsr::launch_densify_fold(P, d_max_radii, d_accum, d_count, max_radii2D, xyz_grad_accum, xyz_grad_count,
+                                    (cudaStream_t)stream), "densify_fold kernel");
+  return GSR_OK;
+}
+
 size_t gsr_sort_workspace_bytes(int64_t n) {
   return gsr_sort::Workspace::carve(nullptr, n).bytes + 128;  // + the device-side element count
 }

@@ -249,4 +249,12 @@ cudaError_t launch_preprocess_backward(const GsrView& v, const GsrGaussiansDev& 
 cudaError_t launch_export_geom(int P, const int32_t* radii, const GeomState& geom, float* depths, float* means2D,
                                float* cov3D, float* conic_opacity, float* rgb, uint8_t* clamped,
                                uint32_t* tiles_touched, uint32_t* point_offsets, cudaStream_t s);
+// loss.cu / optimizer.cu
+size_t l1_scratch_bytes();
+cudaError_t launch_l1_loss(const float* image, const float* target, long long n, float* dL_dimage, float* out_loss,
+                           void* scratch, cudaStream_t s);
+cudaError_t launch_adam(const struct GsrAdamGroup* groups, int num_groups, int step, double beta1, double beta2,
+                        double eps, int zero_grad, cudaStream_t s);
+cudaError_t launch_densify_fold(int P, const float* d_max_radii, const float* d_accum, const float* d_count,
+                                float* max_radii2D, float* xyz_grad_accum, float* xyz_grad_count, cudaStream_t s);
 }  // namespace gsr

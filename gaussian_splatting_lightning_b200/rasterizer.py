@@ -10,9 +10,11 @@ The compute is libgsr_b200.so (hand-written sm_100a CUDA) reached through _nativ
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import math
 import os
+import threading
 from typing import NamedTuple, Optional
 
 import torch
@@ -179,10 +181,43 @@ def mark_visible(positions: torch.Tensor, viewmatrix: torch.Tensor, projmatrix: 
     return present.bool()
 
 
+class _Sink(threading.local):
+    grads = None
+    stats = None
+
+
+_sink = _Sink()
+
+
+@contextlib.contextmanager
+def accumulate_gradients_into(grads, stats=None):
+    """Fused gradient accumulation for the autograd API.
+
+    GaussianRasterizer calls made inside this context remember `grads` (name -> tensor, the names of
+    backward_raw's `accumulate_into`, e.g. view_parallel.StepBuffers.grads()) and `stats`
+    (StepBuffers.densify_stats()).  Their backward then ADDS the parameter gradients straight into
+    those tensors inside the preprocess-backward kernel (GSR_GRADS_ACCUMULATE) and updates the
+    densification statistics there, and hands autograd None for the inputs it covered -- so autograd
+    neither allocates per-view gradient tensors nor runs its own accumulation kernels.  Point
+    `param.grad` at the same tensors (training.parameter_groups_on) and the optimiser sees the sum over
+    the views.  The dummy means2D leaf still receives its gradient through autograd when it requires one.
+    """
+    prev = (_sink.grads, _sink.stats)
+    _sink.grads, _sink.stats = dict(grads), (dict(stats) if stats else None)
+    try:
+        yield
+    finally:
+        _sink.grads, _sink.stats = prev
+
+
+_SINK_INPUT = dict(dL_dmeans3D=0, dL_dsh=2, dL_dcolors=3, dL_dopacity=4, dL_dscales=5, dL_drotations=6, dL_dcov3D=7)
+
+
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                 raster_settings):
+        ctx.sink = (_sink.grads, _sink.stats) if _sink.grads is not None else None
         num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths, _cap = forward_raw(
             raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
         ctx.raster_settings = raster_settings
@@ -207,6 +242,27 @@ class _RasterizeGaussians(torch.autograd.Function):
                                 ("dL_dcolors", has_col and need[3]), ("dL_dopacity", need[4]),
                                 ("dL_dscales", has_scale and need[5]), ("dL_drotations", has_rot and need[6]),
                                 ("dL_dcov3D", has_cov and need[7])) if ok]
+        if ctx.sink is not None:
+            # fused accumulation (accumulate_gradients_into): wanted gradients the sink covers are added in
+            # place by the kernel; autograd gets None for them.  Anything else wanted is produced fresh
+            # (into a zeroed tensor, since the accumulate flag covers the whole call).
+            sink_grads, sink_stats = ctx.sink
+            P, M = means3D.shape[0], (sh.shape[1] if has_sh else 0)
+            shapes = dict(dL_dmeans2D=(P, 3), dL_dcolors=(P, 3), dL_dopacity=(P, 1), dL_dmeans3D=(P, 3),
+                          dL_dcov3D=(P, 6), dL_dsh=(P, M, 3), dL_dscales=(P, 3), dL_drotations=(P, 4))
+            acc, fresh = {}, {}
+            for n in want:
+                if n in sink_grads:
+                    acc[n] = sink_grads[n]
+                else:
+                    acc[n] = fresh[n] = torch.zeros(shapes[n], dtype=torch.float32, device=means3D.device)
+            backward_raw(ctx.raster_settings, means3D, radii, sh, colors_precomp, opacities, scales, rotations,
+                         cov3Ds_precomp, grad_out_color, grad_out_depth, geomBuffer, binningBuffer, imgBuffer,
+                         ctx.num_rendered, accumulate_into=acc, stats=sink_stats)
+            out = [None] * 9
+            for n, t in fresh.items():
+                out[1 if n == "dL_dmeans2D" else _SINK_INPUT[n]] = t
+            return tuple(out)
         (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
          dL_drotations) = backward_raw(ctx.raster_settings, means3D, radii, sh, colors_precomp, opacities, scales,
                                        rotations, cov3Ds_precomp, grad_out_color, grad_out_depth, geomBuffer,

@@ -1,0 +1,157 @@
+"""The two steps either side of the rasterizer in `GSLightningModule.training_step`,
+as hand-written sm_100a kernels of libgsr_b200.so behind the interfaces the reference uses:
+
+    l1_loss(image, target)      == nn.L1Loss()                 gs_lightning/lightning/gs_lightning_module.py:99,278
+    FusedAdam(param_groups,...) == torch.optim.Adam            gs_lightning_module.py:111-127, configs (eps 1e-15)
+    densify_fold(...)           == GaussianModel.update_max_radii2D / update_xyz_gradient over the views of a step
+                                                               gs_lightning/modules/gaussian_model.py:174-181
+
+CUDA only: CPU tensors raise, a missing library raises ImportError (no fallback).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Iterable, Optional
+
+import torch
+
+from . import _native as N
+
+
+def _need_cuda(t: torch.Tensor, what: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"{what}: gaussian_splatting_lightning_b200 runs on CUDA devices only (no CPU fallback)")
+
+
+class _L1Loss(torch.autograd.Function):
+    """mean |image - target|; value and unit gradient come out of ONE pass over the two images."""
+
+    @staticmethod
+    def forward(ctx, image, target):
+        _need_cuda(image, "l1_loss")
+        if image.shape != target.shape:
+            raise RuntimeError(f"l1_loss: shapes differ: {tuple(image.shape)} vs {tuple(target.shape)}")
+        dev = image.device
+        a, b = N.f32c(image), N.f32c(target, dev)
+        n = a.numel()
+        out = torch.empty((), dtype=torch.float32, device=dev)
+        want_grad = ctx.needs_input_grad[0]
+        unit = torch.empty_like(a) if want_grad else None
+        with torch.cuda.device(dev):
+            scratch = torch.zeros(N.lib().gsr_l1_loss_scratch_bytes(), dtype=torch.uint8, device=dev)
+            N.check(N.lib().gsr_l1_loss(N.ptr(a), N.ptr(b), n, N.ptr(unit), out.data_ptr(), N.ptr(scratch),
+                                        N.stream_ptr(dev)), "gsr_l1_loss")
+        ctx.unit = unit
+        ctx.shape = image.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        if ctx.unit is None:
+            return None, None
+        return (ctx.unit * grad_out).view(ctx.shape), None
+
+
+def l1_loss(image: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    """nn.L1Loss()(image, target) (reduction 'mean'); `target` gets no gradient."""
+    if image.numel() == 0:
+        raise RuntimeError("l1_loss: empty input")
+    return _L1Loss.apply(image, target.detach())
+
+
+def densify_fold(d_max_radii: torch.Tensor, d_accum: torch.Tensor, d_count: torch.Tensor,
+                 max_radii2D: Optional[torch.Tensor], xyz_grad_accum: Optional[torch.Tensor],
+                 xyz_grad_count: Optional[torch.Tensor]) -> None:
+    """Fold a step's statistics deltas (StepBuffers, after the exchange) into the model's running statistics
+    in one launch and without the host synchronisation boolean-mask indexing costs."""
+    _need_cuda(d_count, "densify_fold")
+    dev, P = d_count.device, d_count.numel()
+    for name, t in (("d_max_radii", d_max_radii), ("d_accum", d_accum), ("d_count", d_count),
+                    ("max_radii2D", max_radii2D), ("xyz_grad_accum", xyz_grad_accum),
+                    ("xyz_grad_count", xyz_grad_count)):
+        if t is not None and not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == P):
+            raise RuntimeError(f"densify_fold: {name} must be a contiguous float32 CUDA tensor of {P} elements")
+    with torch.cuda.device(dev):
+        N.check(N.lib().gsr_densify_fold(P, N.ptr(d_max_radii), N.ptr(d_accum), N.ptr(d_count), N.ptr(max_radii2D),
+                                         N.ptr(xyz_grad_accum), N.ptr(xyz_grad_count), N.stream_ptr(dev)),
+                "gsr_densify_fold")
+
+
+class FusedAdam(torch.optim.Optimizer):
+    """torch.optim.Adam (no weight decay, no amsgrad, not maximize) with every parameter group updated by ONE
+    kernel launch.  Same constructor arguments, `param_groups` (LR schedulers keep working:
+    GSWarmUpExponentialDecayScheduler rewrites group["lr"]) and per-parameter state names
+    (`step`, `exp_avg`, `exp_avg_sq`) as torch's, so state dicts are interchangeable.
+
+    step(zero_grad=True) also zeroes the gradients in the same pass (optimizer.zero_grad(set_to_none=False)):
+    with the gradients living in the flat all-reduce buffer (view_parallel.StepBuffers) that removes the
+    buffer's memset from the next step.
+    """
+
+    def __init__(self, params, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8):
+        if not 0.0 <= lr:
+            raise ValueError(f"Invalid learning rate: {lr}")
+        if not 0.0 <= eps:
+            raise ValueError(f"Invalid epsilon value: {eps}")
+        if not 0.0 <= betas[0] < 1.0:
+            raise ValueError(f"Invalid beta parameter at index 0: {betas[0]}")
+        if not 0.0 <= betas[1] < 1.0:
+            raise ValueError(f"Invalid beta parameter at index 1: {betas[1]}")
+        super().__init__(params, dict(lr=lr, betas=tuple(betas), eps=eps))
+
+    @torch.no_grad()
+    def step(self, closure=None, zero_grad: bool = False):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        # (device, betas, eps, step) -> list of (param, grad, exp_avg, exp_avg_sq, lr)
+        batches: Dict[tuple, list] = {}
+        for group in self.param_groups:
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                _need_cuda(p, "FusedAdam")
+                g = p.grad
+                if g.is_sparse:
+                    raise RuntimeError("FusedAdam does not support sparse gradients")
+                if not (p.dtype == torch.float32 and p.is_contiguous() and g.dtype == torch.float32
+                        and g.is_contiguous()):
+                    raise RuntimeError("FusedAdam needs contiguous float32 parameters and gradients")
+                st = self.state[p]
+                if len(st) == 0:
+                    st["step"] = 0
+                    st["exp_avg"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                    st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                st["step"] = int(st["step"]) + 1
+                key = (p.device, float(group["betas"][0]), float(group["betas"][1]), float(group["eps"]), st["step"])
+                batches.setdefault(key, []).append((p, g, st["exp_avg"], st["exp_avg_sq"], float(group["lr"])))
+        for (dev, b1, b2, eps, t), items in batches.items():
+            with torch.cuda.device(dev):
+                for i in range(0, len(items), N.GSR_ADAM_MAX_GROUPS):
+                    part = items[i:i + N.GSR_ADAM_MAX_GROUPS]
+                    arr = (N.GsrAdamGroup * len(part))(*[
+                        N.GsrAdamGroup(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), lr)
+                        for p, g, m, v, lr in part if p.numel() > 0])
+                    N.check(N.lib().gsr_adam_step(arr, len(arr), t, b1, b2, eps,
+                                                  N.GSR_ADAM_ZERO_GRAD if zero_grad else 0, N.stream_ptr(dev)),
+                            "gsr_adam_step")
+        return loss
+
+
+def parameter_groups_on(buffers, params: Dict[str, torch.Tensor]) -> None:
+    """Point `.grad` of the model's parameters at their slices of the step's flat gradient buffer
+    (view_parallel.StepBuffers), so that the rasterizer backward's fused `+=`, the one all-reduce and
+    FusedAdam all work on the same memory: no per-parameter gradient tensors, no pack pass.
+
+    params: name -> leaf tensor with names among means3D (P,3), shs (P,M,3) [or features_dc (P,1,3) +
+    features_rest (P,M-1,3) when the SH block is stored split, gaussian_model.py:317-330 -- not
+    representable as views of one (P,M,3) block, so only `shs` is accepted], opacities, scales, rotations.
+    """
+    names = dict(means3D="dL_dmeans3D", shs="dL_dsh", opacities="dL_dopacity", scales="dL_dscales",
+                 rotations="dL_drotations")
+    views = buffers.grads()
+    for k, p in params.items():
+        if k not in names:
+            raise KeyError(f"unknown parameter {k!r}; expected one of {sorted(names)}")
+        p.grad = views[names[k]].view(p.shape)

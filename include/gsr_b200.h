@@ -185,6 +185,41 @@ int gsr_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* k
                    uint32_t* vals_out, uint64_t* keys_tmp, uint32_t* vals_tmp, int64_t n,
                    int32_t end_bit, void* workspace, void* stream);
 
+/* ---- the steps on either side of the rasterizer in training_step ---- */
+
+/* nn.L1Loss() of gs_lightning/lightning/gs_lightning_module.py:99,278: *out_loss = mean(|image - target|)
+ * (device scalar) and, when dL_dimage is not NULL, the unit gradient sign(image - target) / n in the same
+ * pass.  image / target / dL_dimage: n contiguous floats, 16-byte aligned.  scratch:
+ * gsr_l1_loss_scratch_bytes() of device memory whose first 128 bytes are zero on first use (the kernel
+ * leaves them zero).  The sum is deterministic. */
+size_t gsr_l1_loss_scratch_bytes(void);
+int gsr_l1_loss(const float* image, const float* target, int64_t n, float* dL_dimage, float* out_loss,
+                void* scratch, void* stream);
+
+/* torch.optim.Adam over the parameter groups of gs_lightning_module.py:120-127 in ONE launch
+ * (configs/*.yaml: eps 1e-15, default betas, no weight decay, no amsgrad).  `step` is the 1-based step
+ * count after the increment, as torch uses it for the bias corrections; lr, betas and eps are doubles and are
+ * folded into the float32 kernel constants the way torch folds its Python scalars.  All pointers device. */
+#define GSR_ADAM_MAX_GROUPS 8
+#define GSR_ADAM_ZERO_GRAD 1 /* also zero the gradients (optimizer.zero_grad(), gs_lightning_module.py:168-170) */
+typedef struct GsrAdamGroup {
+  float* param;       /* (n) updated in place                                   */
+  float* grad;        /* (n) read; zeroed with GSR_ADAM_ZERO_GRAD               */
+  float* exp_avg;     /* (n) first moment, updated in place                     */
+  float* exp_avg_sq;  /* (n) second moment, updated in place                    */
+  int64_t n;
+  double lr;          /* the group's learning rate of this step                 */
+} GsrAdamGroup;
+int gsr_adam_step(const GsrAdamGroup* groups, int32_t num_groups, int32_t step, double beta1, double beta2,
+                  double eps, int32_t flags, void* stream);
+
+/* Folds the statistics deltas of one step (GsrDensifyStats buffers the backward filled, summed / maxed over
+ * the ranks) into the model's running statistics, gs_lightning/modules/gaussian_model.py:174-181: where
+ * d_count > 0:  max_radii2D = max(., d_max_radii); xyz_grad_accum += d_accum; xyz_grad_count += d_count.
+ * The three outputs may be NULL. */
+int gsr_densify_fold(int32_t P, const float* d_max_radii, const float* d_accum, const float* d_count,
+                     float* max_radii2D, float* xyz_grad_accum, float* xyz_grad_count, void* stream);
+
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 int64_t gsr_launch_count(void);
 
