@@ -10,23 +10,28 @@
 // accumulated behind the current splat.
 //
 // Design (what differs from a per-pixel-atomics kernel):
-//   * same CTA/warp/pixel mapping and batch staging as the forward kernel; the per-warp hit
-//     words the forward wrote say which list entries touched the warp's 8x4 pixels, so only
-//     those (warp, splat) pairs are replayed and no culling test is evaluated here;
+//   * same CTA/warp/pixel mapping and batch staging as the forward kernel: 4 warps per tile, a warp owns an
+//     8x8 block, a lane the pixels A and B of one column four rows apart, and all per-pixel arithmetic runs
+//     on packed pairs {A, B} (FFMA2 / FMUL2 / FADD2, render_common.cuh) -- the second pixel costs no extra
+//     issue slots for the FP32 work.  The hit words the forward wrote per 8x4 sub-tile say which list entries
+//     touched it; the warp replays the UNION of its two sub-tiles' words and evaluates no culling test
+//     (a pixel the entry does not reach recomputes alpha < 1/255 bit for bit and contributes exact zeros);
 //   * per (pixel, splat) the kernel produces ten RAW sums instead of the ten finished partial
 //     derivatives: with h = opacity * G * dL/dalpha,
 //         S0 = h dx, S1 = h dy, S2 = h dx^2, S3 = h dx dy, S4 = h dy^2, S5 = G dL/dalpha,
 //         S6..8 = w dL/dC_rgb, S9 = w dL/d(1/z)                       (w = alpha * T)
 //     -- everything that multiplies these by per-Gaussian constants (conic, W/2, H/2, -1/2) is
 //     applied once per Gaussian in the preprocess backward kernel, not once per pixel here;
+//   * the loop carries -T, -alpha and -(accumulated colour) (no packed negation exists): every product and FMA
+//     is the exact negation of the textbook one, so the sums are bit-identical to a positive-sign evaluation;
 //   * lanes whose pixel the splat does not reach run the same instruction stream with
 //     alpha = 0 (an exact no-op of the recurrences), so the hit loop has no divergent branch;
-//   * the ten sums are reduced over the warp's 32 pixels with a recursive-halving exchange: at
-//     each xor-shuffle step a lane keeps half of its values and sends the other half, so the
-//     reduction costs 5+3+2+1+1 = 12 shuffles instead of 50, and ends with the ten sums spread
+//   * a lane first adds its two pixels' sums; the ten sums are then reduced over the warp's 32 lanes with a
+//     recursive-halving exchange: at each xor-shuffle step a lane keeps half of its values and sends the other
+//     half, so the reduction costs 5+3+2+1+1 = 12 shuffles instead of 50, and ends with the ten sums spread
 //     over ten lanes;
 //   * those ten lanes issue ONE red.global.add.f32 instruction per (warp, splat) into a
-//     48-byte-per-Gaussian accumulator row -- 1/32 of the atomics of the per-pixel scheme.
+//     48-byte-per-Gaussian accumulator row -- 1/64 of the atomics of the per-pixel scheme.
 #include "gsr_common.cuh"
 #include "render_common.cuh"
 
@@ -58,21 +63,22 @@ __device__ __forceinline__ int reduce10_slot(int lane) {
 
 }  // namespace
 
-__global__ void __launch_bounds__(256) render_backward_kernel(
+__global__ void __launch_bounds__(128) render_backward_kernel(
     const GsrView v, const uint2* __restrict__ ranges, const char* __restrict__ binning,
     const GsrRec* __restrict__ recs, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
     const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth, float* __restrict__ grad_acc) {
-  __shared__ float4 sRec[3][256];  // staged batch, planes as described in render_common.cuh
-  __shared__ uint32_t sHit[8][8];  // [chunk of the batch][warp]
-  __shared__ uint32_t s_warp_max[8];
+  __shared__ float4 sRec[GSR_REC_PLANES][256];  // staged batch, planes as described in render_common.cuh
+  __shared__ uint32_t sHit[8][8];               // [chunk of the batch][sub-tile column]
+  __shared__ uint32_t s_warp_max[4];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
   const int tx = tile % v.gx, ty = tile / v.gx;
-  const int sx0 = tx * GSR_TILE + (warp & 1) * 8, sy0 = ty * GSR_TILE + (warp >> 1) * 4;
-  const int pxi = sx0 + (lane & 7), pyi = sy0 + (lane >> 3);
-  const bool inside = pxi < v.W && pyi < v.H;
-  const float pxf = (float)pxi, pyf = (float)pyi;
+  const int sx0 = tx * GSR_TILE + (warp & 1) * 8, sy0 = ty * GSR_TILE + (warp >> 1) * 8;
+  const int pxi = sx0 + (lane & 7), pyA = sy0 + (lane >> 3), pyB = pyA + 4;
+  const bool insideA = pxi < v.W && pyA < v.H, insideB = pxi < v.W && pyB < v.H;
+  const float pxf = (float)pxi;
+  const int colA = (warp >> 1) * 4 + (warp & 1), colB = colA + 2;
   const uint2 range = ranges[tile];
   const int slot = reduce10_slot(lane);
   const bool b16 = lane & 16, b8 = lane & 8, b4 = lane & 4, b2 = lane & 2;
@@ -85,97 +91,192 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
   const uint32_t* __restrict__ hits = reinterpret_cast<const uint32_t*>(binning + gsr_bin_hits_off(cap));
   const uint32_t* __restrict__ hit_rows = hits + hit_slot(range.x, (uint32_t)tile, 0) * 8;
 
-  float T_final = 0.f, dp0 = 0.f, dp1 = 0.f, dp2 = 0.f, dinv = 0.f;
-  uint32_t last = 0;
-  if (inside) {
-    const size_t HW = (size_t)v.H * v.W;
-    const size_t pid = (size_t)pyi * v.W + pxi;
-    T_final = final_T[pid];
-    last = n_contrib[pid];
-    dp0 = dL_dpix[pid]; dp1 = dL_dpix[HW + pid]; dp2 = dL_dpix[2 * HW + pid];
-    if (dL_dinvdepth) dinv = dL_dinvdepth[pid];
+  const size_t HW = (size_t)v.H * v.W;
+  float TfA = 0.f, TfB = 0.f, dpA[4] = {0.f, 0.f, 0.f, 0.f}, dpB[4] = {0.f, 0.f, 0.f, 0.f};
+  uint32_t lastA = 0, lastB = 0;
+  if (insideA) {
+    const size_t pid = (size_t)pyA * v.W + pxi;
+    TfA = final_T[pid];
+    lastA = n_contrib[pid];
+    dpA[0] = dL_dpix[pid]; dpA[1] = dL_dpix[HW + pid]; dpA[2] = dL_dpix[2 * HW + pid];
+    if (dL_dinvdepth) dpA[3] = dL_dinvdepth[pid];
+  }
+  if (insideB) {
+    const size_t pid = (size_t)pyB * v.W + pxi;
+    TfB = final_T[pid];
+    lastB = n_contrib[pid];
+    dpB[0] = dL_dpix[pid]; dpB[1] = dL_dpix[HW + pid]; dpB[2] = dL_dpix[2 * HW + pid];
+    if (dL_dinvdepth) dpB[3] = dL_dinvdepth[pid];
   }
   const float* __restrict__ bg = v.bg;
-  const float Tf_bg = T_final * (bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2);
+  // per-pixel state and constants, {A, B} (ptxas keeps each pair in an aligned 64-bit register so that the packed
+  // path uses them in place)
+  const float dp0A = dpA[0], dp1A = dpA[1], dp2A = dpA[2], dp3A = dpA[3];
+  const float dp0B = dpB[0], dp1B = dpB[1], dp2B = dpB[2], dp3B = dpB[3];
+  const float TfbgA = TfA * (bg[0] * dp0A + bg[1] * dp1A + bg[2] * dp2A);
+  const float TfbgB = TfB * (bg[0] * dp0B + bg[1] * dp1B + bg[2] * dp2B);
+  const float npyA = -(float)pyA, npyB = -(float)pyB;
 
-  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, last);
+  const uint32_t warp_last = __reduce_max_sync(0xffffffffu, max(lastA, lastB));
   if (lane == 0) s_warp_max[warp] = warp_last;
   __syncthreads();
   uint32_t max_last = 0;
 #pragma unroll
-  for (int w = 0; w < 8; ++w) max_last = max(max_last, s_warp_max[w]);
+  for (int w = 0; w < 4; ++w) max_last = max(max_last, s_warp_max[w]);
   if (max_last == 0) return;
 
-  float T = T_final;
-  float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, ar3 = 0.f;  // colour / inverse depth accumulated behind the splat
+  float nTA = -TfA, nTB = -TfB;                                  // -T
+  float nar0A = 0.f, nar1A = 0.f, nar2A = 0.f, nar3A = 0.f;      // -(colour / inverse depth accumulated behind the splat)
+  float nar0B = 0.f, nar1B = 0.f, nar2B = 0.f, nar3B = 0.f;
+
+// one pixel of the lane against the splat just loaded (scalar path: the entry is in one sub-tile's hit word only)
+#define GSR_BWD_ONE(S)                                                                                   \
+  {                                                                                                      \
+    const float dy = my + npy##S;                                                                        \
+    float e = __fmaf_rn(__fmul_rn(hC, dy), dy, tt);                                                      \
+    e = __fmaf_rn(vv, dy, e);                                                                            \
+    const float G = ex2_approx(-e);                                                                      \
+    float na = fmaxf(__fmul_rn(no, G), -0.99f);                                                          \
+    const bool valid = (idx < last##S) && !(e < 0.f) && (na <= -1.f / 255.f);                            \
+    na = valid ? na : 0.f;                                                                               \
+    const float rcp = rcp_approx(1.f + na);                                                              \
+    nT##S *= rcp;                                                                                        \
+    const float w = na * nT##S;                                                                          \
+    const float d0 = cr + nar0##S, d1 = cg + nar1##S, d2 = cb + nar2##S, d3 = iz + nar3##S;              \
+    float dL = d0 * dp0##S;                                                                              \
+    dL = fmaf(d1, dp1##S, dL);                                                                           \
+    dL = fmaf(d2, dp2##S, dL);                                                                           \
+    dL = fmaf(d3, dp3##S, dL);                                                                           \
+    dL = fmaf(dL, nT##S, Tfbg##S * rcp);                                                                 \
+    nar0##S = fmaf(na, d0, nar0##S);                                                                     \
+    nar1##S = fmaf(na, d1, nar1##S);                                                                     \
+    nar2##S = fmaf(na, d2, nar2##S);                                                                     \
+    nar3##S = fmaf(na, d3, nar3##S);                                                                     \
+    const float n5 = valid ? G * dL : 0.f;                                                               \
+    const float h = no * n5;                                                                             \
+    s0 = h * dx; s1 = h * dy;                                                                            \
+    s2 = s0 * dx; s3 = s0 * dy; s4 = s1 * dy;                                                            \
+    s5 = -n5;                                                                                            \
+    s6 = w * dp0##S; s7 = w * dp1##S; s8 = w * dp2##S; s9 = w * dp3##S;                                  \
+  }
 
   const int nb = ((int)max_last + 255) / 256;
   for (int b = nb - 1; b >= 0; --b) {
     const int base = b * 256;
     const int cnt = min(256, (int)max_last - base);
     __syncthreads();
-    if (tid < cnt) {
-      const uint32_t g = point_list[range.x + base + tid];
-      const GsrRec* r = recs + g;
-      float4 a = r->a, bq = r->b, c = r->c;
-      a.z *= GSR_HALF_LOG2E; a.w *= GSR_LOG2E; bq.x *= GSR_HALF_LOG2E;
-      c.w = __uint_as_float(g);
-      sRec[0][tid] = a; sRec[1][tid] = bq; sRec[2][tid] = c;
+#pragma unroll
+    for (int j = tid; j < 256; j += 128) {
+      if (j < cnt) {
+        const uint32_t g = point_list[range.x + base + j];
+        const GsrRec* r = recs + g;
+        float hA, hB, hC, tau2;
+        stage_record(sRec, j, r->a, r->b, r->c, g, hA, hB, hC, tau2);
+      }
     }
     if (tid < 64 && (tid >> 3) * 32 < cnt) sHit[tid >> 3][tid & 7] = hit_rows[(size_t)((base >> 5) + (tid >> 3)) * 8 + (tid & 7)];
     __syncthreads();
     if ((int)warp_last <= base) continue;  // nothing in this batch reaches the warp's pixels
 
     for (int c0 = ((min(cnt, (int)warp_last - base) - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
-      uint32_t mask = sHit[c0 >> 5][warp];
+      const uint32_t maskA = sHit[c0 >> 5][colA], maskB = sHit[c0 >> 5][colB];
+      uint32_t mask = maskA | maskB;
+      const uint32_t both = maskA & maskB;
       while (mask) {
         const int bit = msb_index(mask);
-        mask ^= 1u << bit;
+        const uint32_t bitm = 1u << bit;
+        mask ^= bitm;
         const int j = c0 + bit;
+        const uint32_t idx = (uint32_t)(base + j);
         const uint32_t addr = aRec + (uint32_t)j * 16u;
-        const float4 a = lds128<0>(addr);
-        const float4 bq = lds128<GSR_PLANE>(addr);
-        const float2 c = lds64<2 * GSR_PLANE>(addr);
-        const float dx = a.x - pxf, dy = a.y - pyf;
-        const float e = quad_form(a.z, a.w, bq.x, dx, dy);
-        const float G = ex2_approx(-e);
-        const float alpha_raw = splat_alpha(bq.y, G);
-        const bool valid = ((uint32_t)(base + j) < last) && !(e < 0.f) && (alpha_raw >= 1.f / 255.f);
-        const float alpha = valid ? alpha_raw : 0.f;
+        f32x2 q0, my2, q1, hC2, no2, r2, g2, bl2, iz2, idw;
+        lds2x64<0>(addr, q0, my2);
+        lds2x64<GSR_PLANE>(addr, q1, hC2);
+        lds2x64<2 * GSR_PLANE>(addr, no2, r2);
+        lds2x64<3 * GSR_PLANE>(addr, g2, bl2);
+        lds2x64<4 * GSR_PLANE>(addr, iz2, idw);
+        float mx, hA, hB, unused;
+        upk2(q0, mx, hA);
+        upk2(q1, hB, unused);
+        const float dx = mx - pxf;
+        const float tt = __fmul_rn(__fmul_rn(hA, dx), dx);
+        const float vv = __fmul_rn(hB, dx);
+        float s0, s1, s2, s3, s4, s5, s6, s7, s8, s9;
+        if (both & bitm) {
+          // packed path: both pixels in one instruction stream
+          const f32x2 dx2 = pk2(dx, dx);
+          const f32x2 dy2 = add2(my2, pk2(npyA, npyB));
+          f32x2 e2 = fma2(mul2(hC2, dy2), dy2, pk2(tt, tt));
+          e2 = fma2(pk2(vv, vv), dy2, e2);
+          float eA, eB;
+          upk2(e2, eA, eB);
+          const f32x2 G2 = pk2(ex2_approx(-eA), ex2_approx(-eB));
+          float naA, naB;
+          upk2(mul2(no2, G2), naA, naB);
+          naA = fmaxf(naA, -0.99f);
+          naB = fmaxf(naB, -0.99f);
+          const bool validA = (idx < lastA) && !(eA < 0.f) && (naA <= -1.f / 255.f);
+          const bool validB = (idx < lastB) && !(eB < 0.f) && (naB <= -1.f / 255.f);
+          const f32x2 na2 = pk2(validA ? naA : 0.f, validB ? naB : 0.f);   // -alpha, 0 where the splat does not reach
 
-        const float rcp = rcp_approx(1.f - alpha);
-        T *= rcp;
-        const float w = alpha * T;
-        // ar = colour / inverse depth accumulated BEHIND this splat (all farther splats folded in)
-        const float d0 = bq.z - ar0, d1 = bq.w - ar1, d2 = c.x - ar2, d3 = c.y - ar3;
-        float dLda = d0 * dp0;
-        dLda = fmaf(d1, dp1, dLda);
-        dLda = fmaf(d2, dp2, dLda);
-        dLda = fmaf(d3, dinv, dLda);
-        dLda = fmaf(dLda, T, -Tf_bg * rcp);
-        // fold this splat in for the next (nearer) one: ar <- alpha c + (1 - alpha) ar
-        ar0 = fmaf(alpha, d0, ar0);
-        ar1 = fmaf(alpha, d1, ar1);
-        ar2 = fmaf(alpha, d2, ar2);
-        ar3 = fmaf(alpha, d3, ar3);
+          float omA, omB;
+          upk2(add2(pk2(1.f, 1.f), na2), omA, omB);                         // 1 - alpha
+          const f32x2 rcp2 = pk2(rcp_approx(omA), rcp_approx(omB));
+          const f32x2 nT2 = mul2(pk2(nTA, nTB), rcp2);                      // -T in front of this splat
+          upk2(nT2, nTA, nTB);
+          const f32x2 w2 = mul2(na2, nT2);                                  // alpha T
+          // d = colour - (colour accumulated BEHIND this splat)
+          const f32x2 d0 = add2(r2, pk2(nar0A, nar0B)), d1 = add2(g2, pk2(nar1A, nar1B)),
+                      d2 = add2(bl2, pk2(nar2A, nar2B)), d3 = add2(iz2, pk2(nar3A, nar3B));
+          const f32x2 dp0 = pk2(dp0A, dp0B), dp1 = pk2(dp1A, dp1B), dp2 = pk2(dp2A, dp2B), dp3 = pk2(dp3A, dp3B);
+          f32x2 dL = mul2(d0, dp0);
+          dL = fma2(d1, dp1, dL);
+          dL = fma2(d2, dp2, dL);
+          dL = fma2(d3, dp3, dL);
+          dL = fma2(dL, nT2, mul2(pk2(TfbgA, TfbgB), rcp2));                // -(dL/dalpha)
+          // fold this splat in for the next (nearer) one: -ar <- -(alpha c + (1 - alpha) ar)
+          upk2(fma2(na2, d0, pk2(nar0A, nar0B)), nar0A, nar0B);
+          upk2(fma2(na2, d1, pk2(nar1A, nar1B)), nar1A, nar1B);
+          upk2(fma2(na2, d2, pk2(nar2A, nar2B)), nar2A, nar2B);
+          upk2(fma2(na2, d3, pk2(nar3A, nar3B)), nar3A, nar3B);
 
-        const float s5 = valid ? G * dLda : 0.f;
-        const float h = bq.y * s5;
-        const float s0 = h * dx, s1 = h * dy;
-        const float s2 = s0 * dx, s3 = s0 * dy, s4 = s1 * dy;
-        const float s6 = w * dp0, s7 = w * dp1, s8 = w * dp2, s9 = w * dinv;
+          float n5A, n5B;
+          upk2(mul2(G2, dL), n5A, n5B);                                     // -(G dL/dalpha)
+          const f32x2 n5 = pk2(validA ? n5A : 0.f, validB ? n5B : 0.f);
+          const f32x2 h2 = mul2(no2, n5);                                   // opacity G dL/dalpha
+          const f32x2 p0 = mul2(h2, dx2), p1 = mul2(h2, dy2);
+          const f32x2 p2 = mul2(p0, dx2), p3 = mul2(p0, dy2), p4 = mul2(p1, dy2);
+          const f32x2 p6 = mul2(w2, dp0), p7 = mul2(w2, dp1), p8 = mul2(w2, dp2), p9 = mul2(w2, dp3);
+          // the lane's two pixels first
+          float lo, hi;
+          upk2(p0, lo, hi); s0 = lo + hi;
+          upk2(p1, lo, hi); s1 = lo + hi;
+          upk2(p2, lo, hi); s2 = lo + hi;
+          upk2(p3, lo, hi); s3 = lo + hi;
+          upk2(p4, lo, hi); s4 = lo + hi;
+          upk2(n5, lo, hi); s5 = -lo - hi;
+          upk2(p6, lo, hi); s6 = lo + hi;
+          upk2(p7, lo, hi); s7 = lo + hi;
+          upk2(p8, lo, hi); s8 = lo + hi;
+          upk2(p9, lo, hi); s9 = lo + hi;
+        } else {
+          float my, hC, no, cr, cg, cb, iz;
+          upk2(my2, my, unused); upk2(hC2, hC, unused); upk2(no2, no, unused); upk2(r2, cr, unused);
+          upk2(g2, cg, unused); upk2(bl2, cb, unused); upk2(iz2, iz, unused);
+          if (maskA & bitm) GSR_BWD_ONE(A) else GSR_BWD_ONE(B)
+        }
 
-        // recursive-halving reduction of the ten sums over the 32 pixels
-        float w0, w1, w2, w3, w4;
+        // recursive-halving reduction of the ten sums over the 32 lanes
+        float w0, w1, w2r, w3, w4;
         GSR_XCHG(w0, s0, s5, b16, 16);
         GSR_XCHG(w1, s1, s6, b16, 16);
-        GSR_XCHG(w2, s2, s7, b16, 16);
+        GSR_XCHG(w2r, s2, s7, b16, 16);
         GSR_XCHG(w3, s3, s8, b16, 16);
         GSR_XCHG(w4, s4, s9, b16, 16);
         float u0, u1, u2;
         GSR_XCHG(u0, w0, w3, b8, 8);
         GSR_XCHG(u1, w1, w4, b8, 8);
-        GSR_XCHG(u2, w2, 0.f, b8, 8);
+        GSR_XCHG(u2, w2r, 0.f, b8, 8);
         float t0, t1;
         GSR_XCHG(t0, u0, u2, b4, 4);
         GSR_XCHG(t1, u1, 0.f, b4, 4);
@@ -183,12 +284,14 @@ __global__ void __launch_bounds__(256) render_backward_kernel(
         GSR_XCHG(sum, t0, t1, b2, 2);
         sum += __shfl_xor_sync(0xffffffffu, sum, 1);
         if (slot >= 0) {
-          const uint32_t g = lds32u<2 * GSR_PLANE + 12>(addr);
-          atomicAdd(grad_acc + (size_t)g * 12 + slot, sum);
+          float idf, pad;
+          upk2(idw, idf, pad);
+          atomicAdd(grad_acc + (size_t)__float_as_uint(idf) * 12 + slot, sum);
         }
       }
     }
   }
+#undef GSR_BWD_ONE
 }
 
 cudaError_t launch_render_backward(const GsrView& v, const uint2* ranges, const void* binning, const GsrRec* recs,
@@ -196,7 +299,7 @@ cudaError_t launch_render_backward(const GsrView& v, const uint2* ranges, const 
                                    const float* dL_dinvdepth, float* grad_acc, cudaStream_t s) {
   const int tiles = v.gx * v.gy;
   if (tiles <= 0) return cudaSuccess;
-  render_backward_kernel<<<tiles, 256, 0, s>>>(v, ranges, (const char*)binning, recs, final_T, n_contrib, dL_dpix,
+  render_backward_kernel<<<tiles, 128, 0, s>>>(v, ranges, (const char*)binning, recs, final_T, n_contrib, dL_dpix,
                                                dL_dinvdepth, grad_acc);
   count_launch();
   return cudaGetLastError();

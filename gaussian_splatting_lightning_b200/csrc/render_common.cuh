@@ -76,10 +76,68 @@ __device__ __forceinline__ int msb_index(uint32_t x) {
   return r;
 }
 
-// Staged batch: three planes of 256 float4, plane p of entry j at byte offset p*4096 + j*16.
-//   plane 0 {mean.x, mean.y, hA, hB}   plane 1 {hC, opacity, r, g}   plane 2 {b, 1/z, tau2, bits(gaussian id)}
-//   forward only: plane 3 = cull plane (make_cull_plane)
+// ---- packed FP32 pairs (sm_100a FFMA2 / FMUL2 / FADD2) ------------------------------------------
+// A lane of the compositing kernels owns TWO pixels of the same column, four rows apart (the 8x4 sub-tiles
+// A and B of its warp's 8x8 block), and keeps everything per-pixel as a packed pair {A, B} in a 64-bit
+// register.  One FFMA2 does the FMA of both pixels in ONE issue slot (same FP32-pipe time as two FFMAs:
+// tools/ubench/ffma2.cu measured 73.9 vs 71.5 TFLOP/s), and these kernels are issue bound.  Each half is
+// rounded exactly like the scalar instruction, so results are bit-identical to the one-pixel-per-lane code.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// two 64-bit halves of one 16-byte shared-memory word
+template <int OFF>
+__device__ __forceinline__ void lds2x64(uint32_t addr, f32x2& lo, f32x2& hi) {
+  asm volatile("ld.shared.v2.b64 {%0,%1}, [%2+%3];" : "=l"(lo), "=l"(hi) : "r"(addr), "n"(OFF));
+}
+template <int OFF>
+__device__ __forceinline__ f32x2 lds1x64(uint32_t addr) {
+  f32x2 v;
+  asm volatile("ld.shared.b64 %0, [%1+%2];" : "=l"(v) : "r"(addr), "n"(OFF));
+  return v;
+}
+
+// Staged batch: planes of 256 float4, plane p of entry j at byte offset p*4096 + j*16.  Values a packed
+// instruction needs for both pixels are stored twice, so that one 64-bit half of a 128-bit shared load IS the
+// broadcast pair (no MOVs in the hit loop); opacity is stored negated because the loops carry -alpha and -T
+// (T (1 - alpha) = fma(-T, -alpha, -T) negated, alpha T = (-alpha)(-T): exact, and no packed negation exists).
+//   plane 0 {mean.x, hA, mean.y, mean.y}   plane 1 {hB, tau2, hC, hC}   plane 2 {-o, -o, r, r}
+//   plane 3 {g, g, b, b}                    plane 4 {1/z, 1/z, bits(gaussian id), 0}
+//   forward only: plane 5 = cull plane (make_cull_plane)
 #define GSR_PLANE 4096
+#define GSR_REC_PLANES 5
+
+// a, b, c: the GsrRec words {mean2D.xy, conic.A, conic.B}, {conic.C, opacity, r, g}, {b, 1/z, tau, z}
+__device__ __forceinline__ void stage_record(float4 (*sRec)[256], int j, const float4 a, const float4 b, const float4 c,
+                                             uint32_t gid, float& hA, float& hB, float& hC, float& tau2) {
+  hA = a.z * GSR_HALF_LOG2E; hB = a.w * GSR_LOG2E; hC = b.x * GSR_HALF_LOG2E; tau2 = c.z * GSR_LOG2E;
+  sRec[0][j] = make_float4(a.x, hA, a.y, a.y);
+  sRec[1][j] = make_float4(hB, tau2, hC, hC);
+  sRec[2][j] = make_float4(-b.y, -b.y, b.z, b.z);
+  sRec[3][j] = make_float4(b.w, b.w, c.x, c.x);
+  sRec[4][j] = make_float4(c.y, c.y, __uint_as_float(gid), 0.f);
+}
 
 // e = hA dx^2 + hC dy^2 + hB dx dy with a FIXED rounding sequence: the forward and the backward
 // kernel must agree bit for bit on alpha (the backward replays the forward's accept/reject

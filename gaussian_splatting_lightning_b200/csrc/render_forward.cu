@@ -10,30 +10,32 @@
 // out = C + T * bg, inverse depth D, final_T, n_contrib (1-based index of the last splat used).
 //
 // Design:
-//   * one CTA per tile, 8 warps; warp w owns the 8x4 pixel sub-tile (w&1, w>>1) so that a warp's
-//     pixels are spatially compact;
-//   * the tile's list is consumed in batches of 256: each thread gathers one packed 48-byte
-//     GsrRec (three 128-bit loads, L2-resident at 1M Gaussians) and stages it in shared memory
-//     with the quadratic form pre-scaled into the log2 domain (render_common.cuh), so that the
-//     inner loop is 6 FP32 ops + one MUFU.EX2 per (pixel, splat);
-//   * sub-tile culling: before touching a batch, each lane tests ONE splat of the batch
-//     against the warp's 8x4 pixel rectangle (exact minimum of the quadratic form over the
-//     rectangle vs. tau2 = log2(255 * opacity), conservative margin) and a ballot turns the 32
-//     answers into a bit mask; the warp then iterates only over set bits.  A splat rejected
-//     here has alpha < 1/255 on every pixel of the sub-tile, so results are identical to the
-//     unculled loop while most (pixel, splat) pairs are never evaluated;
-//   * the hit loop is branch-free per lane (predicated updates);
-//   * for every chunk of 32 list entries the warp records which entries contributed to at
-//     least one of its pixels (one 32-bit "hit word" per warp and chunk, 1 byte per list entry
-//     in total): the backward kernel replays exactly those and needs no culling test;
-//   * warp ballots retire a warp as soon as its 32 pixels are saturated; the CTA leaves the
+//   * one CTA (4 warps) per tile; warp w owns the 8x8 pixel block (w&1, w>>1) and every lane TWO pixels of one
+//     column, four rows apart: pixel A in the block's upper 8x4 sub-tile, pixel B in the lower one.  All
+//     per-pixel arithmetic runs on packed pairs {A, B} (FFMA2 / FMUL2 / FADD2, render_common.cuh): the second
+//     pixel costs no extra issue slots for the FP32 work, and these kernels are issue bound;
+//   * the tile's list is consumed in batches of 256: each thread gathers two packed 48-byte GsrRec (three
+//     128-bit loads each, L2-resident at 1M Gaussians) and stages them in shared memory with the quadratic
+//     form pre-scaled into the log2 domain and the per-pixel operands duplicated (render_common.cuh), so that
+//     the inner loop is 8 FP32 issue slots + two MUFU.EX2 per (pixel pair, splat);
+//   * sub-tile culling: before touching a chunk of 32 entries, each lane tests ONE splat against each of
+//     the warp's two 8x4 rectangles (exact minimum of the quadratic form over the rectangle vs.
+//     tau2 = log2(255 * opacity), conservative margin) and two ballots turn the answers into bit masks; the
+//     warp iterates over the UNION of the two masks.  A splat rejected for a sub-tile has alpha < 1/255 on
+//     every pixel of it, so evaluating it there anyway (when the other sub-tile needs it) changes nothing;
+//   * the hit loop is branch-free per lane (predicated updates); it carries -T and -alpha (see
+//     render_common.cuh) -- every product and FMA is the exact negation of the textbook one;
+//   * for every chunk of 32 list entries and each 8x4 sub-tile the warp records which entries contributed to
+//     at least one of the sub-tile's pixels (one 32-bit "hit word" per sub-tile and chunk): the backward
+//     kernel replays exactly those and needs no culling test;
+//   * warp ballots retire a warp as soon as its 64 pixels are saturated; the CTA leaves the
 //     list when __syncthreads_and says every pixel is done.
 #include "gsr_common.cuh"
 #include "render_common.cuh"
 
 namespace gsr {
 
-__global__ void __launch_bounds__(256) render_forward_kernel(const GsrView v, const uint2* __restrict__ ranges,
+__global__ void __launch_bounds__(128) render_forward_kernel(const GsrView v, const uint2* __restrict__ ranges,
                                                              const uint32_t* __restrict__ point_list,
                                                              const GsrRec* __restrict__ recs,
                                                              float* __restrict__ out_color,
@@ -41,86 +43,172 @@ __global__ void __launch_bounds__(256) render_forward_kernel(const GsrView v, co
                                                              float* __restrict__ final_T,
                                                              uint32_t* __restrict__ n_contrib,
                                                              uint32_t* __restrict__ hits) {
-  __shared__ float4 sRec[4][256];  // staged batch, planes as described in render_common.cuh (3 = cull plane)
+  __shared__ float4 sRec[GSR_REC_PLANES + 1][256];  // staged batch (render_common.cuh); last plane = cull plane
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
   const int tx = tile % v.gx, ty = tile / v.gx;
-  // warp -> 8x4 sub-tile, lane -> pixel inside it
-  const int sx0 = tx * GSR_TILE + (warp & 1) * 8, sy0 = ty * GSR_TILE + (warp >> 1) * 4;
-  const int pxi = sx0 + (lane & 7), pyi = sy0 + (lane >> 3);
-  const bool inside = pxi < v.W && pyi < v.H;
-  const float pxf = (float)pxi, pyf = (float)pyi;
-  const SubTile st = make_subtile(sx0, sy0, v.W, v.H);
+  // warp -> 8x8 block = sub-tiles A (upper 8x4) and B (lower 8x4); lane -> one pixel in each
+  const int sx0 = tx * GSR_TILE + (warp & 1) * 8, sy0 = ty * GSR_TILE + (warp >> 1) * 8;
+  const int pxi = sx0 + (lane & 7), pyA = sy0 + (lane >> 3), pyB = pyA + 4;
+  const bool insideA = pxi < v.W && pyA < v.H, insideB = pxi < v.W && pyB < v.H;
+  const float pxf = (float)pxi;
+  const SubTile stA = make_subtile(sx0, sy0, v.W, v.H), stB = make_subtile(sx0, sy0 + 4, v.W, v.H);
   const uint32_t aRec = (uint32_t)__cvta_generic_to_shared(sRec);
+  // hit-word columns of the two sub-tiles (8 per chunk: sub-tile (x, y) of the tile at column 2y + x)
+  const int colA = (warp >> 1) * 4 + (warp & 1), colB = colA + 2;
 
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
-  uint32_t* __restrict__ hit_row = hits + hit_slot(range.x, (uint32_t)tile, 0) * 8 + warp;
+  uint32_t* __restrict__ hit_row = hits + hit_slot(range.x, (uint32_t)tile, 0) * 8;
 
-  float T = 1.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
-  uint32_t last = 0;
-  bool done = !inside;
+  // per-pixel state, {A, B}; ptxas keeps each pair in an aligned 64-bit register so that the packed path below
+  // uses them in place.  thr = the alpha floor of the pixel, -inf once the pixel is saturated (or outside).
+  const float NEG_INF = __int_as_float(0xff800000);
+  float nTA = -1.f, nTB = -1.f;                 // -T
+  float c0A = 0.f, c0B = 0.f, c1A = 0.f, c1B = 0.f, c2A = 0.f, c2B = 0.f, dA = 0.f, dB = 0.f;
+  float thrA = insideA ? -1.f / 255.f : NEG_INF, thrB = insideB ? -1.f / 255.f : NEG_INF;
+  uint32_t lastA = 0, lastB = 0;
+  const float npyA = -(float)pyA, npyB = -(float)pyB;
 
-  for (int base = 0; base < n; base += 256) {
-    if (__syncthreads_and(done)) break;
-    const int cnt = min(256, n - base);
-    if (tid < cnt) {
-      const uint32_t g = point_list[range.x + base + tid];
-      const GsrRec* r = recs + g;
-      float4 a = r->a, b = r->b, c = r->c;
-      a.z *= GSR_HALF_LOG2E; a.w *= GSR_LOG2E; b.x *= GSR_HALF_LOG2E; c.z *= GSR_LOG2E;
-      sRec[0][tid] = a; sRec[1][tid] = b; sRec[2][tid] = c;
-      sRec[3][tid] = make_cull_plane(a.z, a.w, b.x, c.z);
-    } else {
-      sRec[3][tid] = make_float4(0.f, 0.f, __int_as_float(0xff800000), 0.f);  // padding: never a hit
-    }
-    __syncthreads();
-    if (__all_sync(0xffffffffu, done)) continue;  // whole warp saturated: only keep the barriers
-
-    for (int c0 = 0; c0 < cnt; c0 += 32) {
-      // one splat per lane against the warp's sub-tile
-      const bool hit = subtile_may_contribute(sRec[0][c0 + lane], sRec[1][c0 + lane].x, sRec[3][c0 + lane], st);
-      uint32_t mask = __ballot_sync(0xffffffffu, hit);
-      uint32_t used = 0;
-      while (mask) {
-        const int bit = __ffs(mask) - 1;
-        mask &= mask - 1;
-        const uint32_t addr = aRec + (uint32_t)(c0 + bit) * 16u;
-        const float4 a = lds128<0>(addr);
-        const float4 b = lds128<GSR_PLANE>(addr);
-        const float2 c = lds64<2 * GSR_PLANE>(addr);
-        const float dx = a.x - pxf, dy = a.y - pyf;
-        const float e = quad_form(a.z, a.w, b.x, dx, dy);
-        const float alpha = splat_alpha(b.y, ex2_approx(-e));
-        const float test_T = __fmaf_rn(-T, alpha, T);
-        bool ok = !(e < 0.f) && (alpha >= 1.f / 255.f) && !done;
-        done = done || (ok && test_T < 0.0001f);
-        ok = ok && !(test_T < 0.0001f);
-        const float w = ok ? alpha * T : 0.f;
-        C0 = fmaf(b.z, w, C0);
-        C1 = fmaf(b.w, w, C1);
-        C2 = fmaf(c.x, w, C2);
-        D = fmaf(c.y, w, D);
-        T = ok ? test_T : T;
-        last = ok ? (uint32_t)(base + c0 + bit + 1) : last;
-        if (__any_sync(0xffffffffu, ok)) used |= 1u << bit;
-      }
-      if (lane == 0) hit_row[(size_t)((base + c0) >> 5) * 8] = used;
-      if (__all_sync(0xffffffffu, done)) break;
-    }
+// one pixel of the lane against the splat just loaded (scalar path: the splat reaches only one sub-tile)
+#define GSR_FWD_ONE(S)                                                                      \
+  {                                                                                         \
+    const float dy = my + npy##S;                                                           \
+    float e = __fmaf_rn(__fmul_rn(hC, dy), dy, tt);                                         \
+    e = __fmaf_rn(vv, dy, e);                                                               \
+    const float na = fmaxf(__fmul_rn(no, ex2_approx(-e)), -0.99f);                          \
+    const float test = __fmaf_rn(nT##S, na, nT##S);                                         \
+    bool ok = !(e < 0.f) && (na <= thr##S);                                                 \
+    const bool sat = test > -0.0001f;                                                       \
+    thr##S = (ok && sat) ? NEG_INF : thr##S;                                                \
+    ok = ok && !sat;                                                                        \
+    const float w = ok ? __fmul_rn(na, nT##S) : 0.f;                                        \
+    c0##S = fmaf(cr, w, c0##S);                                                             \
+    c1##S = fmaf(cg, w, c1##S);                                                             \
+    c2##S = fmaf(cb, w, c2##S);                                                             \
+    d##S = fmaf(iz, w, d##S);                                                               \
+    nT##S = ok ? test : nT##S;                                                              \
+    ok##S##_bits |= ok ? bitm : 0u;                                                         \
   }
 
-  if (inside) {
-    const size_t HW = (size_t)v.H * v.W;
-    const size_t pid = (size_t)pyi * v.W + pxi;
-    const float* __restrict__ bg = v.bg;
+  for (int base = 0; base < n; base += 256) {
+    if (__syncthreads_and(thrA == NEG_INF && thrB == NEG_INF)) break;
+    const int cnt = min(256, n - base);
+#pragma unroll
+    for (int j = tid; j < 256; j += 128) {
+      if (j < cnt) {
+        const uint32_t g = point_list[range.x + base + j];
+        const GsrRec* r = recs + g;
+        float hA, hB, hC, tau2;
+        stage_record(sRec, j, r->a, r->b, r->c, g, hA, hB, hC, tau2);
+        sRec[GSR_REC_PLANES][j] = make_cull_plane(hA, hB, hC, tau2);
+      } else {
+        sRec[GSR_REC_PLANES][j] = make_float4(0.f, 0.f, NEG_INF, 0.f);  // padding: never a hit
+      }
+    }
+    __syncthreads();
+    if (__all_sync(0xffffffffu, thrA == NEG_INF && thrB == NEG_INF)) continue;  // warp saturated: only the barriers
+
+    for (int c0 = 0; c0 < cnt; c0 += 32) {
+      // one splat per lane against the warp's two sub-tiles
+      const float4 p0 = sRec[0][c0 + lane], p1 = sRec[1][c0 + lane], cull = sRec[GSR_REC_PLANES][c0 + lane];
+      const float4 geo = make_float4(p0.x, p0.z, p0.y, p1.x);  // {mean.x, mean.y, hA, hB}
+      const bool allA = __all_sync(0xffffffffu, thrA == NEG_INF), allB = __all_sync(0xffffffffu, thrB == NEG_INF);
+      if (allA && allB) break;
+      const uint32_t maskA = __ballot_sync(0xffffffffu, !allA && subtile_may_contribute(geo, p1.z, cull, stA));
+      const uint32_t maskB = __ballot_sync(0xffffffffu, !allB && subtile_may_contribute(geo, p1.z, cull, stB));
+      uint32_t mask = maskA | maskB;
+      const uint32_t both = maskA & maskB;
+      uint32_t okA_bits = 0, okB_bits = 0;  // per lane: entries of the chunk that contributed to pixel A / B
+      while (mask) {
+        const int bit = __ffs(mask) - 1;
+        const uint32_t bitm = mask & (0u - mask);
+        mask ^= bitm;
+        const uint32_t addr = aRec + (uint32_t)(c0 + bit) * 16u;
+        f32x2 q0, my2, q1, hC2, no2, r2, g2, bl2;
+        lds2x64<0>(addr, q0, my2);
+        lds2x64<GSR_PLANE>(addr, q1, hC2);
+        lds2x64<2 * GSR_PLANE>(addr, no2, r2);
+        lds2x64<3 * GSR_PLANE>(addr, g2, bl2);
+        const f32x2 iz2 = lds1x64<4 * GSR_PLANE>(addr);
+        float mx, hA, hB, unused, my, hC, no, cr, cg, cb, iz;
+        upk2(q0, mx, hA);
+        upk2(q1, hB, unused);
+        // e = hA dx^2 + hC dy^2 + hB dx dy, per pixel exactly quad_form()'s rounding sequence
+        const float dx = mx - pxf;
+        const float tt = __fmul_rn(__fmul_rn(hA, dx), dx);
+        const float vv = __fmul_rn(hB, dx);
+        if (both & bitm) {
+          // packed path: both pixels in one instruction stream
+          const f32x2 dy2 = add2(my2, pk2(npyA, npyB));
+          f32x2 e2 = fma2(mul2(hC2, dy2), dy2, pk2(tt, tt));
+          e2 = fma2(pk2(vv, vv), dy2, e2);
+          float eA, eB;
+          upk2(e2, eA, eB);
+          float naA, naB;
+          upk2(mul2(no2, pk2(ex2_approx(-eA), ex2_approx(-eB))), naA, naB);   // (-opacity) G
+          naA = fmaxf(naA, -0.99f);
+          naB = fmaxf(naB, -0.99f);
+          const f32x2 na2 = pk2(naA, naB), nT2 = pk2(nTA, nTB);
+          float tA, tB, wA, wB;
+          upk2(fma2(nT2, na2, nT2), tA, tB);        // -(T (1 - alpha))
+          upk2(mul2(na2, nT2), wA, wB);             // alpha T
+          bool okA = !(eA < 0.f) && (naA <= thrA);
+          bool okB = !(eB < 0.f) && (naB <= thrB);
+          const bool satA = tA > -0.0001f, satB = tB > -0.0001f;   // T (1 - alpha) < 1e-4: stop BEFORE this splat
+          thrA = (okA && satA) ? NEG_INF : thrA;
+          thrB = (okB && satB) ? NEG_INF : thrB;
+          okA = okA && !satA;
+          okB = okB && !satB;
+          const f32x2 w2 = pk2(okA ? wA : 0.f, okB ? wB : 0.f);
+          upk2(fma2(r2, w2, pk2(c0A, c0B)), c0A, c0B);
+          upk2(fma2(g2, w2, pk2(c1A, c1B)), c1A, c1B);
+          upk2(fma2(bl2, w2, pk2(c2A, c2B)), c2A, c2B);
+          upk2(fma2(iz2, w2, pk2(dA, dB)), dA, dB);
+          nTA = okA ? tA : nTA;
+          nTB = okB ? tB : nTB;
+          okA_bits |= okA ? bitm : 0u;
+          okB_bits |= okB ? bitm : 0u;
+        } else {
+          upk2(my2, my, unused); upk2(hC2, hC, unused); upk2(no2, no, unused); upk2(r2, cr, unused);
+          upk2(g2, cg, unused); upk2(bl2, cb, unused); upk2(iz2, iz, unused);
+          if (maskA & bitm) GSR_FWD_ONE(A) else GSR_FWD_ONE(B)
+        }
+      }
+      const uint32_t usedA = __reduce_or_sync(0xffffffffu, okA_bits), usedB = __reduce_or_sync(0xffffffffu, okB_bits);
+      if (lane == 0) {
+        uint32_t* row = hit_row + (size_t)((base + c0) >> 5) * 8;
+        row[colA] = usedA;
+        row[colB] = usedB;
+      }
+      if (okA_bits) lastA = (uint32_t)(base + c0 + msb_index(okA_bits) + 1);
+      if (okB_bits) lastB = (uint32_t)(base + c0 + msb_index(okB_bits) + 1);
+    }
+  }
+#undef GSR_FWD_ONE
+
+  const size_t HW = (size_t)v.H * v.W;
+  const float* __restrict__ bg = v.bg;
+  if (insideA) {
+    const size_t pid = (size_t)pyA * v.W + pxi;
+    const float T = -nTA;
     final_T[pid] = T;
-    n_contrib[pid] = last;
-    out_color[pid] = fmaf(T, bg[0], C0);
-    out_color[HW + pid] = fmaf(T, bg[1], C1);
-    out_color[2 * HW + pid] = fmaf(T, bg[2], C2);
-    out_invdepth[pid] = D;
+    n_contrib[pid] = lastA;
+    out_color[pid] = fmaf(T, bg[0], c0A);
+    out_color[HW + pid] = fmaf(T, bg[1], c1A);
+    out_color[2 * HW + pid] = fmaf(T, bg[2], c2A);
+    out_invdepth[pid] = dA;
+  }
+  if (insideB) {
+    const size_t pid = (size_t)pyB * v.W + pxi;
+    const float T = -nTB;
+    final_T[pid] = T;
+    n_contrib[pid] = lastB;
+    out_color[pid] = fmaf(T, bg[0], c0B);
+    out_color[HW + pid] = fmaf(T, bg[1], c1B);
+    out_color[2 * HW + pid] = fmaf(T, bg[2], c2B);
+    out_invdepth[pid] = dB;
   }
 }
 
@@ -129,7 +217,7 @@ cudaError_t launch_render_forward(const GsrView& v, const uint2* ranges, const u
                                   uint32_t* n_contrib, uint32_t* hits, cudaStream_t s) {
   const int tiles = v.gx * v.gy;
   if (tiles <= 0) return cudaSuccess;
-  render_forward_kernel<<<tiles, 256, 0, s>>>(v, ranges, point_list, recs, out_color, out_invdepth, final_T,
+  render_forward_kernel<<<tiles, 128, 0, s>>>(v, ranges, point_list, recs, out_color, out_invdepth, final_T,
                                               n_contrib, hits);
   count_launch();
   return cudaGetLastError();

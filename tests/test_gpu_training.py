@@ -170,7 +170,8 @@ def test_fused_gradient_accumulation_equals_autograd_accumulation():
         assert float((a - b).abs().max()) <= 2e-5 * s, k       # same kernels; only the summation order differs
     mr, ac, ct = torch.zeros(P, device=U.DEV), torch.zeros(P, device=U.DEV), torch.zeros(P, device=U.DEV)
     for sp_f, sp, radii in zip(spa, spb, rb):
-        assert torch.equal(sp_f.grad, sp.grad)                  # the dummy means2D leaf still gets its gradient
+        # the dummy means2D leaf still gets its gradient (two runs differ by the order of the L2 reductions)
+        assert float((sp_f.grad - sp.grad).abs().max()) <= 2e-5 * float(sp.grad.abs().max())
         vis = radii > 0
         mr[vis] = torch.max(mr[vis], radii[vis].float())
         ac[vis] += torch.norm(sp.grad[vis, :2], dim=1)
