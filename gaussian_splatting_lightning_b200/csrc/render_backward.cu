@@ -63,7 +63,7 @@ __device__ __forceinline__ int reduce10_slot(int lane) {
 
 }  // namespace
 
-__global__ void __launch_bounds__(128) render_backward_kernel(
+__global__ void __launch_bounds__(128, 8) render_backward_kernel(
     const GsrView v, const uint2* __restrict__ ranges, const char* __restrict__ binning,
     const GsrRec* __restrict__ recs, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
     const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth, float* __restrict__ grad_acc) {

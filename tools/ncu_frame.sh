@@ -1,0 +1,14 @@
+#!/bin/bash
+# ncu captures of ONE frame of the C3 workload on the GPU box (run via gpurun, after the plain command exited 0).
+#   tools/ncu_frame.sh <tag>   ->  gpurun_out/<tag>_launches.csv, gpurun_out/<tag>_full.ncu-rep, gpurun_out/<tag>_full_raw.csv
+set -u
+TAG=${1:-r1}
+CMD="python bench.py --steps 2 --warmup 3 --views-per-rank 2 --streams 1 --no-e2e --no-cpu-baseline"
+mkdir -p gpurun_out
+$CMD > gpurun_out/${TAG}_plain.json 2> gpurun_out/${TAG}_plain.err || { echo "plain run failed"; tail -5 gpurun_out/${TAG}_plain.err; exit 1; }
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1
+# one frame = 13 launches (preprocess, scan, duplicate, 6 sort passes, ranges, render fwd, render bwd, preprocess bwd);
+# skip the warm-up frames and capture the kernels of one whole frame with the full set
+ncu --set full --clock-control none --import-source on --launch-skip 130 -c 13 -f -o gpurun_out/${TAG}_full $CMD > gpurun_out/${TAG}_ncu2.log 2>&1
+ncu -i gpurun_out/${TAG}_full.ncu-rep --page raw --csv > gpurun_out/${TAG}_full_raw.csv 2>/dev/null
+tail -3 gpurun_out/${TAG}_ncu2.log
