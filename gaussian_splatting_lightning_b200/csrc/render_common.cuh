@@ -109,12 +109,12 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
 // two 64-bit halves of one 16-byte shared-memory word
 template <int OFF>
 __device__ __forceinline__ void lds2x64(uint32_t addr, f32x2& lo, f32x2& hi) {
-  asm volatile("ld.shared.v2.b64 {%0,%1}, [%2+%3];" : "=l"(lo), "=l"(hi) : "r"(addr), "n"(OFF));
+  asm volatile("ld.shared.v2.b64 {%0,%1}, [%2+%3];" : "=l"(lo), "=l"(hi) : "r"(addr), "n"(OFF) : "memory");
 }
 template <int OFF>
 __device__ __forceinline__ f32x2 lds1x64(uint32_t addr) {
   f32x2 v;
-  asm volatile("ld.shared.b64 %0, [%1+%2];" : "=l"(v) : "r"(addr), "n"(OFF));
+  asm volatile("ld.shared.b64 %0, [%1+%2];" : "=l"(v) : "r"(addr), "n"(OFF) : "memory");
   return v;
 }
 

@@ -104,7 +104,11 @@ __global__ void __launch_bounds__(128) render_forward_kernel(const GsrView v, co
         stage_record(sRec, j, r->a, r->b, r->c, g, hA, hB, hC, tau2);
         sRec[GSR_REC_PLANES][j] = make_cull_plane(hA, hB, hC, tau2);
       } else {
-        sRec[GSR_REC_PLANES][j] = make_float4(0.f, 0.f, NEG_INF, 0.f);  // padding: never a hit
+        // padding: never a hit.  The geometry planes the culling test reads are zeroed too: stale shared memory
+        // (another kernel's data) may hold -inf / NaN patterns, and -inf <= -inf would let a padded entry pass.
+        sRec[0][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        sRec[1][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        sRec[GSR_REC_PLANES][j] = make_float4(0.f, 0.f, NEG_INF, 0.f);
       }
     }
     __syncthreads();
