@@ -438,6 +438,27 @@ def run_ours(args):
             ms_ = ev_ms(fn)
             neighbours.append({"kernel": name, "ms": ms_, "algorithmic_bytes": nbytes, "GBps": nbytes / (ms_ * 1e6),
                                "hbm_frac": nbytes / (ms_ * 1e6) / hbm_pk})
+        # fused SSIM (value + gradient, one launch) next to the reference's own CUDA kernels (oracle/_ref, compiled from
+        # /root/reference/submodules/fused-ssim by oracle/build_ref.py) on the same image pair: fusedssim + fusedssim_backward
+        from gaussian_splatting_lightning_b200.training import fused_ssim
+        im_a, im_b = img_a.detach()[None].clone().requires_grad_(True), img_b[None]
+        ms_ = ev_ms(lambda: fused_ssim(im_a, im_b))
+        ent = {"kernel": "fused_ssim value + gradient (one launch)", "ms": ms_, "algorithmic_bytes": 12 * 3 * H * W,
+               "GBps": 12 * 3 * H * W / (ms_ * 1e6), "hbm_frac": 12 * 3 * H * W / (ms_ * 1e6) / hbm_pk}
+        try:
+            from oracle import build_ref
+            if build_ref.available():
+                ref_mod = build_ref.load()
+                dmap = torch.full_like(im_b, 1.0 / im_b.numel())
+
+                def ref_ssim():
+                    _m, d1, d2, d3 = ref_mod.fusedssim(0.01 ** 2, 0.03 ** 2, im_a.detach(), im_b, True)
+                    ref_mod.fusedssim_backward(0.01 ** 2, 0.03 ** 2, im_a.detach(), im_b, dmap, d1, d2, d3)
+                ent["reference_cuda_ms"] = ev_ms(ref_ssim)
+                ent["reference"] = "submodules/fused-ssim fusedssim + fusedssim_backward (oracle/_ref), same GPU"
+        except Exception as ex:  # the checker is optional on the box
+            ent["reference"] = f"unavailable: {ex}"
+        neighbours.append(ent)
         e2e["neighbours"] = neighbours
         del params, opt
 

@@ -68,7 +68,8 @@ EXPORTED_SYMBOLS = [
     "gsr_backward_scratch_bytes", "gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_export_state",
     "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count", "gsr_profile_enable", "gsr_profile_reset",
     "gsr_profile_collect", "gsr_profile_stage_count", "gsr_profile_stage_name", "gsr_profile_stage_ms",
-    "gsr_profile_stage_calls", "gsr_l1_loss_scratch_bytes", "gsr_l1_loss", "gsr_adam_step", "gsr_densify_fold",
+    "gsr_profile_stage_calls", "gsr_l1_loss_scratch_bytes", "gsr_l1_loss", "gsr_adam_step", "gsr_densify_fold", "gsr_fused_ssim_scratch_bytes",
+    "gsr_fused_ssim",
 ]
 
 _lib = None
@@ -120,6 +121,11 @@ def lib():
     L.gsr_l1_loss_scratch_bytes.argtypes = []
     L.gsr_l1_loss.restype = C.c_int
     L.gsr_l1_loss.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gsr_fused_ssim_scratch_bytes.restype = C.c_size_t
+    L.gsr_fused_ssim_scratch_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int32]
+    L.gsr_fused_ssim.restype = C.c_int
+    L.gsr_fused_ssim.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float,
+                                 C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.gsr_adam_step.restype = C.c_int
     L.gsr_adam_step.argtypes = [C.POINTER(GsrAdamGroup), C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double,
                                 C.c_int32, C.c_void_p]

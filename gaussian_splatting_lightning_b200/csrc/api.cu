@@ -346,6 +346,20 @@ int gsr_l1_loss(const float* image, const float* target, int64_t n, float* dL_di
   return GSR_OK;
 }
 
+size_t gsr_fused_ssim_scratch_bytes(int32_t planes, int32_t H, int32_t W) { return gsr::ssim_scratch_bytes(planes, H, W); }
+
+int gsr_fused_ssim(const float* img1, const float* img2, int32_t planes, int32_t H, int32_t W, float C1, float C2,
+                   int32_t padding_valid, float* dL_dimg1, float* out_ssim, void* scratch, void* stream) {
+  if (planes <= 0 || H <= 0 || W <= 0 || !img1 || !img2 || !out_ssim || !scratch)
+    return fail(GSR_EINVAL, "fused_ssim: bad arguments");
+  if (planes > 65535) return fail(GSR_ELIMIT, "fused_ssim: more than 65535 image planes");
+  if (padding_valid && (H <= 10 || W <= 10)) return fail(GSR_EINVAL, "fused_ssim: padding 'valid' needs H, W > 10");
+  if (((uintptr_t)scratch) & 15) return fail(GSR_EINVAL, "fused_ssim: scratch must be 16-byte aligned");
+  GSR_CUDA(gsr::launch_fused_ssim(img1, img2, planes, H, W, C1, C2, padding_valid ? 1 : 0, dL_dimg1, out_ssim, scratch,
+                                  (cudaStream_t)stream), "fused_ssim kernel");
+  return GSR_OK;
+}
+
 int gsr_adam_step(const GsrAdamGroup* groups, int32_t num_groups, int32_t step, double beta1, double beta2, double eps,
                   int32_t flags, void* stream) {
   if (!groups || num_groups < 0 || num_groups > GSR_ADAM_MAX_GROUPS || step < 1)

@@ -253,6 +253,9 @@ cudaError_t launch_export_geom(int P, const int32_t* radii, const GeomState& geo
 size_t l1_scratch_bytes();
 cudaError_t launch_l1_loss(const float* image, const float* target, long long n, float* dL_dimage, float* out_loss,
                            void* scratch, cudaStream_t s);
+size_t ssim_scratch_bytes(int planes, int H, int W);
+cudaError_t launch_fused_ssim(const float* img1, const float* img2, int planes, int H, int W, float C1, float C2,
+                              int valid, float* dL_dimg1, float* out_mean, void* scratch, cudaStream_t s);
 cudaError_t launch_adam(const struct GsrAdamGroup* groups, int num_groups, int step, double beta1, double beta2,
                         double eps, int zero_grad, cudaStream_t s);
 cudaError_t launch_densify_fold(int P, const float* d_max_radii, const float* d_accum, const float* d_count,

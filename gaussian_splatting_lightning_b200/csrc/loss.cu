@@ -101,3 +101,215 @@ cudaError_t launch_l1_loss(const float* image, const float* target, long long n,
   return cudaGetLastError();
 }
 }  // namespace gsr
+
+// ---- fused SSIM: value + gradient in ONE kernel ----------------------------------------------------------
+// Reference: submodules/fused-ssim (ssim.cu:187-366 fusedssimCUDA / fusedssim_backwardCUDA, fused_ssim/__init__.py:8-41),
+// used as `1 - fused_ssim(rendered, gt)` at gs_lightning/lightning/gs_lightning_module.py:100,279.
+//
+//   mu1 = g*x, mu2 = g*y, s11 = g*(x x) - mu1^2, s22 = g*(y y) - mu2^2, s12 = g*(x y) - mu1 mu2     (g: 11x11 Gaussian,
+//   A = mu1^2 + mu2^2 + C1, B = s11 + s22 + C2, C = 2 mu1 mu2 + C1, D = 2 s12 + C2, m = C D / (A B)   sigma 1.5, zero pad)
+//   ssim = mean(m)  over the image ("same") or over the image minus a 5-pixel border ("valid")
+//   d ssim / d x = g*(w dm/dmu1) + 2 x g*(w dm/ds11) + y g*(w dm/ds12),  w = 1/N inside the averaged region, else 0
+//
+// The reference runs two kernels with three full-size derivative maps in between (28 B/element written, 32 read, plus
+// four memsets).  Here a CTA recomputes the derivative maps on its tile + 5-pixel halo from the images on a 10-pixel
+// halo, all in shared memory: HBM traffic is the two images in and the gradient out, 12 B/element, one launch.
+namespace {
+
+constexpr int SS_TX = 32, SS_TY = 32, SS_R = 5;
+constexpr int SS_W2 = SS_TX + 2 * SS_R, SS_H2 = SS_TY + 2 * SS_R;      // derivative-map region 42 x 42
+constexpr int SS_W1 = SS_TX + 4 * SS_R, SS_H1 = SS_TY + 4 * SS_R;      // image region 52 x 52
+constexpr int SS_THREADS = 256;
+constexpr size_t SS_SMEM = (size_t)(2 * SS_H1 * SS_W1 + 5 * SS_H1 * SS_W2 + 3 * SS_H2 * SS_W2) * sizeof(float);
+
+__constant__ float kGauss[11] = {0.001028380123898387f, 0.0075987582094967365f, 0.036000773310661316f,
+                                 0.10936068743467331f,  0.21300552785396576f,   0.26601171493530273f,
+                                 0.21300552785396576f,  0.10936068743467331f,   0.036000773310661316f,
+                                 0.0075987582094967365f, 0.001028380123898387f};
+
+template <bool GRAD>
+__global__ void __launch_bounds__(SS_THREADS) fused_ssim_kernel(const float* __restrict__ img1,
+                                                                const float* __restrict__ img2, int H, int W, float C1,
+                                                                float C2, int valid, float inv_n,
+                                                                float* __restrict__ dL_dimg1, float* __restrict__ out_mean,
+                                                                double* partials, unsigned int* ticket) {
+  extern __shared__ float smem[];
+  float(*sx)[SS_W1] = reinterpret_cast<float(*)[SS_W1]>(smem);                         // [52][52] img1
+  float(*sy)[SS_W1] = reinterpret_cast<float(*)[SS_W1]>(smem + SS_H1 * SS_W1);         // [52][52] img2
+  float* hbase = smem + 2 * SS_H1 * SS_W1;                                             // 5 x [52][42] row sums
+  float* pbase = hbase + 5 * SS_H1 * SS_W2;                                            // 3 x [42][42] weighted dm/d.
+  const int tid = threadIdx.x;
+  const int x0 = blockIdx.x * SS_TX, y0 = blockIdx.y * SS_TY;
+  const size_t plane = (size_t)blockIdx.z * H * W;
+  const float* __restrict__ a = img1 + plane;
+  const float* __restrict__ b = img2 + plane;
+  float g[11];
+#pragma unroll
+  for (int k = 0; k < 11; ++k) g[k] = kGauss[k];
+
+  // 1. the two images on the tile + 10-pixel halo (zero outside the image)
+  for (int i = tid; i < SS_H1 * SS_W1; i += SS_THREADS) {
+    const int r = i / SS_W1, c = i - r * SS_W1;
+    const int y = y0 - 2 * SS_R + r, x = x0 - 2 * SS_R + c;
+    const bool in = (unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W;
+    sx[r][c] = in ? __ldg(a + (size_t)y * W + x) : 0.f;
+    sy[r][c] = in ? __ldg(b + (size_t)y * W + x) : 0.f;
+  }
+  __syncthreads();
+  // 2. horizontal 11-tap sums of x, y, xx, yy, xy: rows of the image region, columns of the map region
+  for (int i = tid; i < SS_H1 * SS_W2; i += SS_THREADS) {
+    const int r = i / SS_W2, c = i - r * SS_W2;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f, s4 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; ++k) {
+      const float xv = sx[r][c + k], yv = sy[r][c + k], w = g[k];
+      const float wx = w * xv, wy = w * yv;
+      s0 += wx; s1 += wy;
+      s2 = fmaf(wx, xv, s2); s3 = fmaf(wy, yv, s3); s4 = fmaf(wx, yv, s4);
+    }
+    hbase[0 * SS_H1 * SS_W2 + i] = s0; hbase[1 * SS_H1 * SS_W2 + i] = s1; hbase[2 * SS_H1 * SS_W2 + i] = s2;
+    hbase[3 * SS_H1 * SS_W2 + i] = s3; hbase[4 * SS_H1 * SS_W2 + i] = s4;
+  }
+  __syncthreads();
+  // 3. vertical sums -> statistics -> m and its three partial derivatives on the tile + 5-pixel halo
+  float local = 0.f;
+  for (int i = tid; i < SS_H2 * SS_W2; i += SS_THREADS) {
+    const int r = i / SS_W2, c = i - r * SS_W2;
+    float mu1 = 0.f, mu2 = 0.f, exx = 0.f, eyy = 0.f, exy = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; ++k) {
+      const int o = (r + k) * SS_W2 + c;
+      const float w = g[k];
+      mu1 = fmaf(w, hbase[o], mu1);
+      mu2 = fmaf(w, hbase[SS_H1 * SS_W2 + o], mu2);
+      exx = fmaf(w, hbase[2 * SS_H1 * SS_W2 + o], exx);
+      eyy = fmaf(w, hbase[3 * SS_H1 * SS_W2 + o], eyy);
+      exy = fmaf(w, hbase[4 * SS_H1 * SS_W2 + o], exy);
+    }
+    const int y = y0 - SS_R + r, x = x0 - SS_R + c;
+    const bool in_img = (unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W;
+    const bool counted = in_img && (!valid || (y >= SS_R && y < H - SS_R && x >= SS_R && x < W - SS_R));
+    const float s11 = exx - mu1 * mu1, s22 = eyy - mu2 * mu2, s12 = exy - mu1 * mu2;
+    const float A = mu1 * mu1 + mu2 * mu2 + C1, B = s11 + s22 + C2;
+    const float C = 2.f * mu1 * mu2 + C1, D = 2.f * s12 + C2;
+    const float rAB = 1.f / (A * B);
+    const float m = C * D * rAB;
+    const bool centre = r >= SS_R && r < SS_R + SS_TY && c >= SS_R && c < SS_R + SS_TX;
+    if (centre && counted) local += m;
+    if (GRAD) {
+      const float wgt = counted ? inv_n : 0.f;
+      const float CD = C * D;
+      const float d_mu1 = 2.f * mu2 * (D - C) * rAB - 2.f * mu1 * CD * rAB / A + 2.f * mu1 * CD * rAB / B;
+      pbase[i] = wgt * d_mu1;
+      pbase[SS_H2 * SS_W2 + i] = wgt * (-CD * rAB / B);
+      pbase[2 * SS_H2 * SS_W2 + i] = wgt * (2.f * C * rAB);
+    }
+  }
+  if (GRAD) {
+    __syncthreads();
+    // 4. horizontal sums of the three weighted derivative maps (rows of the map region, columns of the tile);
+    //    reuses the row-sum storage of step 2
+    for (int i = tid; i < SS_H2 * SS_TX; i += SS_THREADS) {
+      const int r = i / SS_TX, c = i - r * SS_TX;
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+      for (int k = 0; k < 11; ++k) {
+        const int o = r * SS_W2 + c + k;
+        const float w = g[k];
+        s0 = fmaf(w, pbase[o], s0);
+        s1 = fmaf(w, pbase[SS_H2 * SS_W2 + o], s1);
+        s2 = fmaf(w, pbase[2 * SS_H2 * SS_W2 + o], s2);
+      }
+      hbase[i] = s0; hbase[SS_H2 * SS_TX + i] = s1; hbase[2 * SS_H2 * SS_TX + i] = s2;
+    }
+    __syncthreads();
+    // 5. vertical sums and the gradient of the tile's pixels
+    for (int i = tid; i < SS_TY * SS_TX; i += SS_THREADS) {
+      const int r = i / SS_TX, c = i - r * SS_TX;
+      const int y = y0 + r, x = x0 + c;
+      if (y < H && x < W) {
+        float t0 = 0.f, t1 = 0.f, t2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; ++k) {
+          const int o = (r + k) * SS_TX + c;
+          const float w = g[k];
+          t0 = fmaf(w, hbase[o], t0);
+          t1 = fmaf(w, hbase[SS_H2 * SS_TX + o], t1);
+          t2 = fmaf(w, hbase[2 * SS_H2 * SS_TX + o], t2);
+        }
+        const float xv = sx[r + 2 * SS_R][c + 2 * SS_R], yv = sy[r + 2 * SS_R][c + 2 * SS_R];
+        dL_dimg1[plane + (size_t)y * W + x] = t0 + 2.f * xv * t1 + yv * t2;
+      }
+    }
+  }
+
+  // deterministic sum of m: CTA partial in double, the last CTA adds the partials in index order
+  double v = (double)local;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  __shared__ double warp_sum[SS_THREADS / 32];
+  __shared__ bool last;
+  if ((tid & 31) == 0) warp_sum[tid >> 5] = v;
+  __syncthreads();
+  const unsigned int nblocks = gridDim.x * gridDim.y * gridDim.z;
+  const unsigned int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  if (tid == 0) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < SS_THREADS / 32; ++w) s += warp_sum[w];
+    partials[bid] = s;
+    __threadfence();
+    last = (atomicAdd(ticket, 1u) == nblocks - 1);
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  double t = 0.0;
+  for (unsigned int i = tid; i < nblocks; i += SS_THREADS) t += ((volatile double*)partials)[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+  __syncthreads();
+  if ((tid & 31) == 0) warp_sum[tid >> 5] = t;
+  __syncthreads();
+  if (tid == 0) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < SS_THREADS / 32; ++w) s += warp_sum[w];
+    *out_mean = (float)(s * (double)inv_n);
+    *ticket = 0u;
+  }
+}
+
+}  // namespace
+
+namespace gsr {
+size_t ssim_scratch_bytes(int planes, int H, int W) {
+  const size_t blocks = (size_t)((W + SS_TX - 1) / SS_TX) * ((H + SS_TY - 1) / SS_TY) * (size_t)(planes > 0 ? planes : 1);
+  return 128 + blocks * sizeof(double);
+}
+
+cudaError_t launch_fused_ssim(const float* img1, const float* img2, int planes, int H, int W, float C1, float C2,
+                              int valid, float* dL_dimg1, float* out_mean, void* scratch, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(fused_ssim_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(fused_ssim_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS_SMEM);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const long long hh = valid ? H - 2 * SS_R : H, ww = valid ? W - 2 * SS_R : W;
+  const double n = (double)planes * (double)(hh > 0 ? hh : 0) * (double)(ww > 0 ? ww : 0);
+  const float inv_n = n > 0 ? (float)(1.0 / n) : 0.f;
+  dim3 grid((W + SS_TX - 1) / SS_TX, (H + SS_TY - 1) / SS_TY, planes);
+  double* partials = reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + 128);
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
+  if (dL_dimg1)
+    fused_ssim_kernel<true><<<grid, SS_THREADS, SS_SMEM, s>>>(img1, img2, H, W, C1, C2, valid, inv_n, dL_dimg1, out_mean,
+                                                             partials, ticket);
+  else
+    fused_ssim_kernel<false><<<grid, SS_THREADS, SS_SMEM, s>>>(img1, img2, H, W, C1, C2, valid, inv_n, nullptr, out_mean,
+                                                              partials, ticket);
+  count_launch();
+  return cudaGetLastError();
+}
+}  // namespace gsr

@@ -155,3 +155,42 @@ def parameter_groups_on(buffers, params: Dict[str, torch.Tensor]) -> None:
         if k not in names:
             raise KeyError(f"unknown parameter {k!r}; expected one of {sorted(names)}")
         p.grad = views[names[k]].view(p.shape)
+
+
+class _FusedSSIM(torch.autograd.Function):
+    """mean SSIM map and its gradient w.r.t. img1 from ONE launch (gsr_fused_ssim)."""
+
+    @staticmethod
+    def forward(ctx, img1, img2, valid, train):
+        _need_cuda(img1, "fused_ssim")
+        if img1.dim() != 4 or img1.shape != img2.shape:
+            raise RuntimeError(f"fused_ssim: expected two (B, C, H, W) tensors of one shape, got "
+                               f"{tuple(img1.shape)} and {tuple(img2.shape)}")
+        dev = img1.device
+        a, b = N.f32c(img1), N.f32c(img2, dev)
+        B, CH, H, W = a.shape
+        out = torch.empty((), dtype=torch.float32, device=dev)
+        want_grad = bool(train) and ctx.needs_input_grad[0]
+        unit = torch.empty_like(a) if want_grad else None
+        with torch.cuda.device(dev):
+            scratch = torch.zeros(N.lib().gsr_fused_ssim_scratch_bytes(B * CH, H, W), dtype=torch.uint8, device=dev)
+            N.check(N.lib().gsr_fused_ssim(N.ptr(a), N.ptr(b), B * CH, H, W, 0.01 ** 2, 0.03 ** 2, int(valid),
+                                           N.ptr(unit), out.data_ptr(), N.ptr(scratch), N.stream_ptr(dev)),
+                    "gsr_fused_ssim")
+        ctx.unit = unit
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        if ctx.unit is None:
+            return None, None, None, None
+        return ctx.unit * grad_out, None, None, None
+
+
+def fused_ssim(img1: torch.Tensor, img2: torch.Tensor, padding: str = "same", train: bool = True) -> torch.Tensor:
+    """fused_ssim.fused_ssim (submodules/fused-ssim/fused_ssim/__init__.py:33-41): mean SSIM of two (B, C, H, W)
+    images, 11x11 Gaussian window, sigma 1.5, C1 = 0.01^2, C2 = 0.03^2; gradient flows to img1 only, as upstream.
+    The reference's loss term is `1 - fused_ssim(rendered.unsqueeze(0), gt.unsqueeze(0))`
+    (gs_lightning/lightning/gs_lightning_module.py:100,279)."""
+    assert padding in ("same", "valid")
+    return _FusedSSIM.apply(img1, img2.detach(), padding == "valid", train)

@@ -196,6 +196,17 @@ size_t gsr_l1_loss_scratch_bytes(void);
 int gsr_l1_loss(const float* image, const float* target, int64_t n, float* dL_dimage, float* out_loss,
                 void* scratch, void* stream);
 
+/* fused_ssim(img1, img2, padding, train) of submodules/fused-ssim (fused_ssim/__init__.py:33-41, ssim.cu:187-444),
+ * used as `1 - fused_ssim(rendered, gt)` at gs_lightning_module.py:100,279: *out_ssim = mean of the SSIM map
+ * (11x11 Gaussian window, sigma 1.5, zero padding; padding_valid != 0 averages the map without its 5-pixel border)
+ * and, when dL_dimg1 is not NULL, d(out_ssim)/d(img1) -- both from ONE launch (the reference's fusedssim +
+ * fusedssim_backward pair with dL_dmap = 1/N).  img1 / img2 / dL_dimg1: planes x H x W contiguous floats
+ * (planes = batch x channels).  scratch: gsr_fused_ssim_scratch_bytes() of device memory whose first 128 bytes
+ * are zero on first use (the kernel leaves them zero).  Deterministic. */
+size_t gsr_fused_ssim_scratch_bytes(int32_t planes, int32_t H, int32_t W);
+int gsr_fused_ssim(const float* img1, const float* img2, int32_t planes, int32_t H, int32_t W, float C1, float C2,
+                   int32_t padding_valid, float* dL_dimg1, float* out_ssim, void* scratch, void* stream);
+
 /* torch.optim.Adam over the parameter groups of gs_lightning_module.py:120-127 in ONE launch
  * (configs/*.yaml: eps 1e-15, default betas, no weight decay, no amsgrad).  `step` is the 1-based step
  * count after the increment, as torch uses it for the bias corrections; lr, betas and eps are doubles and are

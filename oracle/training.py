@@ -59,3 +59,41 @@ def densify_fold(d_max_radii, d_accum, d_count, max_radii2D, xyz_grad_accum, xyz
     ac[seen] = ac[seen] + np.asarray(d_accum, f32)[seen]
     ct[seen] = ct[seen] + np.asarray(d_count, f32)[seen]
     return mr, ac, ct
+
+
+def _gauss11() -> np.ndarray:
+    """The 11-tap window of submodules/fused-ssim/tests/test.py:14-16 (sigma 1.5, normalised)."""
+    g = np.exp(-((np.arange(11) - 5) ** 2) / (2 * 1.5 ** 2))
+    return g / g.sum()
+
+
+def _blur(a: np.ndarray) -> np.ndarray:
+    """Separable 11x11 Gaussian filter with zero padding over the last two axes (float64)."""
+    g = _gauss11()
+    H, W = a.shape[-2:]
+    p = np.pad(a, [(0, 0)] * (a.ndim - 2) + [(5, 5), (5, 5)])
+    h = sum(g[k] * p[..., :, k:k + W] for k in range(11))
+    return sum(g[k] * h[..., k:k + H, :] for k in range(11))
+
+
+def fused_ssim(img1, img2, padding: str = "same", C1: float = 0.01 ** 2, C2: float = 0.03 ** 2):
+    """(mean SSIM, d mean / d img1) in float64, the arithmetic of submodules/fused-ssim/ssim.cu:187-366
+    (forward map + the three partial derivatives, backward = three filtered products) with dL_dmap = 1/N
+    (fused_ssim/__init__.py:33-41; padding 'valid' drops a 5-pixel border from the mean)."""
+    x, y = np.asarray(img1, np.float64), np.asarray(img2, np.float64)
+    mu1, mu2 = _blur(x), _blur(y)
+    s11, s22, s12 = _blur(x * x) - mu1 * mu1, _blur(y * y) - mu2 * mu2, _blur(x * y) - mu1 * mu2
+    A, B = mu1 * mu1 + mu2 * mu2 + C1, s11 + s22 + C2
+    C, D = 2 * mu1 * mu2 + C1, 2 * s12 + C2
+    m = C * D / (A * B)
+    w = np.zeros_like(m)
+    if padding == "valid":
+        w[..., 5:-5, 5:-5] = 1.0
+    else:
+        w[...] = 1.0
+    w /= w.sum()
+    d_mu1 = 2 * mu2 * (D - C) / (A * B) - 2 * mu1 * C * D / (A * A * B) + 2 * mu1 * C * D / (A * B * B)
+    d_s11 = -C * D / (A * B * B)
+    d_s12 = 2 * C / (A * B)
+    grad = _blur(w * d_mu1) + 2 * x * _blur(w * d_s11) + y * _blur(w * d_s12)
+    return float((w * m).sum()), grad

@@ -179,3 +179,57 @@ def test_fused_gradient_accumulation_equals_autograd_accumulation():
     st = ba.densify_stats()
     assert torch.equal(st["max_radii2D"], mr) and torch.equal(st["xyz_grad_count"], ct)
     np.testing.assert_allclose(st["xyz_grad_accum"].cpu().numpy(), ac.cpu().numpy(), rtol=1e-5, atol=1e-9)
+
+
+@pytest.mark.parametrize("shape,padding", [((1, 3, 200, 320), "same"), ((2, 3, 67, 45), "same"), ((1, 3, 64, 96), "valid"),
+                                           ((1, 1, 12, 11), "valid"), ((1, 3, 33, 31), "same")])
+def test_fused_ssim_matches_oracle(shape, padding):
+    from gaussian_splatting_lightning_b200.training import fused_ssim
+    g = torch.Generator().manual_seed(11)
+    a = torch.rand(shape, generator=g)
+    b = (a + 0.2 * torch.rand(shape, generator=g)).clamp(0, 1)
+    want_val, want_grad = OT.fused_ssim(a.numpy(), b.numpy(), padding)
+    x = a.to(U.DEV).requires_grad_(True)
+    val = fused_ssim(x, b.to(U.DEV), padding=padding)
+    (1.0 - val).backward()                      # the reference's loss term: 1 - fused_ssim(...)
+    assert abs(float(val.detach()) - want_val) <= 2e-6
+    s = float(np.abs(want_grad).max())
+    # tolerance: FP32 against the float64 oracle, 1e-4 of the largest gradient entry
+    assert float(np.abs(-x.grad.cpu().numpy() - want_grad).max()) <= 1e-4 * s
+    assert float(fused_ssim(x.detach(), b.to(U.DEV), padding=padding, train=False)) == float(val.detach())
+
+
+def _reference_fused_ssim(mod, img1, img2, padding="same"):
+    """fused_ssim.fused_ssim restated over the reference's compiled kernels (fused_ssim/__init__.py:8-41)."""
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12 = mod.fusedssim(C1, C2, img1, img2, True)
+    m = ssim_map[:, :, 5:-5, 5:-5] if padding == "valid" else ssim_map
+    dL_dmap = torch.full_like(m, 1.0 / m.numel())
+    if padding == "valid":
+        full = torch.zeros_like(img1)
+        full[:, :, 5:-5, 5:-5] = dL_dmap
+        dL_dmap = full
+    grad = mod.fusedssim_backward(C1, C2, img1, img2, dL_dmap, dm_dmu1, dm_dsigma1_sq, dm_dsigma12)
+    return m.mean(), grad
+
+
+@pytest.mark.parametrize("shape,padding", [((1, 3, 1080, 1920), "same"), ((2, 3, 211, 173), "same"),
+                                           ((1, 3, 300, 200), "valid")])
+def test_fused_ssim_matches_the_reference_cuda_kernels(shape, padding):
+    """oracle/_ref/fused_ssim_cuda.so is the reference's own fused-ssim extension compiled for sm_100a by
+    oracle/build_ref.py from /root/reference/submodules/fused-ssim; it travels to the GPU box with the snapshot."""
+    from oracle import build_ref
+    if not build_ref.available():
+        pytest.skip("oracle/_ref/fused_ssim_cuda.so has not been built (needs /root/reference)")
+    from gaussian_splatting_lightning_b200.training import fused_ssim
+    mod = build_ref.load()
+    g = torch.Generator().manual_seed(12)
+    a = torch.rand(shape, generator=g).to(U.DEV)
+    b = (a + 0.3 * torch.rand(shape, generator=g).to(U.DEV)).clamp(0, 1)
+    ref_val, ref_grad = _reference_fused_ssim(mod, a, b, padding)
+    x = a.clone().requires_grad_(True)
+    val = fused_ssim(x, b, padding=padding)
+    val.backward()
+    assert abs(float(val.detach()) - float(ref_val)) <= 2e-6
+    s = float(ref_grad.abs().max())
+    assert float((x.grad - ref_grad).abs().max()) <= 1e-4 * s

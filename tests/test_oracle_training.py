@@ -68,3 +68,32 @@ def test_densify_fold_matches_view_by_view_updates():
     np.testing.assert_array_equal(got[0], ref[0].numpy())
     np.testing.assert_allclose(got[1], ref[1].numpy(), rtol=1e-6)
     np.testing.assert_array_equal(got[2], ref[2].numpy())
+
+
+def _torch_ssim(img1, img2, padding):
+    """The PyTorch SSIM the reference's own test compares fused-ssim with (submodules/fused-ssim/tests/test.py:14-54):
+    grouped conv2d with the 11x11 Gaussian window, zero padding; 'valid' crops 5 pixels before the mean."""
+    import torch.nn.functional as F
+    ch = img1.shape[1]
+    g = torch.tensor([np.exp(-(x - 5) ** 2 / (2 * 1.5 ** 2)) for x in range(11)], dtype=img1.dtype)
+    g = g / g.sum()
+    win = (g[:, None] @ g[None, :]).expand(ch, 1, 11, 11).contiguous()
+    blur = lambda t: F.conv2d(t, win, padding=5, groups=ch)
+    mu1, mu2 = blur(img1), blur(img2)
+    s11, s22, s12 = blur(img1 * img1) - mu1 ** 2, blur(img2 * img2) - mu2 ** 2, blur(img1 * img2) - mu1 * mu2
+    m = ((2 * mu1 * mu2 + 0.01 ** 2) * (2 * s12 + 0.03 ** 2)) / ((mu1 ** 2 + mu2 ** 2 + 0.01 ** 2) * (s11 + s22 + 0.03 ** 2))
+    if padding == "valid":
+        m = m[:, :, 5:-5, 5:-5]
+    return m.mean()
+
+
+def test_ssim_oracle_matches_torch_autograd():
+    g = torch.Generator().manual_seed(7)
+    for shape, padding in (((2, 3, 37, 45), "same"), ((1, 3, 40, 33), "valid"), ((1, 1, 12, 11), "valid")):
+        a = torch.rand(shape, generator=g, dtype=torch.float64, requires_grad=True)
+        b = (a.detach() + 0.2 * torch.rand(shape, generator=g, dtype=torch.float64)).clamp(0, 1)
+        val = _torch_ssim(a, b, padding)
+        val.backward()
+        got_val, got_grad = OT.fused_ssim(a.detach().numpy(), b.numpy(), padding)
+        assert abs(got_val - float(val.detach())) <= 1e-12
+        np.testing.assert_allclose(got_grad, a.grad.numpy(), rtol=1e-9, atol=1e-13)
