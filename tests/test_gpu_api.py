@@ -157,3 +157,33 @@ def test_backward_accumulate_stats_and_optional_outputs():
     assert np.array_equal(max_radii.cpu().numpy(), want_max)
     assert np.array_equal(count.cpu().numpy(), want_count.astype(np.float32))
     assert np.abs(accum.cpu().numpy() - want_accum).max() <= 2e-4 * max(1.0, want_accum.max())
+
+
+def test_ply_checkpoint_and_collated_cameras_through_the_render_path(tmp_path):
+    """SURVEY 8(f) rows 3-4 end to end: Gaussians saved to a PLY, loaded straight to the device, rendered for a
+    default_collate'd batch of ColmapDataset-style items; same pixels as rendering the original tensors per view."""
+    from torch.utils.data import default_collate
+    from gaussian_splatting_lightning_b200 import cameras, io, synthetic
+    from gaussian_splatting_lightning_b200.rasterizer import GaussianRasterizer
+    P, deg, W, H, V = 4000, 3, 160, 96, 3
+    scene = synthetic.make_scene(P, deg, W, H, seed=5)
+    path = str(tmp_path / "point_cloud.ply")
+    io.save_ply(path, scene["means3D"], scene["shs"][:, :1], scene["shs"][:, 1:], scene["opacities"], scene["scales"],
+                scene["rotations"])
+    ck = io.load_ply(path, device=U.DEV, canonical=True)
+    shs = torch.cat([ck["features_dc"], ck["features_rest"]], 1)
+    assert ck["xyz"].is_cuda and torch.equal(shs.cpu(), scene["shs"]) and ck["active_sh_degree"] == 3
+    items = []
+    for k in range(V):
+        c = synthetic.make_camera(W, H, k=k, num_views=V)
+        items.append(dict(image=torch.zeros(3, H, W), background=torch.tensor([0.1, 0.2, 0.3]), tanfovx=c["tanfovx"],
+                          tanfovy=c["tanfovy"], viewmatrix=c["viewmatrix"], projmatrix=c["projmatrix"], campos=c["campos"]))
+    sets = cameras.settings_from_batch(default_collate(items), sh_degree=deg, device=U.DEV)
+    d = {k: v.to(U.DEV) for k, v in scene.items()}
+    for s, it in zip(sets, items):
+        a = GaussianRasterizer(s)(means3D=ck["xyz"], means2D=None, shs=shs, opacities=ck["opacity"],
+                                  scales=ck["scaling"], rotations=ck["rotation"])[0]
+        b = GaussianRasterizer(cameras.settings_from_item(it, deg))(means3D=d["means3D"], means2D=None, shs=d["shs"],
+                                                                   opacities=d["opacities"], scales=d["scales"],
+                                                                   rotations=d["rotations"])[0]
+        assert torch.equal(a, b)
