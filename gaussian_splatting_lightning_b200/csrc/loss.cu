@@ -10,6 +10,7 @@
 // in index order and resets the ticket, so the scratch can be reused by the next call on the same stream.
 #include "../../include/gsr_b200.h"
 #include "gsr_common.cuh"
+#include "render_common.cuh"
 
 namespace {
 
@@ -119,7 +120,7 @@ namespace {
 constexpr int SS_TX = 32, SS_TY = 32, SS_R = 5;
 constexpr int SS_W2 = SS_TX + 2 * SS_R, SS_H2 = SS_TY + 2 * SS_R;      // derivative-map region 42 x 42
 constexpr int SS_W1 = SS_TX + 4 * SS_R, SS_H1 = SS_TY + 4 * SS_R;      // image region 52 x 52
-constexpr int SS_THREADS = 256;
+constexpr int SS_THREADS = 384;
 constexpr size_t SS_SMEM = (size_t)(2 * SS_H1 * SS_W1 + 5 * SS_H1 * SS_W2 + 3 * SS_H2 * SS_W2) * sizeof(float);
 
 __constant__ float kGauss[11] = {0.001028380123898387f, 0.0075987582094967365f, 0.036000773310661316f,
@@ -127,17 +128,27 @@ __constant__ float kGauss[11] = {0.001028380123898387f, 0.0075987582094967365f, 
                                  0.21300552785396576f,  0.10936068743467331f,   0.036000773310661316f,
                                  0.0075987582094967365f, 0.001028380123898387f};
 
+// Shared-memory layout (floats): the two images interleaved as (x, y) pairs on the 52 x 52 region; the horizontal
+// sums as (sum x, sum y) pairs, (sum xx, sum yy) pairs and sum xy on 52 x 42; the weighted derivative maps as
+// (dm/dmu1, dm/ds11) pairs and dm/ds12 on 42 x 42.  Pairs go through the packed FP32 instructions (FFMA2) with the
+// Gaussian weight broadcast; every thread owns a strip of 3-4 consecutive outputs along the filter direction so that
+// a loaded value feeds up to 11 x 3 multiply-adds from registers.
+constexpr int SS_N1 = SS_H1 * SS_W1, SS_NH = SS_H1 * SS_W2, SS_N2 = SS_H2 * SS_W2;
+
 template <bool GRAD>
-__global__ void __launch_bounds__(SS_THREADS) fused_ssim_kernel(const float* __restrict__ img1,
+__global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* __restrict__ img1,
                                                                 const float* __restrict__ img2, int H, int W, float C1,
                                                                 float C2, int valid, float inv_n,
                                                                 float* __restrict__ dL_dimg1, float* __restrict__ out_mean,
                                                                 double* partials, unsigned int* ticket) {
-  extern __shared__ float smem[];
-  float(*sx)[SS_W1] = reinterpret_cast<float(*)[SS_W1]>(smem);                         // [52][52] img1
-  float(*sy)[SS_W1] = reinterpret_cast<float(*)[SS_W1]>(smem + SS_H1 * SS_W1);         // [52][52] img2
-  float* hbase = smem + 2 * SS_H1 * SS_W1;                                             // 5 x [52][42] row sums
-  float* pbase = hbase + 5 * SS_H1 * SS_W2;                                            // 3 x [42][42] weighted dm/d.
+  using gsr::f32x2; using gsr::pk2; using gsr::upk2; using gsr::fma2; using gsr::mul2;
+  extern __shared__ __align__(16) float smem[];
+  float2* sxy = reinterpret_cast<float2*>(smem);                    // [52][52] (x, y)
+  float2* hA = reinterpret_cast<float2*>(smem + 2 * SS_N1);         // [52][42] (sum x, sum y)
+  float2* hB = hA + SS_NH;                                          // [52][42] (sum xx, sum yy)
+  float* hC = reinterpret_cast<float*>(hB + SS_NH);                 // [52][42] sum xy
+  float2* pA = reinterpret_cast<float2*>(hC + SS_NH);               // [42][42] w (dm/dmu1, dm/ds11)
+  float* pC = reinterpret_cast<float*>(pA + SS_N2);                 // [42][42] w dm/ds12
   const int tid = threadIdx.x;
   const int x0 = blockIdx.x * SS_TX, y0 = blockIdx.y * SS_TY;
   const size_t plane = (size_t)blockIdx.z * H * W;
@@ -147,98 +158,166 @@ __global__ void __launch_bounds__(SS_THREADS) fused_ssim_kernel(const float* __r
 #pragma unroll
   for (int k = 0; k < 11; ++k) g[k] = kGauss[k];
 
-  // 1. the two images on the tile + 10-pixel halo (zero outside the image)
-  for (int i = tid; i < SS_H1 * SS_W1; i += SS_THREADS) {
-    const int r = i / SS_W1, c = i - r * SS_W1;
-    const int y = y0 - 2 * SS_R + r, x = x0 - 2 * SS_R + c;
-    const bool in = (unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W;
-    sx[r][c] = in ? __ldg(a + (size_t)y * W + x) : 0.f;
-    sy[r][c] = in ? __ldg(b + (size_t)y * W + x) : 0.f;
-  }
-  __syncthreads();
-  // 2. horizontal 11-tap sums of x, y, xx, yy, xy: rows of the image region, columns of the map region
-  for (int i = tid; i < SS_H1 * SS_W2; i += SS_THREADS) {
-    const int r = i / SS_W2, c = i - r * SS_W2;
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f, s4 = 0.f;
+  // 1. the two images on the tile + 10-pixel halo (zero outside the image); all of a thread's loads are issued
+  //    before the first store so that their latencies overlap
+  {
+    constexpr int IT = (SS_N1 + SS_THREADS - 1) / SS_THREADS;
+    float2 t[IT];
 #pragma unroll
-    for (int k = 0; k < 11; ++k) {
-      const float xv = sx[r][c + k], yv = sy[r][c + k], w = g[k];
-      const float wx = w * xv, wy = w * yv;
-      s0 += wx; s1 += wy;
-      s2 = fmaf(wx, xv, s2); s3 = fmaf(wy, yv, s3); s4 = fmaf(wx, yv, s4);
+    for (int k = 0; k < IT; ++k) {
+      const int i = tid + k * SS_THREADS;
+      const int r = i / SS_W1, c = i - r * SS_W1;
+      const int y = y0 - 2 * SS_R + r, x = x0 - 2 * SS_R + c;
+      const bool in = i < SS_N1 && (unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W;
+      const size_t o = in ? (size_t)y * W + x : 0;
+      t[k] = in ? make_float2(__ldg(a + o), __ldg(b + o)) : make_float2(0.f, 0.f);
     }
-    hbase[0 * SS_H1 * SS_W2 + i] = s0; hbase[1 * SS_H1 * SS_W2 + i] = s1; hbase[2 * SS_H1 * SS_W2 + i] = s2;
-    hbase[3 * SS_H1 * SS_W2 + i] = s3; hbase[4 * SS_H1 * SS_W2 + i] = s4;
+#pragma unroll
+    for (int k = 0; k < IT; ++k) {
+      const int i = tid + k * SS_THREADS;
+      if (i < SS_N1) sxy[i] = t[k];
+    }
   }
   __syncthreads();
-  // 3. vertical sums -> statistics -> m and its three partial derivatives on the tile + 5-pixel halo
+  // 2. horizontal 11-tap sums: a thread owns 3 consecutive columns of one row
+  for (int it = tid; it < SS_H1 * (SS_W2 / 3); it += SS_THREADS) {
+    const int r = it / (SS_W2 / 3), c = (it - r * (SS_W2 / 3)) * 3;
+    f32x2 v[13], q[13];
+    float xy[13];
+#pragma unroll
+    for (int k = 0; k < 13; ++k) {
+      const float2 t = sxy[r * SS_W1 + c + k];
+      v[k] = pk2(t.x, t.y);
+      q[k] = mul2(v[k], v[k]);
+      xy[k] = t.x * t.y;
+    }
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      f32x2 s01 = 0ull, s23 = 0ull;
+      float s4 = 0.f;
+#pragma unroll
+      for (int k = 0; k < 11; ++k) {
+        const f32x2 w2 = pk2(g[k], g[k]);
+        s01 = fma2(w2, v[j + k], s01);
+        s23 = fma2(w2, q[j + k], s23);
+        s4 = fmaf(g[k], xy[j + k], s4);
+      }
+      const int o = r * SS_W2 + c + j;
+      float lo, hi;
+      upk2(s01, lo, hi); hA[o] = make_float2(lo, hi);
+      upk2(s23, lo, hi); hB[o] = make_float2(lo, hi);
+      hC[o] = s4;
+    }
+  }
+  __syncthreads();
+  // 3. vertical sums -> statistics -> m and its three partial derivatives: a thread owns 3 consecutive rows of one column
   float local = 0.f;
-  for (int i = tid; i < SS_H2 * SS_W2; i += SS_THREADS) {
-    const int r = i / SS_W2, c = i - r * SS_W2;
-    float mu1 = 0.f, mu2 = 0.f, exx = 0.f, eyy = 0.f, exy = 0.f;
+  for (int it = tid; it < (SS_H2 / 3) * SS_W2; it += SS_THREADS) {
+    const int rs = it / SS_W2, c = it - rs * SS_W2, r0 = rs * 3;
+    f32x2 vA[13], vB[13];
+    float vC[13];
 #pragma unroll
-    for (int k = 0; k < 11; ++k) {
-      const int o = (r + k) * SS_W2 + c;
-      const float w = g[k];
-      mu1 = fmaf(w, hbase[o], mu1);
-      mu2 = fmaf(w, hbase[SS_H1 * SS_W2 + o], mu2);
-      exx = fmaf(w, hbase[2 * SS_H1 * SS_W2 + o], exx);
-      eyy = fmaf(w, hbase[3 * SS_H1 * SS_W2 + o], eyy);
-      exy = fmaf(w, hbase[4 * SS_H1 * SS_W2 + o], exy);
+    for (int k = 0; k < 13; ++k) {
+      const int o = (r0 + k) * SS_W2 + c;
+      const float2 ta = hA[o], tb = hB[o];
+      vA[k] = pk2(ta.x, ta.y);
+      vB[k] = pk2(tb.x, tb.y);
+      vC[k] = hC[o];
     }
-    const int y = y0 - SS_R + r, x = x0 - SS_R + c;
-    const bool in_img = (unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W;
-    const bool counted = in_img && (!valid || (y >= SS_R && y < H - SS_R && x >= SS_R && x < W - SS_R));
-    const float s11 = exx - mu1 * mu1, s22 = eyy - mu2 * mu2, s12 = exy - mu1 * mu2;
-    const float A = mu1 * mu1 + mu2 * mu2 + C1, B = s11 + s22 + C2;
-    const float C = 2.f * mu1 * mu2 + C1, D = 2.f * s12 + C2;
-    const float rAB = 1.f / (A * B);
-    const float m = C * D * rAB;
-    const bool centre = r >= SS_R && r < SS_R + SS_TY && c >= SS_R && c < SS_R + SS_TX;
-    if (centre && counted) local += m;
-    if (GRAD) {
-      const float wgt = counted ? inv_n : 0.f;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      f32x2 m12 = 0ull, e12 = 0ull;
+      float exy = 0.f;
+#pragma unroll
+      for (int k = 0; k < 11; ++k) {
+        const f32x2 w2 = pk2(g[k], g[k]);
+        m12 = fma2(w2, vA[j + k], m12);
+        e12 = fma2(w2, vB[j + k], e12);
+        exy = fmaf(g[k], vC[j + k], exy);
+      }
+      float mu1, mu2, exx, eyy;
+      upk2(m12, mu1, mu2);
+      upk2(e12, exx, eyy);
+      const int r = r0 + j;
+      const int y = y0 - SS_R + r, x = x0 - SS_R + c;
+      const bool in_img = (unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W;
+      const bool counted = in_img && (!valid || (y >= SS_R && y < H - SS_R && x >= SS_R && x < W - SS_R));
+      const float s11 = exx - mu1 * mu1, s22 = eyy - mu2 * mu2, s12 = exy - mu1 * mu2;
+      const float A = mu1 * mu1 + mu2 * mu2 + C1, B = s11 + s22 + C2;
+      const float C = 2.f * mu1 * mu2 + C1, D = 2.f * s12 + C2;
+      const float rA = __frcp_rn(A), rB = __frcp_rn(B);
+      const float rAB = rA * rB;
       const float CD = C * D;
-      const float d_mu1 = 2.f * mu2 * (D - C) * rAB - 2.f * mu1 * CD * rAB / A + 2.f * mu1 * CD * rAB / B;
-      pbase[i] = wgt * d_mu1;
-      pbase[SS_H2 * SS_W2 + i] = wgt * (-CD * rAB / B);
-      pbase[2 * SS_H2 * SS_W2 + i] = wgt * (2.f * C * rAB);
+      const float m = CD * rAB;
+      const bool centre = r >= SS_R && r < SS_R + SS_TY && c >= SS_R && c < SS_R + SS_TX;
+      if (centre && counted) local += m;
+      if (GRAD) {
+        const float wgt = counted ? inv_n : 0.f;
+        const float wm = wgt * m;                                     // w C D / (A B)
+        const float d_mu1 = 2.f * (wgt * rAB) * mu2 * (D - C) + 2.f * mu1 * wm * (rB - rA);
+        const int o = r * SS_W2 + c;
+        pA[o] = make_float2(d_mu1, -wm * rB);
+        pC[o] = 2.f * C * (wgt * rAB);
+      }
     }
   }
   if (GRAD) {
     __syncthreads();
-    // 4. horizontal sums of the three weighted derivative maps (rows of the map region, columns of the tile);
-    //    reuses the row-sum storage of step 2
-    for (int i = tid; i < SS_H2 * SS_TX; i += SS_THREADS) {
-      const int r = i / SS_TX, c = i - r * SS_TX;
-      float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+    // 4. horizontal sums of the weighted derivative maps: a thread owns 4 consecutive columns of one row;
+    //    results reuse the storage of step 2
+    for (int it = tid; it < SS_H2 * (SS_TX / 4); it += SS_THREADS) {
+      const int r = it / (SS_TX / 4), c = (it - r * (SS_TX / 4)) * 4;
+      f32x2 v[14];
+      float u[14];
 #pragma unroll
-      for (int k = 0; k < 11; ++k) {
-        const int o = r * SS_W2 + c + k;
-        const float w = g[k];
-        s0 = fmaf(w, pbase[o], s0);
-        s1 = fmaf(w, pbase[SS_H2 * SS_W2 + o], s1);
-        s2 = fmaf(w, pbase[2 * SS_H2 * SS_W2 + o], s2);
+      for (int k = 0; k < 14; ++k) {
+        const float2 t = pA[r * SS_W2 + c + k];
+        v[k] = pk2(t.x, t.y);
+        u[k] = pC[r * SS_W2 + c + k];
       }
-      hbase[i] = s0; hbase[SS_H2 * SS_TX + i] = s1; hbase[2 * SS_H2 * SS_TX + i] = s2;
-    }
-    __syncthreads();
-    // 5. vertical sums and the gradient of the tile's pixels
-    for (int i = tid; i < SS_TY * SS_TX; i += SS_THREADS) {
-      const int r = i / SS_TX, c = i - r * SS_TX;
-      const int y = y0 + r, x = x0 + c;
-      if (y < H && x < W) {
-        float t0 = 0.f, t1 = 0.f, t2 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        f32x2 s01 = 0ull;
+        float s2 = 0.f;
 #pragma unroll
         for (int k = 0; k < 11; ++k) {
-          const int o = (r + k) * SS_TX + c;
-          const float w = g[k];
-          t0 = fmaf(w, hbase[o], t0);
-          t1 = fmaf(w, hbase[SS_H2 * SS_TX + o], t1);
-          t2 = fmaf(w, hbase[2 * SS_H2 * SS_TX + o], t2);
+          s01 = fma2(pk2(g[k], g[k]), v[j + k], s01);
+          s2 = fmaf(g[k], u[j + k], s2);
         }
-        const float xv = sx[r + 2 * SS_R][c + 2 * SS_R], yv = sy[r + 2 * SS_R][c + 2 * SS_R];
-        dL_dimg1[plane + (size_t)y * W + x] = t0 + 2.f * xv * t1 + yv * t2;
+        float lo, hi;
+        upk2(s01, lo, hi);
+        hA[r * SS_TX + c + j] = make_float2(lo, hi);
+        hC[r * SS_TX + c + j] = s2;
+      }
+    }
+    __syncthreads();
+    // 5. vertical sums and the gradient: a thread owns 4 consecutive rows of one column
+    for (int it = tid; it < (SS_TY / 4) * SS_TX; it += SS_THREADS) {
+      const int rs = it / SS_TX, c = it - rs * SS_TX, r0 = rs * 4;
+      f32x2 v[14];
+      float u[14];
+#pragma unroll
+      for (int k = 0; k < 14; ++k) {
+        const float2 t = hA[(r0 + k) * SS_TX + c];
+        v[k] = pk2(t.x, t.y);
+        u[k] = hC[(r0 + k) * SS_TX + c];
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        f32x2 t01 = 0ull;
+        float t2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; ++k) {
+          t01 = fma2(pk2(g[k], g[k]), v[j + k], t01);
+          t2 = fmaf(g[k], u[j + k], t2);
+        }
+        const int y = y0 + r0 + j, x = x0 + c;
+        if (y < H && x < W) {
+          float t0, t1;
+          upk2(t01, t0, t1);
+          const float2 px = sxy[(r0 + j + 2 * SS_R) * SS_W1 + c + 2 * SS_R];
+          dL_dimg1[plane + (size_t)y * W + x] = t0 + 2.f * px.x * t1 + px.y * t2;
+        }
       }
     }
   }
