@@ -189,15 +189,11 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
         const int j = c0 + bit;
         const uint32_t idx = (uint32_t)(base + j);
         const uint32_t addr = aRec + (uint32_t)j * 16u;
-        f32x2 q0, my2, q1, hC2, no2, r2, g2, bl2, iz2, idw;
-        lds2x64<0>(addr, q0, my2);
-        lds2x64<GSR_PLANE>(addr, q1, hC2);
-        lds2x64<2 * GSR_PLANE>(addr, no2, r2);
-        lds2x64<3 * GSR_PLANE>(addr, g2, bl2);
-        lds2x64<4 * GSR_PLANE>(addr, iz2, idw);
-        float mx, hA, hB, unused;
-        upk2(q0, mx, hA);
-        upk2(q1, hB, unused);
+        const float4 ra = lds128<0>(addr);                    // {mean.x, mean.y, hA, hB}
+        const float4 rb = lds128<GSR_PLANE>(addr);            // {hC, -opacity, r, g}
+        const float4 rc = lds128<2 * GSR_PLANE>(addr);        // {b, 1/z, tau2, bits(gaussian id)}
+        const float mx = ra.x, my = ra.y, hA = ra.z, hB = ra.w, hC = rb.x, no = rb.y, cr = rb.z, cg = rb.w, cb = rc.x,
+                    iz = rc.y;
         const float dx = mx - pxf;
         const float tt = __fmul_rn(__fmul_rn(hA, dx), dx);
         const float vv = __fmul_rn(hB, dx);
@@ -205,13 +201,14 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
         if (both & bitm) {
           // packed path: both pixels in one instruction stream
           const f32x2 dx2 = pk2(dx, dx);
-          const f32x2 dy2 = add2(my2, pk2(npyA, npyB));
-          f32x2 e2 = fma2(mul2(hC2, dy2), dy2, pk2(tt, tt));
+          const f32x2 dy2 = add2(pk2(my, my), pk2(npyA, npyB));
+          f32x2 e2 = fma2(mul2(pk2(hC, hC), dy2), dy2, pk2(tt, tt));
           e2 = fma2(pk2(vv, vv), dy2, e2);
           float eA, eB;
           upk2(e2, eA, eB);
           const f32x2 G2 = pk2(ex2_approx(-eA), ex2_approx(-eB));
           float naA, naB;
+          const f32x2 no2 = pk2(no, no);
           upk2(mul2(no2, G2), naA, naB);
           naA = fmaxf(naA, -0.99f);
           naB = fmaxf(naB, -0.99f);
@@ -226,8 +223,8 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
           upk2(nT2, nTA, nTB);
           const f32x2 w2 = mul2(na2, nT2);                                  // alpha T
           // d = colour - (colour accumulated BEHIND this splat)
-          const f32x2 d0 = add2(r2, pk2(nar0A, nar0B)), d1 = add2(g2, pk2(nar1A, nar1B)),
-                      d2 = add2(bl2, pk2(nar2A, nar2B)), d3 = add2(iz2, pk2(nar3A, nar3B));
+          const f32x2 d0 = add2(pk2(cr, cr), pk2(nar0A, nar0B)), d1 = add2(pk2(cg, cg), pk2(nar1A, nar1B)),
+                      d2 = add2(pk2(cb, cb), pk2(nar2A, nar2B)), d3 = add2(pk2(iz, iz), pk2(nar3A, nar3B));
           const f32x2 dp0 = pk2(dp0A, dp0B), dp1 = pk2(dp1A, dp1B), dp2 = pk2(dp2A, dp2B), dp3 = pk2(dp3A, dp3B);
           f32x2 dL = mul2(d0, dp0);
           dL = fma2(d1, dp1, dL);
@@ -260,9 +257,6 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
           upk2(p8, lo, hi); s8 = lo + hi;
           upk2(p9, lo, hi); s9 = lo + hi;
         } else {
-          float my, hC, no, cr, cg, cb, iz;
-          upk2(my2, my, unused); upk2(hC2, hC, unused); upk2(no2, no, unused); upk2(r2, cr, unused);
-          upk2(g2, cg, unused); upk2(bl2, cb, unused); upk2(iz2, iz, unused);
           if (maskA & bitm) GSR_BWD_ONE(A) else GSR_BWD_ONE(B)
         }
 
@@ -284,9 +278,7 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
         GSR_XCHG(sum, t0, t1, b2, 2);
         sum += __shfl_xor_sync(0xffffffffu, sum, 1);
         if (slot >= 0) {
-          float idf, pad;
-          upk2(idw, idf, pad);
-          atomicAdd(grad_acc + (size_t)__float_as_uint(idf) * 12 + slot, sum);
+          atomicAdd(grad_acc + (size_t)__float_as_uint(rc.w) * 12 + slot, sum);
         }
       }
     }

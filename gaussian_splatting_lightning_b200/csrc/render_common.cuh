@@ -118,25 +118,22 @@ __device__ __forceinline__ f32x2 lds1x64(uint32_t addr) {
   return v;
 }
 
-// Staged batch: planes of 256 float4, plane p of entry j at byte offset p*4096 + j*16.  Values a packed
-// instruction needs for both pixels are stored twice, so that one 64-bit half of a 128-bit shared load IS the
-// broadcast pair (no MOVs in the hit loop); opacity is stored negated because the loops carry -alpha and -T
-// (T (1 - alpha) = fma(-T, -alpha, -T) negated, alpha T = (-alpha)(-T): exact, and no packed negation exists).
-//   plane 0 {mean.x, hA, mean.y, mean.y}   plane 1 {hB, tau2, hC, hC}   plane 2 {-o, -o, r, r}
-//   plane 3 {g, g, b, b}                    plane 4 {1/z, 1/z, bits(gaussian id), 0}
-//   forward only: plane 5 = cull plane (make_cull_plane)
+// Staged batch: planes of 256 float4, plane p of entry j at byte offset p*4096 + j*16.  Opacity is stored negated
+// because the loops carry -alpha and -T (T (1 - alpha) = fma(-T, -alpha, -T) negated, alpha T = (-alpha)(-T): exact,
+// and no packed negation exists).  The packed instructions take a scalar register as a broadcast operand
+// (SASS `R.F32`), so per-splat values need no duplication: pk2(v, v) costs nothing.
+//   plane 0 {mean.x, mean.y, hA, hB}   plane 1 {hC, -opacity, r, g}   plane 2 {b, 1/z, tau2, bits(gaussian id)}
+//   forward only: plane 3 = cull plane (make_cull_plane)
 #define GSR_PLANE 4096
-#define GSR_REC_PLANES 5
+#define GSR_REC_PLANES 3
 
 // a, b, c: the GsrRec words {mean2D.xy, conic.A, conic.B}, {conic.C, opacity, r, g}, {b, 1/z, tau, z}
 __device__ __forceinline__ void stage_record(float4 (*sRec)[256], int j, const float4 a, const float4 b, const float4 c,
                                              uint32_t gid, float& hA, float& hB, float& hC, float& tau2) {
   hA = a.z * GSR_HALF_LOG2E; hB = a.w * GSR_LOG2E; hC = b.x * GSR_HALF_LOG2E; tau2 = c.z * GSR_LOG2E;
-  sRec[0][j] = make_float4(a.x, hA, a.y, a.y);
-  sRec[1][j] = make_float4(hB, tau2, hC, hC);
-  sRec[2][j] = make_float4(-b.y, -b.y, b.z, b.z);
-  sRec[3][j] = make_float4(b.w, b.w, c.x, c.x);
-  sRec[4][j] = make_float4(c.y, c.y, __uint_as_float(gid), 0.f);
+  sRec[0][j] = make_float4(a.x, a.y, hA, hB);
+  sRec[1][j] = make_float4(hC, -b.y, b.z, b.w);
+  sRec[2][j] = make_float4(c.x, c.y, tau2, __uint_as_float(gid));
 }
 
 // e = hA dx^2 + hC dy^2 + hB dx dy with a FIXED rounding sequence: the forward and the backward

@@ -16,8 +16,8 @@
 //     pixel costs no extra issue slots for the FP32 work, and these kernels are issue bound;
 //   * the tile's list is consumed in batches of 256: each thread gathers two packed 48-byte GsrRec (three
 //     128-bit loads each, L2-resident at 1M Gaussians) and stages them in shared memory with the quadratic
-//     form pre-scaled into the log2 domain and the per-pixel operands duplicated (render_common.cuh), so that
-//     the inner loop is 8 FP32 issue slots + two MUFU.EX2 per (pixel pair, splat);
+//     form pre-scaled into the log2 domain (render_common.cuh; per-splat values enter the packed instructions as
+//     broadcast scalar operands), so that the inner loop is 8 FP32 issue slots + two MUFU.EX2 per (pixel pair, splat);
 //   * sub-tile culling: before touching a chunk of 32 entries, each lane tests ONE splat against each of
 //     the warp's two 8x4 rectangles (exact minimum of the quadratic form over the rectangle vs.
 //     tau2 = log2(255 * opacity), conservative margin) and two ballots turn the answers into bit masks; the
@@ -116,12 +116,12 @@ __global__ void __launch_bounds__(128) render_forward_kernel(const GsrView v, co
 
     for (int c0 = 0; c0 < cnt; c0 += 32) {
       // one splat per lane against the warp's two sub-tiles
-      const float4 p0 = sRec[0][c0 + lane], p1 = sRec[1][c0 + lane], cull = sRec[GSR_REC_PLANES][c0 + lane];
-      const float4 geo = make_float4(p0.x, p0.z, p0.y, p1.x);  // {mean.x, mean.y, hA, hB}
+      const float4 geo = sRec[0][c0 + lane], cull = sRec[GSR_REC_PLANES][c0 + lane];   // {mean.x, mean.y, hA, hB}
+      const float hCl = sRec[1][c0 + lane].x;
       const bool allA = __all_sync(0xffffffffu, thrA == NEG_INF), allB = __all_sync(0xffffffffu, thrB == NEG_INF);
       if (allA && allB) break;
-      const uint32_t maskA = __ballot_sync(0xffffffffu, !allA && subtile_may_contribute(geo, p1.z, cull, stA));
-      const uint32_t maskB = __ballot_sync(0xffffffffu, !allB && subtile_may_contribute(geo, p1.z, cull, stB));
+      const uint32_t maskA = __ballot_sync(0xffffffffu, !allA && subtile_may_contribute(geo, hCl, cull, stA));
+      const uint32_t maskB = __ballot_sync(0xffffffffu, !allB && subtile_may_contribute(geo, hCl, cull, stB));
       uint32_t mask = maskA | maskB;
       const uint32_t both = maskA & maskB;
       uint32_t okA_bits = 0, okB_bits = 0;  // per lane: entries of the chunk that contributed to pixel A / B
@@ -130,28 +130,24 @@ __global__ void __launch_bounds__(128) render_forward_kernel(const GsrView v, co
         const uint32_t bitm = mask & (0u - mask);
         mask ^= bitm;
         const uint32_t addr = aRec + (uint32_t)(c0 + bit) * 16u;
-        f32x2 q0, my2, q1, hC2, no2, r2, g2, bl2;
-        lds2x64<0>(addr, q0, my2);
-        lds2x64<GSR_PLANE>(addr, q1, hC2);
-        lds2x64<2 * GSR_PLANE>(addr, no2, r2);
-        lds2x64<3 * GSR_PLANE>(addr, g2, bl2);
-        const f32x2 iz2 = lds1x64<4 * GSR_PLANE>(addr);
-        float mx, hA, hB, unused, my, hC, no, cr, cg, cb, iz;
-        upk2(q0, mx, hA);
-        upk2(q1, hB, unused);
+        const float4 ra = lds128<0>(addr);                    // {mean.x, mean.y, hA, hB}
+        const float4 rb = lds128<GSR_PLANE>(addr);            // {hC, -opacity, r, g}
+        const float2 rc = lds64<2 * GSR_PLANE>(addr);         // {b, 1/z}
+        const float mx = ra.x, my = ra.y, hA = ra.z, hB = ra.w, hC = rb.x, no = rb.y, cr = rb.z, cg = rb.w, cb = rc.x,
+                    iz = rc.y;
         // e = hA dx^2 + hC dy^2 + hB dx dy, per pixel exactly quad_form()'s rounding sequence
         const float dx = mx - pxf;
         const float tt = __fmul_rn(__fmul_rn(hA, dx), dx);
         const float vv = __fmul_rn(hB, dx);
         if (both & bitm) {
           // packed path: both pixels in one instruction stream
-          const f32x2 dy2 = add2(my2, pk2(npyA, npyB));
-          f32x2 e2 = fma2(mul2(hC2, dy2), dy2, pk2(tt, tt));
+          const f32x2 dy2 = add2(pk2(my, my), pk2(npyA, npyB));
+          f32x2 e2 = fma2(mul2(pk2(hC, hC), dy2), dy2, pk2(tt, tt));
           e2 = fma2(pk2(vv, vv), dy2, e2);
           float eA, eB;
           upk2(e2, eA, eB);
           float naA, naB;
-          upk2(mul2(no2, pk2(ex2_approx(-eA), ex2_approx(-eB))), naA, naB);   // (-opacity) G
+          upk2(mul2(pk2(no, no), pk2(ex2_approx(-eA), ex2_approx(-eB))), naA, naB);   // (-opacity) G
           naA = fmaxf(naA, -0.99f);
           naB = fmaxf(naB, -0.99f);
           const f32x2 na2 = pk2(naA, naB), nT2 = pk2(nTA, nTB);
@@ -166,17 +162,15 @@ __global__ void __launch_bounds__(128) render_forward_kernel(const GsrView v, co
           okA = okA && !satA;
           okB = okB && !satB;
           const f32x2 w2 = pk2(okA ? wA : 0.f, okB ? wB : 0.f);
-          upk2(fma2(r2, w2, pk2(c0A, c0B)), c0A, c0B);
-          upk2(fma2(g2, w2, pk2(c1A, c1B)), c1A, c1B);
-          upk2(fma2(bl2, w2, pk2(c2A, c2B)), c2A, c2B);
-          upk2(fma2(iz2, w2, pk2(dA, dB)), dA, dB);
+          upk2(fma2(pk2(cr, cr), w2, pk2(c0A, c0B)), c0A, c0B);
+          upk2(fma2(pk2(cg, cg), w2, pk2(c1A, c1B)), c1A, c1B);
+          upk2(fma2(pk2(cb, cb), w2, pk2(c2A, c2B)), c2A, c2B);
+          upk2(fma2(pk2(iz, iz), w2, pk2(dA, dB)), dA, dB);
           nTA = okA ? tA : nTA;
           nTB = okB ? tB : nTB;
           okA_bits |= okA ? bitm : 0u;
           okB_bits |= okB ? bitm : 0u;
         } else {
-          upk2(my2, my, unused); upk2(hC2, hC, unused); upk2(no2, no, unused); upk2(r2, cr, unused);
-          upk2(g2, cg, unused); upk2(bl2, cb, unused); upk2(iz2, iz, unused);
           if (maskA & bitm) GSR_FWD_ONE(A) else GSR_FWD_ONE(B)
         }
       }
