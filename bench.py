@@ -489,12 +489,12 @@ def run_ours(args):
         s["share_of_kernel_time"] = s["ms_per_frame"] * s["calls"] / stage_sum
     dom = max(stages, key=lambda s: s["ms_per_frame"] * s["calls"])
     traffic, traffic_src = None, None
-    tp = os.path.join(ROOT, "profiles", "r1_v4_traffic.json")      # dram bytes per launch from the ncu --set full capture
+    tp = os.path.join(ROOT, "profiles", "r1_v5_traffic.json")      # dram bytes per launch from the ncu --set full capture
     if os.path.exists(tp):
         tj = json.load(open(tp))
         ent = tj.get(dom["stage"] + "_kernel") or tj.get({"sort": "onesweep_pass_kernel"}.get(dom["stage"], ""))
         if ent:
-            traffic, traffic_src = ent["dram_bytes_per_launch"], "profiles/r1_v4_traffic.json: " + tj.get("_source", "")
+            traffic, traffic_src = ent["dram_bytes_per_launch"], "profiles/r1_v5_traffic.json: " + tj.get("_source", "")
     roofline = {"kernel": dom["stage"], "bound": "hbm", "achieved": dom["GBps"], "peak": hbm_peak, "unit": "GB/s",
                 "frac": dom["hbm_frac"], "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": dom["algorithmic_bytes"], "ms_per_launch": dom["ms_per_frame"],
@@ -522,7 +522,7 @@ def run_ours(args):
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "stages": stages,
         "cpu_baseline": cpu_baseline,
     }
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -580,11 +580,28 @@ def run_reference(args):
                        "note": "one step = one full frame on the CPU; steps capped at 20 so the run ends within a minute; wall %.1f s" % wall},
             "cpu_baseline": cb, "gpu_launches": 0,
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
+
+
+_JSON_OUT = None
+
+
+def emit(line: dict) -> None:
+    """The ONE JSON line goes to the process's original stdout; everything else that libraries write to fd 1 during
+    the run (NCCL prints its version banner there) was redirected to stderr by main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_OUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_OUT, data)
 
 
 def main():
+    global _JSON_OUT
     args = parse_args()
+    sys.stdout.flush()
+    _JSON_OUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
