@@ -373,7 +373,11 @@ def run_ours(args):
                 sl["gt"].copy_(gt_host[j], non_blocking=True)
                 sl["ready"].record(copy_stream)
 
+        from gaussian_splatting_lightning_b200.training import photometric_loss
+        loss_fns = {"l1": l1_loss, "full": lambda c_, g_: photometric_loss(c_[None], g_[None], 0.2)[0]}
+
         def e2e_view(j):
+            loss_fn = loss_fns[e2e_loss[0]]
             st = torch.cuda.current_stream()                 # ViewStreams.run: view j on stream j mod n
             if j + n_slots - 1 < vpr:
                 upload(j + n_slots - 1)                      # its slot was freed by view j-1; overlaps the rendering
@@ -388,7 +392,7 @@ def run_ours(args):
                     means3D=params["means3D"], means2D=sp, shs=params["shs"], colors_precomp=None,
                     opacities=params["opacities"], scales=params["scales"], rotations=params["rotations"],
                     cov3D_precomp=None)
-            loss = l1_loss(color, gt)
+            loss = loss_fn(color, gt)
             loss.backward()
             loss_host[j].copy_(loss.detach(), non_blocking=True)
             sl["free"].record(st)
@@ -404,12 +408,18 @@ def run_ours(args):
             main.synchronize()                               # the step's result (losses) is on the host
             return float(loss_host.sum())
 
+        e2e_loss = ["l1"]
         ms_e2e, _, _ = timed(e2e_step, K, 2)
+        e2e_loss[0] = "full"     # the reference's training loss: 0.8 L1 + 0.2 (1 - SSIM), one fused kernel
+        ms_e2e_full, _, _ = timed(e2e_step, K, 2)
+        e2e_loss[0] = "l1"
         h2d = vpr * (3 * H * W * 4 + 38 * 4)
         e2e = {"value": frames / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": vpr * 4,
                "what": "GaussianRasterizer autograd API + fused L1 loss (training.l1_loss) with fused gradient accumulation "
                        "(accumulate_gradients_into) on the same CUDA streams as `value`; per view: pinned GT image and "
-                       "camera H2D (copy stream, ring of streams+1 slots, inside the timed region), loss D2H"}
+                       "camera H2D (copy stream, ring of streams+1 slots, inside the timed region), loss D2H",
+               "with_reference_training_loss": {"value": frames / (ms_e2e_full / 1e3), "unit": UNIT, "what": "same, with "
+                   "the loss of GSLightningModule.calculate_loss: 0.8 L1 + 0.2 (1 - fused_ssim) (training.photometric_loss)"}}
         # ---- the training-step neighbours of the path, each one launch, HBM bound --------
         from gaussian_splatting_lightning_b200.training import FusedAdam, densify_fold
 

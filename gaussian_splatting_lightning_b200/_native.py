@@ -69,7 +69,7 @@ EXPORTED_SYMBOLS = [
     "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count", "gsr_profile_enable", "gsr_profile_reset",
     "gsr_profile_collect", "gsr_profile_stage_count", "gsr_profile_stage_name", "gsr_profile_stage_ms",
     "gsr_profile_stage_calls", "gsr_l1_loss_scratch_bytes", "gsr_l1_loss", "gsr_adam_step", "gsr_densify_fold", "gsr_fused_ssim_scratch_bytes",
-    "gsr_fused_ssim",
+    "gsr_fused_ssim", "gsr_photometric_loss",
 ]
 
 _lib = None
@@ -126,6 +126,9 @@ def lib():
     L.gsr_fused_ssim.restype = C.c_int
     L.gsr_fused_ssim.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float,
                                  C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gsr_photometric_loss.restype = C.c_int
+    L.gsr_photometric_loss.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.gsr_adam_step.restype = C.c_int
     L.gsr_adam_step.argtypes = [C.POINTER(GsrAdamGroup), C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double,
                                 C.c_int32, C.c_void_p]

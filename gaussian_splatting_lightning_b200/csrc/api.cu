@@ -355,8 +355,22 @@ int gsr_fused_ssim(const float* img1, const float* img2, int32_t planes, int32_t
   if (planes > 65535) return fail(GSR_ELIMIT, "fused_ssim: more than 65535 image planes");
   if (padding_valid && (H <= 10 || W <= 10)) return fail(GSR_EINVAL, "fused_ssim: padding 'valid' needs H, W > 10");
   if (((uintptr_t)scratch) & 15) return fail(GSR_EINVAL, "fused_ssim: scratch must be 16-byte aligned");
-  GSR_CUDA(gsr::launch_fused_ssim(img1, img2, planes, H, W, C1, C2, padding_valid ? 1 : 0, dL_dimg1, out_ssim, scratch,
-                                  (cudaStream_t)stream), "fused_ssim kernel");
+  GSR_CUDA(gsr::launch_fused_ssim(img1, img2, planes, H, W, C1, C2, padding_valid ? 1 : 0, 0.f, 1.f, 0.f, dL_dimg1, nullptr,
+                                  out_ssim, nullptr, scratch, (cudaStream_t)stream), "fused_ssim kernel");
+  return GSR_OK;
+}
+
+int gsr_photometric_loss(const float* image, const float* target, int32_t planes, int32_t H, int32_t W, float w_ssim,
+                         float* dL_dimage, float* out_loss, float* out_l1, float* out_ssim, void* scratch,
+                         void* stream) {
+  if (planes <= 0 || H <= 0 || W <= 0 || !image || !target || !out_loss || !scratch)
+    return fail(GSR_EINVAL, "photometric_loss: bad arguments");
+  if (planes > 65535) return fail(GSR_ELIMIT, "photometric_loss: more than 65535 image planes");
+  if (((uintptr_t)scratch) & 15) return fail(GSR_EINVAL, "photometric_loss: scratch must be 16-byte aligned");
+  // (1 - w) L1 + w (1 - ssim) = (1 - w) L1 - w ssim + w
+  GSR_CUDA(gsr::launch_fused_ssim(image, target, planes, H, W, 0.01f * 0.01f, 0.03f * 0.03f, 0, 1.f - w_ssim, -w_ssim,
+                                  w_ssim, dL_dimage, out_loss, out_ssim, out_l1, scratch, (cudaStream_t)stream),
+           "photometric_loss kernel");
   return GSR_OK;
 }
 

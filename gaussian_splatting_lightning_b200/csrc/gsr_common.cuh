@@ -255,7 +255,8 @@ cudaError_t launch_l1_loss(const float* image, const float* target, long long n,
                            void* scratch, cudaStream_t s);
 size_t ssim_scratch_bytes(int planes, int H, int W);
 cudaError_t launch_fused_ssim(const float* img1, const float* img2, int planes, int H, int W, float C1, float C2,
-                              int valid, float* dL_dimg1, float* out_mean, void* scratch, cudaStream_t s);
+                              int valid, float w_l1, float w_ssim, float w_const, float* dL_dimg1, float* out_loss,
+                              float* out_ssim, float* out_l1, void* scratch, cudaStream_t s);
 cudaError_t launch_adam(const struct GsrAdamGroup* groups, int num_groups, int step, double beta1, double beta2,
                         double eps, int zero_grad, cudaStream_t s);
 cudaError_t launch_densify_fold(int P, const float* d_max_radii, const float* d_accum, const float* d_count,

@@ -135,12 +135,17 @@ __constant__ float kGauss[11] = {0.001028380123898387f, 0.0075987582094967365f, 
 // a loaded value feeds up to 11 x 3 multiply-adds from registers.
 constexpr int SS_N1 = SS_H1 * SS_W1, SS_NH = SS_H1 * SS_W2, SS_N2 = SS_H2 * SS_W2;
 
+// loss = w_l1 * mean|x - y| + w_ssim * ssim + w_const   (fused_ssim alone: 0, 1, 0; the reference's training loss
+// (1 - w) L1 + w (1 - ssim), gs_lightning_module.py:281-284: 1 - w, -w, w).  inv_n_l1 = 1 / (planes H W).
+struct SsimLossWeights { float w_l1, w_ssim, w_const, inv_n_l1; };
+
 template <bool GRAD>
 __global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* __restrict__ img1,
                                                                 const float* __restrict__ img2, int H, int W, float C1,
                                                                 float C2, int valid, float inv_n,
-                                                                float* __restrict__ dL_dimg1, float* __restrict__ out_mean,
-                                                                double* partials, unsigned int* ticket) {
+                                                                const SsimLossWeights lw, float* __restrict__ dL_dimg1,
+                                                                float* out_loss, float* out_ssim, float* out_l1, double* partials,
+                                                                unsigned int* ticket) {
   using gsr::f32x2; using gsr::pk2; using gsr::upk2; using gsr::fma2; using gsr::mul2;
   extern __shared__ __align__(16) float smem[];
   float2* sxy = reinterpret_cast<float2*>(smem);                    // [52][52] (x, y)
@@ -211,7 +216,7 @@ __global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* 
   }
   __syncthreads();
   // 3. vertical sums -> statistics -> m and its three partial derivatives: a thread owns 3 consecutive rows of one column
-  float local = 0.f;
+  float local = 0.f, local_l1 = 0.f;
   for (int it = tid; it < (SS_H2 / 3) * SS_W2; it += SS_THREADS) {
     const int rs = it / SS_W2, c = it - rs * SS_W2, r0 = rs * 3;
     f32x2 vA[13], vB[13];
@@ -251,6 +256,10 @@ __global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* 
       const float m = CD * rAB;
       const bool centre = r >= SS_R && r < SS_R + SS_TY && c >= SS_R && c < SS_R + SS_TX;
       if (centre && counted) local += m;
+      if (centre && in_img) {
+        const float2 px = sxy[(r + SS_R) * SS_W1 + c + SS_R];
+        local_l1 += fabsf(px.x - px.y);
+      }
       if (GRAD) {
         const float wgt = counted ? inv_n : 0.f;
         const float wm = wgt * m;                                     // w C D / (A B)
@@ -316,45 +325,61 @@ __global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* 
           float t0, t1;
           upk2(t01, t0, t1);
           const float2 px = sxy[(r0 + j + 2 * SS_R) * SS_W1 + c + 2 * SS_R];
-          dL_dimg1[plane + (size_t)y * W + x] = t0 + 2.f * px.x * t1 + px.y * t2;
+          const float dss = t0 + 2.f * px.x * t1 + px.y * t2;          // d ssim / d x
+          const float d = px.x - px.y;
+          const float sg = (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f);
+          dL_dimg1[plane + (size_t)y * W + x] = lw.w_ssim * dss + (lw.w_l1 * lw.inv_n_l1) * sg;
         }
       }
     }
   }
 
-  // deterministic sum of m: CTA partial in double, the last CTA adds the partials in index order
-  double v = (double)local;
+  // deterministic sums of m and |x - y|: CTA partials in double, the last CTA adds the partials in index order
+  double v = (double)local, v1 = (double)local_l1;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-  __shared__ double warp_sum[SS_THREADS / 32];
+  for (int o = 16; o > 0; o >>= 1) {
+    v += __shfl_down_sync(0xffffffffu, v, o);
+    v1 += __shfl_down_sync(0xffffffffu, v1, o);
+  }
+  __shared__ double warp_sum[2][SS_THREADS / 32];
   __shared__ bool last;
-  if ((tid & 31) == 0) warp_sum[tid >> 5] = v;
+  if ((tid & 31) == 0) { warp_sum[0][tid >> 5] = v; warp_sum[1][tid >> 5] = v1; }
   __syncthreads();
   const unsigned int nblocks = gridDim.x * gridDim.y * gridDim.z;
   const unsigned int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
   if (tid == 0) {
-    double s = 0.0;
+    double s = 0.0, s1 = 0.0;
 #pragma unroll
-    for (int w = 0; w < SS_THREADS / 32; ++w) s += warp_sum[w];
-    partials[bid] = s;
+    for (int w = 0; w < SS_THREADS / 32; ++w) { s += warp_sum[0][w]; s1 += warp_sum[1][w]; }
+    partials[2 * bid] = s;
+    partials[2 * bid + 1] = s1;
     __threadfence();
     last = (atomicAdd(ticket, 1u) == nblocks - 1);
   }
   __syncthreads();
   if (!last) return;
   __threadfence();
-  double t = 0.0;
-  for (unsigned int i = tid; i < nblocks; i += SS_THREADS) t += ((volatile double*)partials)[i];
+  double t = 0.0, t1 = 0.0;
+  for (unsigned int i = tid; i < nblocks; i += SS_THREADS) {
+    t += ((volatile double*)partials)[2 * i];
+    t1 += ((volatile double*)partials)[2 * i + 1];
+  }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+  for (int o = 16; o > 0; o >>= 1) {
+    t += __shfl_down_sync(0xffffffffu, t, o);
+    t1 += __shfl_down_sync(0xffffffffu, t1, o);
+  }
   __syncthreads();
-  if ((tid & 31) == 0) warp_sum[tid >> 5] = t;
+  if ((tid & 31) == 0) { warp_sum[0][tid >> 5] = t; warp_sum[1][tid >> 5] = t1; }
   __syncthreads();
   if (tid == 0) {
-    double s = 0.0;
+    double s = 0.0, s1 = 0.0;
 #pragma unroll
-    for (int w = 0; w < SS_THREADS / 32; ++w) s += warp_sum[w];
-    *out_mean = (float)(s * (double)inv_n);
+    for (int w = 0; w < SS_THREADS / 32; ++w) { s += warp_sum[0][w]; s1 += warp_sum[1][w]; }
+    const float ssim = (float)(s * (double)inv_n), l1 = (float)(s1 * (double)lw.inv_n_l1);
+    if (out_loss) *out_loss = lw.w_l1 * l1 + lw.w_ssim * ssim + lw.w_const;
+    if (out_ssim) *out_ssim = ssim;
+    if (out_l1) *out_l1 = l1;
     *ticket = 0u;
   }
 }
@@ -364,11 +389,13 @@ __global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* 
 namespace gsr {
 size_t ssim_scratch_bytes(int planes, int H, int W) {
   const size_t blocks = (size_t)((W + SS_TX - 1) / SS_TX) * ((H + SS_TY - 1) / SS_TY) * (size_t)(planes > 0 ? planes : 1);
-  return 128 + blocks * sizeof(double);
+  return 128 + blocks * 2 * sizeof(double);
 }
 
+// *out_loss = w_l1 * L1 + w_ssim * ssim + w_const, *out_ssim = ssim, *out_l1 = L1 (each may be NULL)
 cudaError_t launch_fused_ssim(const float* img1, const float* img2, int planes, int H, int W, float C1, float C2,
-                              int valid, float* dL_dimg1, float* out_mean, void* scratch, cudaStream_t s) {
+                              int valid, float w_l1, float w_ssim, float w_const, float* dL_dimg1, float* out_loss,
+                              float* out_ssim, float* out_l1, void* scratch, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(fused_ssim_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS_SMEM);
@@ -379,15 +406,18 @@ cudaError_t launch_fused_ssim(const float* img1, const float* img2, int planes, 
   const long long hh = valid ? H - 2 * SS_R : H, ww = valid ? W - 2 * SS_R : W;
   const double n = (double)planes * (double)(hh > 0 ? hh : 0) * (double)(ww > 0 ? ww : 0);
   const float inv_n = n > 0 ? (float)(1.0 / n) : 0.f;
+  SsimLossWeights lw;
+  lw.w_l1 = w_l1; lw.w_ssim = w_ssim; lw.w_const = w_const;
+  lw.inv_n_l1 = (float)(1.0 / ((double)planes * H * W));
   dim3 grid((W + SS_TX - 1) / SS_TX, (H + SS_TY - 1) / SS_TY, planes);
   double* partials = reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + 128);
   unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
   if (dL_dimg1)
-    fused_ssim_kernel<true><<<grid, SS_THREADS, SS_SMEM, s>>>(img1, img2, H, W, C1, C2, valid, inv_n, dL_dimg1, out_mean,
-                                                             partials, ticket);
+    fused_ssim_kernel<true><<<grid, SS_THREADS, SS_SMEM, s>>>(img1, img2, H, W, C1, C2, valid, inv_n, lw, dL_dimg1, out_loss,
+                                                             out_ssim, out_l1, partials, ticket);
   else
-    fused_ssim_kernel<false><<<grid, SS_THREADS, SS_SMEM, s>>>(img1, img2, H, W, C1, C2, valid, inv_n, nullptr, out_mean,
-                                                              partials, ticket);
+    fused_ssim_kernel<false><<<grid, SS_THREADS, SS_SMEM, s>>>(img1, img2, H, W, C1, C2, valid, inv_n, lw, nullptr, out_loss,
+                                                              out_ssim, out_l1, partials, ticket);
   count_launch();
   return cudaGetLastError();
 }

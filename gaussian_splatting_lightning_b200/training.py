@@ -194,3 +194,43 @@ def fused_ssim(img1: torch.Tensor, img2: torch.Tensor, padding: str = "same", tr
     (gs_lightning/lightning/gs_lightning_module.py:100,279)."""
     assert padding in ("same", "valid")
     return _FusedSSIM.apply(img1, img2.detach(), padding == "valid", train)
+
+
+class _PhotometricLoss(torch.autograd.Function):
+    """(1 - w) L1 + w (1 - ssim) and its gradient from ONE launch (gsr_photometric_loss)."""
+
+    @staticmethod
+    def forward(ctx, image, target, w_ssim):
+        _need_cuda(image, "photometric_loss")
+        if image.dim() != 4 or image.shape != target.shape:
+            raise RuntimeError(f"photometric_loss: expected two (B, C, H, W) tensors of one shape, got "
+                               f"{tuple(image.shape)} and {tuple(target.shape)}")
+        dev = image.device
+        a, b = N.f32c(image), N.f32c(target, dev)
+        B, CH, H, W = a.shape
+        out = torch.empty(3, dtype=torch.float32, device=dev)          # loss, L1, mean SSIM
+        unit = torch.empty_like(a) if ctx.needs_input_grad[0] else None
+        with torch.cuda.device(dev):
+            scratch = torch.zeros(N.lib().gsr_fused_ssim_scratch_bytes(B * CH, H, W), dtype=torch.uint8, device=dev)
+            p = out.data_ptr()
+            N.check(N.lib().gsr_photometric_loss(N.ptr(a), N.ptr(b), B * CH, H, W, float(w_ssim), N.ptr(unit), p, p + 4,
+                                                 p + 8, N.ptr(scratch), N.stream_ptr(dev)), "gsr_photometric_loss")
+        ctx.unit = unit
+        loss, l1, ssim = out[0], out[1], out[2]
+        ctx.mark_non_differentiable(l1, ssim)
+        return loss, l1, ssim
+
+    @staticmethod
+    def backward(ctx, grad_out, _g1, _g2):
+        if ctx.unit is None:
+            return None, None, None
+        return ctx.unit * grad_out, None, None
+
+
+def photometric_loss(image: torch.Tensor, target: torch.Tensor, w_ssim: float = 0.2):
+    """GSLightningModule.calculate_loss's loss (gs_lightning/lightning/gs_lightning_module.py:278-291) for (B, C, H, W)
+    images: returns (loss, recon, ssim) with loss = recon * (1 - w_ssim) + ssim * w_ssim, recon = nn.L1Loss(),
+    ssim = 1 - fused_ssim(image, target) -- the three entries of the reference's loss_log.  One kernel reads the two
+    images once and writes the combined gradient."""
+    loss, l1, mean_ssim = _PhotometricLoss.apply(image, target.detach(), float(w_ssim))
+    return loss, l1, 1.0 - mean_ssim

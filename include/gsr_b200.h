@@ -207,6 +207,14 @@ size_t gsr_fused_ssim_scratch_bytes(int32_t planes, int32_t H, int32_t W);
 int gsr_fused_ssim(const float* img1, const float* img2, int32_t planes, int32_t H, int32_t W, float C1, float C2,
                    int32_t padding_valid, float* dL_dimg1, float* out_ssim, void* scratch, void* stream);
 
+/* The training loss of GSLightningModule.calculate_loss (gs_lightning_module.py:278-284) in ONE launch:
+ *   *out_loss = (1 - w_ssim) * L1(image, target) + w_ssim * (1 - fused_ssim(image, target))       (padding "same")
+ * and, when dL_dimage is not NULL, d(out_loss)/d(image).  *out_l1 (may be NULL) receives the L1 term and
+ * *out_ssim (may be NULL) the mean SSIM (the reference logs recon = L1 and ssim = 1 - mean SSIM).  Same kernel,
+ * scratch and determinism as gsr_fused_ssim: the images are read once for both terms. */
+int gsr_photometric_loss(const float* image, const float* target, int32_t planes, int32_t H, int32_t W, float w_ssim,
+                         float* dL_dimage, float* out_loss, float* out_l1, float* out_ssim, void* scratch, void* stream);
+
 /* torch.optim.Adam over the parameter groups of gs_lightning_module.py:120-127 in ONE launch
  * (configs/*.yaml: eps 1e-15, default betas, no weight decay, no amsgrad).  `step` is the 1-based step
  * count after the increment, as torch uses it for the bias corrections; lr, betas and eps are doubles and are

@@ -233,3 +233,24 @@ def test_fused_ssim_matches_the_reference_cuda_kernels(shape, padding):
     assert abs(float(val.detach()) - float(ref_val)) <= 2e-6
     s = float(ref_grad.abs().max())
     assert float((x.grad - ref_grad).abs().max()) <= 1e-4 * s
+
+
+@pytest.mark.parametrize("shape,w", [((1, 3, 200, 320), 0.2), ((2, 3, 67, 45), 0.5), ((1, 3, 33, 31), 0.0)])
+def test_photometric_loss_equals_the_two_terms(shape, w):
+    """(1 - w) L1 + w (1 - ssim) from one launch against the oracle's two terms (and the reference's operators)."""
+    from gaussian_splatting_lightning_b200.training import photometric_loss
+    g = torch.Generator().manual_seed(13)
+    a = torch.rand(shape, generator=g)
+    b = (a + 0.2 * torch.rand(shape, generator=g)).clamp(0, 1)
+    l1_val, l1_grad = OT.l1_loss(a.numpy(), b.numpy())
+    ss_val, ss_grad = OT.fused_ssim(a.numpy(), b.numpy(), "same")
+    want = (1 - w) * float(l1_val) + w * (1 - ss_val)
+    want_grad = (1 - w) * l1_grad.astype(np.float64) - w * ss_grad
+    x = a.to(U.DEV).requires_grad_(True)
+    loss, recon, ssim = photometric_loss(x, b.to(U.DEV), w)
+    (2.0 * loss).backward()
+    assert abs(float(loss.detach()) - want) <= 3e-6
+    assert abs(float(recon) - float(l1_val)) <= 2e-7 and abs(float(ssim) - (1 - ss_val)) <= 2e-6
+    assert not recon.requires_grad and not ssim.requires_grad
+    s = float(np.abs(want_grad).max())
+    assert float(np.abs(x.grad.cpu().numpy() - 2.0 * want_grad).max()) <= 2e-4 * s
