@@ -26,40 +26,18 @@
 //     is the exact negation of the textbook one, so the sums are bit-identical to a positive-sign evaluation;
 //   * lanes whose pixel the splat does not reach run the same instruction stream with
 //     alpha = 0 (an exact no-op of the recurrences), so the hit loop has no divergent branch;
-//   * a lane first adds its two pixels' sums; the ten sums are then reduced over the warp's 32 lanes with a
-//     recursive-halving exchange: at each xor-shuffle step a lane keeps half of its values and sends the other
-//     half, so the reduction costs 5+3+2+1+1 = 12 shuffles instead of 50, and ends with the ten sums spread
-//     over ten lanes;
-//   * those ten lanes issue ONE red.global.add.f32 instruction per (warp, splat) into a
-//     48-byte-per-Gaussian accumulator row -- 1/64 of the atomics of the per-pixel scheme.
+//   * a lane first adds its two pixels' sums and parks the ten sums in a per-warp transposition buffer in shared
+//     memory (row = visit slot * 10 + sum, column = lane, row stride 36 floats: conflict-free 128-bit row reads);
+//     every third visit the warp adds the 30 parked rows, one row per lane (8 LDS.128 + 31 adds), and 30 lanes issue
+//     ONE red.global.add.f32 instruction into the 48-byte-per-Gaussian accumulator rows -- 1/64 of the atomics of
+//     the per-pixel scheme.  Measured against a recursive-halving shuffle reduction (12 shuffles + 22 selects + 12
+//     adds per visit): 0.873 -> 0.850 ms; a hybrid (one shuffle level, then shared memory) was slower (0.900 ms).
 #include "gsr_common.cuh"
 #include "render_common.cuh"
 
 namespace gsr {
 
 namespace {
-
-// After warp_reduce10 the sum of value `slot` lives in the lanes for which this returns
-// slot (even lanes only); -1 elsewhere.
-__device__ __forceinline__ int reduce10_slot(int lane) {
-  if (lane & 1) return -1;
-  const int tI = (lane & 2) ? 1 : 0;
-  const int uI = ((lane & 4) ? 2 : 0) + tI;
-  if (lane & 8) {
-    if (uI >= 2) return -1;
-  } else {
-    if (uI >= 3) return -1;
-  }
-  const int wI = ((lane & 8) ? 3 : 0) + uI;
-  return ((lane & 16) ? 5 : 0) + wI;
-}
-
-#define GSR_XCHG(dst, lo_val, hi_val, pred, bit)                            \
-  {                                                                         \
-    const float keep_ = (pred) ? (hi_val) : (lo_val);                       \
-    const float send_ = (pred) ? (lo_val) : (hi_val);                       \
-    dst = keep_ + __shfl_xor_sync(0xffffffffu, send_, (bit));               \
-  }
 
 }  // namespace
 
@@ -70,6 +48,11 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
   __shared__ float4 sRec[GSR_REC_PLANES][256];  // staged batch, planes as described in render_common.cuh
   __shared__ uint32_t sHit[8][8];               // [chunk of the batch][sub-tile column]
   __shared__ uint32_t s_warp_max[4];
+  // reduction over the warp's lanes by transposition through shared memory: RED_STRIDE = 36 floats per row keeps the
+  // rows 16-byte aligned and the 128-bit row reads of a quarter warp on 32 distinct banks
+  constexpr int RED_STRIDE = 36;
+  __shared__ __align__(16) float sRed[4][30 * RED_STRIDE];
+  __shared__ uint32_t sRedId[4][4];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
@@ -80,8 +63,29 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
   const float pxf = (float)pxi;
   const int colA = (warp >> 1) * 4 + (warp & 1), colB = colA + 2;
   const uint2 range = ranges[tile];
-  const int slot = reduce10_slot(lane);
-  const bool b16 = lane & 16, b8 = lane & 8, b4 = lane & 4, b2 = lane & 2;
+  float* red = sRed[warp];
+  uint32_t* red_id = sRedId[warp];
+  const int red_visit = lane / 10, red_sum = lane - red_visit * 10;   // the row lane `lane` adds at a flush
+  int nslot = 0;                                                       // visits parked in the buffer (warp-uniform)
+
+// add the parked rows: lane l < 10 nslot owns row l = (visit, sum) and issues its red.global.add
+#define GSR_BWD_FLUSH()                                                                                   \
+  {                                                                                                       \
+    __syncwarp();                                                                                         \
+    if (lane < nslot * 10) {                                                                              \
+      const float4* row = reinterpret_cast<const float4*>(red + lane * RED_STRIDE);                       \
+      const float4 r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3], r4 = row[4], r5 = row[5], r6 = row[6],  \
+                   r7 = row[7];                                                                           \
+      const float t0 = (r0.x + r0.y) + (r0.z + r0.w), t1 = (r1.x + r1.y) + (r1.z + r1.w);                 \
+      const float t2 = (r2.x + r2.y) + (r2.z + r2.w), t3 = (r3.x + r3.y) + (r3.z + r3.w);                 \
+      const float t4 = (r4.x + r4.y) + (r4.z + r4.w), t5 = (r5.x + r5.y) + (r5.z + r5.w);                 \
+      const float t6 = (r6.x + r6.y) + (r6.z + r6.w), t7 = (r7.x + r7.y) + (r7.z + r7.w);                 \
+      const float sum = ((t0 + t1) + (t2 + t3)) + ((t4 + t5) + (t6 + t7));                                \
+      atomicAdd(grad_acc + (size_t)red_id[red_visit] * 12 + red_sum, sum);                                \
+    }                                                                                                     \
+    __syncwarp();                                                                                         \
+    nslot = 0;                                                                                            \
+  }
   const uint32_t aRec = (uint32_t)__cvta_generic_to_shared(sRec);
 
   // the binning buffer describes itself (BinningHeader): sorted point list + hit words
@@ -260,29 +264,21 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
           if (maskA & bitm) GSR_BWD_ONE(A) else GSR_BWD_ONE(B)
         }
 
-        // recursive-halving reduction of the ten sums over the 32 lanes
-        float w0, w1, w2r, w3, w4;
-        GSR_XCHG(w0, s0, s5, b16, 16);
-        GSR_XCHG(w1, s1, s6, b16, 16);
-        GSR_XCHG(w2r, s2, s7, b16, 16);
-        GSR_XCHG(w3, s3, s8, b16, 16);
-        GSR_XCHG(w4, s4, s9, b16, 16);
-        float u0, u1, u2;
-        GSR_XCHG(u0, w0, w3, b8, 8);
-        GSR_XCHG(u1, w1, w4, b8, 8);
-        GSR_XCHG(u2, w2r, 0.f, b8, 8);
-        float t0, t1;
-        GSR_XCHG(t0, u0, u2, b4, 4);
-        GSR_XCHG(t1, u1, 0.f, b4, 4);
-        float sum;
-        GSR_XCHG(sum, t0, t1, b2, 2);
-        sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-        if (slot >= 0) {
-          atomicAdd(grad_acc + (size_t)__float_as_uint(rc.w) * 12 + slot, sum);
+        // park the lane's ten sums in the warp's transposition buffer (row = visit slot * 10 + sum, column = lane);
+        // every third visit the warp adds the 30 rows, one row per lane (GSR_BWD_FLUSH)
+        {
+          float* dst = red + nslot * (10 * RED_STRIDE) + lane;
+          dst[0 * RED_STRIDE] = s0; dst[1 * RED_STRIDE] = s1; dst[2 * RED_STRIDE] = s2; dst[3 * RED_STRIDE] = s3;
+          dst[4 * RED_STRIDE] = s4; dst[5 * RED_STRIDE] = s5; dst[6 * RED_STRIDE] = s6; dst[7 * RED_STRIDE] = s7;
+          dst[8 * RED_STRIDE] = s8; dst[9 * RED_STRIDE] = s9;
+          if (lane == 0) red_id[nslot] = __float_as_uint(rc.w);
+          if (++nslot == 3) GSR_BWD_FLUSH()
         }
       }
     }
   }
+  if (nslot) GSR_BWD_FLUSH()
+#undef GSR_BWD_FLUSH
 #undef GSR_BWD_ONE
 }
 
