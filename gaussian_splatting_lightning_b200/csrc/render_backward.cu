@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
   const int colA = (warp >> 1) * 4 + (warp & 1), colB = colA + 2;
   const uint2 range = ranges[tile];
   float* red = sRed[warp];
+  const uint32_t red_addr = (uint32_t)__cvta_generic_to_shared(red) + (uint32_t)lane * 4u;
   uint32_t* red_id = sRedId[warp];
   const int red_visit = lane / 10, red_sum = lane - red_visit * 10;   // the row lane `lane` adds at a flush
   int nslot = 0;                                                       // visits parked in the buffer (warp-uniform)
@@ -267,11 +268,12 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
         // park the lane's ten sums in the warp's transposition buffer (row = visit slot * 10 + sum, column = lane);
         // every third visit the warp adds the 30 rows, one row per lane (GSR_BWD_FLUSH)
         {
-          float* dst = red + nslot * (10 * RED_STRIDE) + lane;
-          dst[0 * RED_STRIDE] = s0; dst[1 * RED_STRIDE] = s1; dst[2 * RED_STRIDE] = s2; dst[3 * RED_STRIDE] = s3;
-          dst[4 * RED_STRIDE] = s4; dst[5 * RED_STRIDE] = s5; dst[6 * RED_STRIDE] = s6; dst[7 * RED_STRIDE] = s7;
-          dst[8 * RED_STRIDE] = s8; dst[9 * RED_STRIDE] = s9;
-          if (lane == 0) red_id[nslot] = __float_as_uint(rc.w);
+          const uint32_t dst = red_addr + (uint32_t)nslot * (10u * RED_STRIDE * 4u);
+          sts32<0 * RED_STRIDE * 4>(dst, s0); sts32<1 * RED_STRIDE * 4>(dst, s1); sts32<2 * RED_STRIDE * 4>(dst, s2);
+          sts32<3 * RED_STRIDE * 4>(dst, s3); sts32<4 * RED_STRIDE * 4>(dst, s4); sts32<5 * RED_STRIDE * 4>(dst, s5);
+          sts32<6 * RED_STRIDE * 4>(dst, s6); sts32<7 * RED_STRIDE * 4>(dst, s7); sts32<8 * RED_STRIDE * 4>(dst, s8);
+          sts32<9 * RED_STRIDE * 4>(dst, s9);
+          red_id[nslot] = __float_as_uint(rc.w);   // every lane stores the same word: one wavefront, no predicate
           if (++nslot == 3) GSR_BWD_FLUSH()
         }
       }

@@ -69,6 +69,10 @@ __device__ __forceinline__ uint32_t lds32u(uint32_t addr) {
   asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFF));
   return v;
 }
+template <int OFF>
+__device__ __forceinline__ void sts32(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0+%1], %2;" : : "r"(addr), "n"(OFF), "f"(v) : "memory");
+}
 // index of the most significant set bit (x != 0)
 __device__ __forceinline__ int msb_index(uint32_t x) {
   int r;
