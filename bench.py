@@ -549,6 +549,12 @@ def cpu_oracle_frames_per_s(workload, scene_cpu, cam_host, repeats):
     rng = np.random.default_rng(0)
     dC = rng.standard_normal((3, H, W)).astype(np.float32)
     dD = rng.standard_normal((H, W)).astype(np.float32)
+    # all the host cores this process may use, whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1)
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    oracle.set_num_threads(max(1, avail))
     cores = oracle.num_threads()
     times = []
     for _ in range(repeats):
