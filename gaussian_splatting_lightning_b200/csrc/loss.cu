@@ -396,13 +396,10 @@ size_t ssim_scratch_bytes(int planes, int H, int W) {
 cudaError_t launch_fused_ssim(const float* img1, const float* img2, int planes, int H, int W, float C1, float C2,
                               int valid, float w_l1, float w_ssim, float w_const, float* dL_dimg1, float* out_loss,
                               float* out_ssim, float* out_l1, void* scratch, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(fused_ssim_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(fused_ssim_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS_SMEM);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
+  // per call: the attribute belongs to the (function, device) pair and a process may drive several devices
+  cudaError_t e = cudaFuncSetAttribute(fused_ssim_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS_SMEM);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(fused_ssim_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SS_SMEM);
+  if (e != cudaSuccess) return e;
   const long long hh = valid ? H - 2 * SS_R : H, ww = valid ? W - 2 * SS_R : W;
   const double n = (double)planes * (double)(hh > 0 ? hh : 0) * (double)(ww > 0 ? ww : 0);
   const float inv_n = n > 0 ? (float)(1.0 / n) : 0.f;
