@@ -26,6 +26,7 @@ SOURCES = {
     "api.cu": [],
     "preprocess.cu": ["-fmad=false"],
     "binning.cu": ["-fmad=false"],
+    "tile_binning.cu": ["-fmad=false"],
     "radix_sort.cu": [],
     "render_forward.cu": [],
     "render_backward.cu": [],

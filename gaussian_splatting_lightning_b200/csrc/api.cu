@@ -5,6 +5,7 @@
 // types, no CPU fallback: every stage is a CUDA kernel of this library.
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -91,6 +92,16 @@ struct Mailbox {
 };
 constexpr int MAX_DEVICES = 64;
 thread_local Mailbox g_mail[MAX_DEVICES];
+
+// Which binning the forward runs: tile-segmented (tile_binning.cu, default) or the global onesweep
+// radix sort (GSR_BINNING=onesweep; kept for A/B measurements and as the gsr_sort_pairs primitive).
+bool binning_segmented() {
+  static const bool seg = [] {
+    const char* e = getenv("GSR_BINNING");
+    return !(e && strcmp(e, "onesweep") == 0);
+  }();
+  return seg;
+}
 
 int get_mailbox(Mailbox** out) {
   int dev = 0;
@@ -195,12 +206,19 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
   GeomState geom = GeomState::carve(geom_ptr, P);
   ImgState img = ImgState::carve(img_ptr, v.W, v.H);
 
-  // one memset clears ranges + control block, one the scan status words
+  // GSR_BINNING=onesweep selects the global radix sort (K3-K6); the default is the tile-segmented binning.
+  const bool segmented = binning_segmented();
+  // one memset clears ranges + tile counters + control block, one the scan status words
   GSR_CUDA(cudaMemsetAsync(img_ptr + img.ranges_off, 0, img.bytes - img.ranges_off, stream), "memset(ranges)");
-  GSR_CUDA(cudaMemsetAsync(geom.scan_state, 0, geom.scan_state_bytes(P), stream), "memset(scan state)");
+  if (!segmented) GSR_CUDA(cudaMemsetAsync(geom.scan_state, 0, geom.scan_state_bytes(P), stream), "memset(scan state)");
 
-  GSR_STAGE(ST_PREPROCESS, gsr::launch_preprocess(v, g, radii, geom, stream), "preprocess kernel", debug, stream);
-  GSR_STAGE(ST_SCAN, gsr::launch_scan(P, geom, img.ctrl, stream), "scan kernel", debug, stream);
+  GSR_STAGE(ST_PREPROCESS, gsr::launch_preprocess(v, g, radii, geom, segmented ? img.tile_count : nullptr, stream),
+            "preprocess kernel", debug, stream);
+  if (segmented)
+    GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(P > 0 ? num_tiles : 0, img.tile_count, img.ranges, img.large_tiles, img.ctrl, stream),
+              "tile scan kernel", debug, stream);
+  else
+    GSR_STAGE(ST_SCAN, gsr::launch_scan(P, geom, img.ctrl, stream), "scan kernel", debug, stream);
 
   Mailbox* mail = nullptr;
   rc = get_mailbox(&mail);
@@ -221,7 +239,20 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
     char* bin_ptr = (char*)alloc(alloc_user, GSR_BUF_BINNING, BinningState::carve(nullptr, cap, num_tiles).bytes);
     if (!bin_ptr) return fail(GSR_EALLOC, "allocator returned NULL");
     BinningState bin = BinningState::carve(bin_ptr, cap, num_tiles);
-    if (cap > 0 && P > 0) {
+    if (cap > 0 && P > 0 && segmented) {
+      if (attempt > 0) {  // rebuild the un-truncated ranges, rewind the cursors
+        GSR_CUDA(cudaMemsetAsync(img.tile_cursor, 0, (size_t)num_tiles * 4 * GSR_TILE_COUNT_STRIDE, stream),
+                 "memset(tile cursors)");
+        GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(num_tiles, img.tile_count, img.ranges, img.large_tiles, img.ctrl, stream),
+                  "tile scan kernel", debug, stream);
+      }
+      GSR_STAGE(ST_DUPLICATE, gsr::launch_tile_scatter(v, P, radii, geom, img.ranges, img.tile_cursor, bin.keys_a,
+                                                       (uint32_t)cap, img.ctrl, bin.header, stream),
+                "tile scatter kernel", debug, stream);
+      GSR_STAGE(ST_SORT, gsr::launch_tile_sort(num_tiles, img.ranges, img.large_tiles, img.ctrl, bin.keys_a, bin.vals_a, (uint32_t)cap,
+                                                    stream),
+                "tile sort kernel", debug, stream);
+    } else if (cap > 0 && P > 0) {
       GSR_CUDA(cudaMemsetAsync(bin.sort_ws_base, 0, bin.sort_ws.bytes, stream), "memset(sort workspace)");
       // start in the buffer that makes the last pass land in (keys_a, vals_a)
       unsigned long long* k0 = (npass % 2 == 0) ? bin.keys_a : bin.keys_b;
@@ -246,7 +277,8 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
     if (R <= cap) break;
     // the hint was too small: the frame above rendered a truncated list. Redo binning + compositing.
     cap = R + R / 8 + 1024;
-    GSR_CUDA(cudaMemsetAsync(img.ranges, 0, (size_t)num_tiles * sizeof(uint2), stream), "memset(ranges)");
+    if (!segmented)
+      GSR_CUDA(cudaMemsetAsync(img.ranges, 0, (size_t)num_tiles * sizeof(uint2), stream), "memset(ranges)");
   }
   if (R >= 0xFFFFFFFFll) return fail(GSR_ELIMIT, "more than 2^32 tile instances");
   if (num_rendered) *num_rendered = R;
@@ -308,13 +340,22 @@ int gsr_export_state(const GsrSettings* settings, int32_t P, const int32_t* radi
   ImgState img = ImgState::carve((char*)img_, v.W, v.H);
   const int64_t cap = binning_capacity > 0 ? binning_capacity : num_rendered;
   const size_t R = (size_t)num_rendered;
+  if (binning_segmented() && P > 0) {  // the segmented forward has no per-Gaussian offsets: make them for the export
+    GSR_CUDA(cudaMemsetAsync(geom.scan_state, 0, geom.scan_state_bytes(P), stream), "memset(scan state)");
+    GSR_CUDA(gsr::launch_scan(P, geom, img.ctrl, stream), "export scan kernel");
+  }
   GSR_CUDA(gsr::launch_export_geom(P, radii, geom, out->depths, out->means2D, out->cov3D, out->conic_opacity, out->rgb,
                                    out->clamped, out->tiles_touched, out->point_offsets, stream),
            "export kernel");
   if (R > 0 && binning_) {
     BinningState bin = BinningState::carve((char*)binning_, cap, v.gx * v.gy);
-    if (out->keys_sorted)
-      GSR_CUDA(cudaMemcpyAsync(out->keys_sorted, bin.keys_a, R * 8, cudaMemcpyDeviceToDevice, stream), "export keys");
+    if (out->keys_sorted) {
+      if (binning_segmented())  // the segments hold composites: rebuild (tile << 32 | depth) from the sorted list
+        GSR_CUDA(gsr::launch_export_segment_keys(v.gx * v.gy, img.ranges, bin.vals_a, geom, (uint32_t)R,
+                                                 (unsigned long long*)out->keys_sorted, stream), "export keys");
+      else
+        GSR_CUDA(cudaMemcpyAsync(out->keys_sorted, bin.keys_a, R * 8, cudaMemcpyDeviceToDevice, stream), "export keys");
+    }
     if (out->vals_sorted)
       GSR_CUDA(cudaMemcpyAsync(out->vals_sorted, bin.vals_a, R * 4, cudaMemcpyDeviceToDevice, stream), "export vals");
     if (out->keys_unsorted && out->vals_unsorted)

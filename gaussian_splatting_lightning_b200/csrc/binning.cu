@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, int gx, int gy, c
     for (int k = threadIdx.x; k < npass * gsr_sort::RADIX; k += 256) sh[k] = 0;
     __syncthreads();
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0 && header) { header->capacity = capacity; header->num_tiles = (uint32_t)(gx * gy); }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && header) { header->capacity = capacity; header->num_tiles = (uint32_t)(gx * gy); header->segmented = 0u; }
   bool over = false;
   for (int i = blockIdx.x * 256 + threadIdx.x; i < P; i += gridDim.x * 256) {
     const int r = radii[i];

@@ -36,9 +36,9 @@ struct __align__(16) GsrRec {
 // Per-frame device-side control block (zeroed by one memset at the start of a frame).
 struct GsrControl {
   unsigned int num_rendered;   // R = sum(tiles_touched), written by the scan
-  unsigned int scan_counter;   // dynamic tile id of the scan
+  unsigned int num_mid;        // tiles with 513..2048 instances (tile_binning.cu)
   unsigned int overflow;       // set when R exceeded the binning capacity
-  unsigned int pad;
+  unsigned int num_large;      // tiles with more than 2048 instances
 };
 
 // Kernel-side view of one camera + flags.
@@ -85,10 +85,17 @@ struct GeomState {
 };
 
 // ---- image buffer carving ----------------------------------------------------------
+// Per-tile instance counters sit one per 32-byte sector: the L2 atomic unit serialises the updates of a sector,
+// and neighbouring tiles are updated together.
+constexpr int GSR_TILE_COUNT_STRIDE = 8;
+
 struct ImgState {
   float* final_T;
   uint32_t* n_contrib;
   uint2* ranges;
+  uint32_t* tile_count;   // instances per tile, counted by the preprocess kernel (tile_binning.cu)
+  uint32_t* tile_cursor;  // the scatter's per-tile cursors (same layout)
+  uint32_t* large_tiles;  // lists of the tiles the MID (from the front) and LARGE (from the back) sort launches take
   GsrControl* ctrl;
   size_t ranges_off, bytes;
   static ImgState carve(char* base, int W, int H) {
@@ -101,6 +108,9 @@ struct ImgState {
     s.n_contrib = (uint32_t*)take(HW * 4);
     s.ranges_off = off;
     s.ranges = (uint2*)take(T * 8);
+    s.tile_count = (uint32_t*)take(T * 4 * GSR_TILE_COUNT_STRIDE);
+    s.tile_cursor = (uint32_t*)take(T * 4 * GSR_TILE_COUNT_STRIDE);
+    s.large_tiles = (uint32_t*)take(T * 4);
     s.ctrl = (GsrControl*)take(sizeof(GsrControl));
     s.bytes = off;
     return s;
@@ -146,7 +156,8 @@ struct Workspace {
 struct BinningHeader {
   uint32_t capacity;   // instance capacity the buffer was laid out for
   uint32_t num_tiles;
-  uint32_t pad[30];
+  uint32_t segmented;  // 1: laid out by the tile-segmented binning (tile_binning.cu): keys_a holds composites
+  uint32_t pad[29];
 };
 static_assert(sizeof(BinningHeader) == 128, "binning header is one 128-byte line");
 
@@ -215,8 +226,19 @@ namespace gsr {
 void count_launch(int n = 1);
 
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
+// tile_count (may be NULL): per-tile instance counters the kernel adds every Gaussian's tiles to.
 cudaError_t launch_preprocess(const GsrView& v, const GsrGaussiansDev& g, int32_t* radii, const GeomState& geom,
-                              cudaStream_t s);
+                              uint32_t* tile_count, cudaStream_t s);
+// tile-segmented binning (tile_binning.cu)
+cudaError_t launch_tile_scan(int T, const uint32_t* tile_count, uint2* ranges, uint32_t* large_tiles, GsrControl* ctrl,
+                             cudaStream_t s);
+cudaError_t launch_tile_scatter(const GsrView& v, int P, const int32_t* radii, const GeomState& geom, const uint2* ranges,
+                                uint32_t* cursor, unsigned long long* comp, uint32_t capacity, GsrControl* ctrl,
+                                BinningHeader* header, cudaStream_t s);
+cudaError_t launch_tile_sort(int T, uint2* ranges, const uint32_t* large_tiles, const GsrControl* ctrl,
+                             unsigned long long* comp, uint32_t* vals, uint32_t capacity, cudaStream_t s);
+cudaError_t launch_export_segment_keys(int T, const uint2* ranges, const uint32_t* vals, const GeomState& geom,
+                                       uint32_t limit, unsigned long long* keys, cudaStream_t s);
 cudaError_t launch_scan(int P, const GeomState& geom, GsrControl* ctrl, cudaStream_t s);
 cudaError_t launch_duplicate(const GsrView& v, int P, const int32_t* radii, const GeomState& geom,
                              unsigned long long* keys, uint32_t* vals, uint32_t capacity, GsrControl* ctrl,

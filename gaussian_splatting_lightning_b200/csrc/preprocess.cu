@@ -40,6 +40,7 @@ struct PreArgs {
   float* cov3D;
   uint8_t* clamped;
   uint32_t* tiles_touched;
+  uint32_t* tile_count;  // per-tile instance counters (tile-segmented binning) or NULL
   int use_bulk;  // SH rows staged by cp.async.bulk
 };
 
@@ -157,6 +158,9 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreArgs a) {
       tile_rect(pixx, pixy, radius, a.v.gx, a.v.gy, x0, y0, x1, y1);
       area = (x1 - x0) * (y1 - y0);
       if (area == 0) alive = false;
+      if (a.tile_count)  // one RED per instance; issued here so that they fly under the SH copy
+        for (int y = y0; y < y1; ++y)
+          for (int x = x0; x < x1; ++x) atomicAdd(&a.tile_count[(y * a.v.gx + x) * GSR_TILE_COUNT_STRIDE], 1u);
       opac = a.g.opacities[i] * hscale;  // rasterize.py:72
     }
   }
@@ -206,11 +210,12 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreArgs a) {
 }
 
 cudaError_t launch_preprocess(const GsrView& v, const GsrGaussiansDev& g, int32_t* radii, const GeomState& geom,
-                              cudaStream_t s) {
+                              uint32_t* tile_count, cudaStream_t s) {
   if (g.P <= 0) return cudaSuccess;
   PreArgs a;
   a.v = v; a.g = g; a.radii = radii;
   a.recs = geom.recs; a.cov3D = geom.cov3D; a.clamped = geom.clamped; a.tiles_touched = geom.tiles_touched;
+  a.tile_count = tile_count;
   const size_t smem = g.shs ? (size_t)256 * g.M * 12 : 0;
   // bulk copies need a 16-byte aligned source; the per-CTA offset 256*M*12 is always a multiple of 16
   a.use_bulk = g.shs && ((reinterpret_cast<uintptr_t>(g.shs) & 15) == 0) && smem <= 200 * 1024;

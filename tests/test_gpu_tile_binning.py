@@ -1,0 +1,61 @@
+"""Tile-segmented binning (csrc/tile_binning.cu) against the oracle's global stable sort, on scenes built to reach
+every path of the per-tile sort: segments of a few instances, of 1 000 - 8 000 (the 64 KB shared-memory launch),
+above 8 192 (the in-place network through L2), and depths with many exact ties (the Gaussian index must break
+them the way the reference's stable radix sort does).  Bit-exact: sorted keys, sorted point list, ranges."""
+import numpy as np
+import pytest
+
+import gpu_utils as U
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    # name: (P, W, H, number of distinct depths or 0)
+    "sparse_tiles": (300, 256, 256, 0),
+    "segments_of_thousands": (30_000, 64, 48, 0),
+    "segments_above_8192": (60_000, 32, 32, 0),
+    "ties_everywhere": (20_000, 64, 64, 5),
+    "ties_and_huge_segments": (50_000, 32, 16, 3),
+}
+
+
+def _case(name):
+    P, W, H, levels = CASES[name]
+    cam, arrays = U.synthetic_case(P, 1, W, H, seed=7)
+    if levels:
+        m = arrays["means3D"].copy()
+        z = m[:, 2]
+        q = np.round((np.log(z) - np.log(2.0)) / (np.log(20.0) - np.log(2.0)) * (levels - 1))
+        znew = (2.0 * (10.0 ** (q / max(levels - 1, 1)))).astype(np.float32)
+        m[:, 0] *= znew / z
+        m[:, 1] *= znew / z
+        m[:, 2] = znew
+        arrays["means3D"] = np.ascontiguousarray(m.astype(np.float32))
+    return cam, arrays
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_segmented_binning_equals_global_stable_sort(oracle_lib, name):
+    cam, arrays = _case(name)
+    ref = U.run_oracle_forward(cam, arrays)
+    out = U.run_cuda_forward(cam, arrays)
+    st = U.export(out)
+    assert out["R"] == ref["num_rendered"]
+    counts = ref["ranges"][:, 1].astype(np.int64) - ref["ranges"][:, 0]
+    print(f"{name}: R = {out['R']}, largest segment {counts.max()}, distinct depths "
+          f"{np.unique(ref['depths'][ref['radii'] > 0]).size}")
+    assert np.array_equal(st["ranges"].view(np.uint32), ref["ranges"])
+    assert np.array_equal(st["vals_sorted"].view(np.uint32), ref["point_list"])
+    assert np.array_equal(st["keys_sorted"].view(np.uint64), ref["keys"])
+    frac, mx = U.close_fraction(out["color"].cpu().numpy(), ref["color"], 1e-4, 1e-4)
+    assert frac <= 2e-4 and mx <= 2e-2, (frac, mx)
+
+
+@pytest.mark.parametrize("name", ["segments_of_thousands", "ties_and_huge_segments"])
+def test_too_small_hint_reruns_to_the_same_lists(name):
+    cam, arrays = _case(name)
+    base = U.export(U.run_cuda_forward(cam, arrays, hint=0))
+    for hint in (1, 1000):
+        o = U.export(U.run_cuda_forward(cam, arrays, hint=hint))
+        for k in ("ranges", "vals_sorted", "keys_sorted"):
+            assert np.array_equal(o[k], base[k]), (hint, k)
