@@ -185,13 +185,19 @@ def peaks():
 
 
 def stage_model(P, M, Pvis, R, L, A, HW, T, passes):
-    """Algorithmic bytes / flops per frame of every stage."""
+    """Algorithmic bytes / flops per frame of every stage.  The binning stages are
+    those of the build: tile-segmented (csrc/tile_binning.cu) unless GSR_BINNING=onesweep."""
+    if os.environ.get("GSR_BINNING") == "onesweep":
+        binning = {"scan": dict(bytes=8 * P), "duplicate": dict(bytes=8 * P + 12 * Pvis + 12 * R),
+                   "sort": dict(bytes=(8 + 24 * passes) * R), "tile_ranges": dict(bytes=8 * R + 8 * T)}
+    else:
+        binning = {"scan": dict(bytes=4 * T + 8 * T),                  # tile scan: counts in, ranges out
+                   "duplicate": dict(bytes=4 * P + 36 * Pvis + 12 * R),  # scatter: radii, record, 4 B cursor + 8 B composite
+                   "sort": dict(bytes=8 * T + 12 * R),                  # per-tile sort: composite in, point list out
+                   "tile_ranges": dict(bytes=0)}
     return {
         "preprocess": dict(bytes=52 * P + (12 * M + 67) * Pvis),
-        "scan": dict(bytes=8 * P),
-        "duplicate": dict(bytes=8 * P + 12 * Pvis + 12 * R),
-        "sort": dict(bytes=(8 + 24 * passes) * R),
-        "tile_ranges": dict(bytes=8 * R + 8 * T),
+        **binning,
         "render_forward": dict(bytes=44 * L + 24 * HW, flops=24 * A, ex2=A),
         "render_backward": dict(bytes=84 * L + 24 * HW, flops=75 * A, ex2=A),
         "preprocess_backward": dict(bytes=(187 + 24 * M) * Pvis),

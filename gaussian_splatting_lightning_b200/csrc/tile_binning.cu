@@ -206,8 +206,9 @@ __device__ __forceinline__ void sort16(u64* e) {
 // A warp's 32 units of one round (unit = tid + m * THREADS, 16 composites each) cover one aligned block of 512
 // composites in every pass whose partners lie inside aligned blocks of <= 512: between two such passes the
 // warp only waits for itself.
+template <bool ONE_WARP>  // ONE_WARP: the segment belongs to a single warp (<= 512 composites), never a CTA barrier
 __device__ __forceinline__ void pass_sync(uint32_t span_done, uint32_t span_next) {
-  if (span_done > 512u || span_next > 512u) __syncthreads();
+  if (!ONE_WARP && (span_done > 512u || span_next > 512u)) __syncthreads();
   else __syncwarp();
 }
 
@@ -215,11 +216,15 @@ __device__ __forceinline__ void pass_sync(uint32_t span_done, uint32_t span_next
 // composites (pow2 >= 16, padded with ~0).  A merge of size k is: mirror(k), halve(k/4) ... halve(16), then
 // tail16.  The steps before the tail are taken two per pass (four columns of 4 composites per thread); when
 // their number is odd the mirror step goes alone.
+// Only composites below n are real.  A merge of size k is skipped for a block that holds at most k/2 of them:
+// its lower half is sorted and its upper half is all padding, so it is sorted already (a segment of 540 costs
+// one sort of 512, a little work on the 28 and ONE merge of 1024, not a sort of 1024).
 template <int THREADS>
-__device__ __forceinline__ void bitonic_sort_shared(u64* s, uint32_t pow2, int tid) {
+__device__ __forceinline__ void bitonic_sort_shared(u64* s, uint32_t pow2, uint32_t n, int tid) {
   ulonglong2* s2 = reinterpret_cast<ulonglong2*>(s);
   const uint32_t units = pow2 >> 4;
   for (uint32_t u = tid; u < units; u += THREADS) {
+    if (16u * u >= n) continue;
     u64 e[16];
 #pragma unroll
     for (int g = 0; g < 4; ++g) load4(s2, 16u * u + 4u * g, e + 4 * g);
@@ -227,7 +232,7 @@ __device__ __forceinline__ void bitonic_sort_shared(u64* s, uint32_t pow2, int t
 #pragma unroll
     for (int g = 0; g < 4; ++g) store4(s2, 16u * u + 4u * g, e + 4 * g);
   }
-  pass_sync(16u, 32u);
+  pass_sync<THREADS == 32>(16u, 32u);
   for (uint32_t k = 32; k <= pow2; k <<= 1) {
     const uint32_t nsteps = (uint32_t)(31 - __clz((int)k)) - 4u;  // mirror(k), halve(k/4) .. halve(16)
     uint32_t jj = k >> 2;                                        // distance of the next halving step
@@ -236,18 +241,20 @@ __device__ __forceinline__ void bitonic_sort_shared(u64* s, uint32_t pow2, int t
       for (uint32_t u = tid; u < units; u += THREADS) {
         const uint32_t p0 = 8u * u, r = p0 & (half - 1u), base = (p0 - r) << 1;
         const uint32_t lo = base + r, hi = base + k - 8u - r;
+        if (n <= base + half) continue;
         u64 L[8], H[8];
         load4(s2, lo, L); load4(s2, lo + 4u, L + 4); load4(s2, hi, H); load4(s2, hi + 4u, H + 4);
 #pragma unroll
         for (int q = 0; q < 8; ++q) cx(L[q], H[7 - q]);
         store4(s2, lo, L); store4(s2, lo + 4u, L + 4); store4(s2, hi, H); store4(s2, hi + 4u, H + 4);
       }
-      pass_sync(k, 16u);
+      pass_sync<THREADS == 32>(k, 16u);
     } else {  // mirror(k) + halve(k/4): columns A, B at offset r, C, D at the mirrored offset
       const uint32_t j2 = jj, upb = j2 >> 2;  // units per block of 4 * j2 = k
       for (uint32_t u = tid; u < units; u += THREADS) {
         const uint32_t r = 4u * (u & (upb - 1u)), b = (u / upb) * k, rm = j2 - 4u - r;
         const uint32_t iA = b + r, iB = iA + j2, iC = b + 2u * j2 + rm, iD = iC + j2;
+        if (n <= b + (k >> 1)) continue;
         u64 A[4], B[4], C[4], D[4];
         load4(s2, iA, A); load4(s2, iB, B); load4(s2, iC, C); load4(s2, iD, D);
 #pragma unroll
@@ -256,13 +263,14 @@ __device__ __forceinline__ void bitonic_sort_shared(u64* s, uint32_t pow2, int t
         for (int q = 0; q < 4; ++q) { cx(A[q], B[q]); cx(C[q], D[q]); }
         store4(s2, iA, A); store4(s2, iB, B); store4(s2, iC, C); store4(s2, iD, D);
       }
-      pass_sync(k, 16u);
+      pass_sync<THREADS == 32>(k, 16u);
       jj >>= 1;
     }
     for (; jj >= 32u; jj >>= 2) {  // halve(jj) + halve(jj / 2)
       const uint32_t j2 = jj >> 1, upb = j2 >> 2, blk = 2u * jj;
       for (uint32_t u = tid; u < units; u += THREADS) {
         const uint32_t r = 4u * (u & (upb - 1u)), iA = (u / upb) * blk + r, iB = iA + j2, iC = iB + j2, iD = iC + j2;
+        if (n <= (iA & ~(k - 1u)) + (k >> 1)) continue;
         u64 A[4], B[4], C[4], D[4];
         load4(s2, iA, A); load4(s2, iB, B); load4(s2, iC, C); load4(s2, iD, D);
 #pragma unroll
@@ -271,9 +279,10 @@ __device__ __forceinline__ void bitonic_sort_shared(u64* s, uint32_t pow2, int t
         for (int q = 0; q < 4; ++q) { cx(A[q], B[q]); cx(C[q], D[q]); }
         store4(s2, iA, A); store4(s2, iB, B); store4(s2, iC, C); store4(s2, iD, D);
       }
-      pass_sync(blk, 16u);
+      pass_sync<THREADS == 32>(blk, 16u);
     }
     for (uint32_t u = tid; u < units; u += THREADS) {
+      if (n <= ((16u * u) & ~(k - 1u)) + (k >> 1)) continue;
       u64 e[16];
 #pragma unroll
       for (int g = 0; g < 4; ++g) load4(s2, 16u * u + 4u * g, e + 4 * g);
@@ -281,7 +290,7 @@ __device__ __forceinline__ void bitonic_sort_shared(u64* s, uint32_t pow2, int t
 #pragma unroll
       for (int g = 0; g < 4; ++g) store4(s2, 16u * u + 4u * g, e + 4 * g);
     }
-    pass_sync(16u, 2u * k);
+    pass_sync<THREADS == 32>(16u, 2u * k);
   }
 }
 
@@ -309,13 +318,13 @@ __device__ __forceinline__ void bitonic_sort_global(volatile u64* a, uint32_t n,
 }
 }  // namespace
 
-// Three launches cover the tiles, one warp per 512 composites in each:
-//   SMALL  one CTA of 32 threads per tile: segments of 1..512 instances, 4 KB of shared memory;
-//   MID    CTAs of 128 threads walking the list of tiles with 513..2048 instances (16 KB);
+// Size classes, one warp per 512 composites in each:
+//   SMALL  a warp per tile: segments of 1..512 instances, 4 KB of shared memory;
+//   MID    CTAs of 128 threads walking the list of tiles with 513..2048 instances (16 KB), same launch as SMALL;
 //   LARGE  CTAs of 512 threads walking the list of tiles above 2048 (64 KB up to 8192 instances, above that
-//          the global-memory network).
-// The tile scan makes the two lists.  All three decide on the count clamped to the capacity, so a truncated
-// frame (binning hint too small) stays in bounds: whatever a clamp moved below 513 the SMALL launch takes.
+//          the global-memory network), a second launch.
+// The tile scan makes the two lists.  All decide on the count clamped to the capacity, so a truncated frame
+// (binning hint too small) stays in bounds: whatever a clamp moved below 513 the SMALL warps take.
 constexpr uint32_t TS_SMALL_CAP = 512, TS_MID_CAP = 2048, TS_LARGE_CAP = 8192;
 
 template <int CAP, int THREADS>
@@ -329,9 +338,9 @@ __device__ __forceinline__ void sort_segment(u64* s_comp, uint2* ranges, uint32_
       const uint32_t i = 2u * c;
       s2[swz(c)] = make_ulonglong2(i < n ? seg[i] : ~0ull, i + 1u < n ? seg[i + 1u] : ~0ull);
     }
-    __syncthreads();
-    bitonic_sort_shared<THREADS>(s_comp, pow2, tid);
-    __syncthreads();
+    if (THREADS == 32) __syncwarp(); else __syncthreads();
+    bitonic_sort_shared<THREADS>(s_comp, pow2, n, tid);
+    if (THREADS == 32) __syncwarp(); else __syncthreads();
     for (uint32_t i = tid; i < n; i += THREADS) {
       const ulonglong2 v = s2[swz(i >> 1)];
       vals[lo + i] = (uint32_t)((i & 1u) ? v.y : v.x);
@@ -342,30 +351,47 @@ __device__ __forceinline__ void sort_segment(u64* s_comp, uint2* ranges, uint32_
   }
 }
 
-__global__ void __launch_bounds__(32) tile_sort_small_kernel(uint2* ranges, u64* comp, uint32_t* __restrict__ vals,
-                                                             uint32_t capacity) {
-  __shared__ __align__(16) u64 s_comp[TS_SMALL_CAP];
-  const uint32_t t = blockIdx.x;
-  const uint2 r = ranges[t];
-  const uint32_t lo = min(r.x, capacity), hi = min(r.y, capacity), n = hi - lo;
-  if ((lo != r.x || hi != r.y) && threadIdx.x == 0) ranges[t] = make_uint2(lo, hi);  // truncated frame (hint too small)
-  if (n == 0u || n > TS_SMALL_CAP) return;
-  sort_segment<TS_SMALL_CAP, 32>(s_comp, ranges, t, comp, vals, lo, n, threadIdx.x);
+// SMALL and MID in one launch (CTAs of 128 threads, 16 KB): the first `mid_ctas` CTAs walk the MID list, one tile
+// at a time; every other CTA takes four consecutive tiles, one per warp (a warp sorts up to 512 composites with
+// no CTA barrier at all).  The few, long MID sorts start first and run under the many short ones.
+__global__ void __launch_bounds__(128) tile_sort_kernel(uint2* ranges, const uint32_t* __restrict__ mid_tiles, int T,
+                                                        const GsrControl* __restrict__ ctrl, u64* comp,
+                                                        uint32_t* __restrict__ vals, uint32_t capacity,
+                                                        uint32_t mid_ctas) {
+  __shared__ __align__(16) u64 s_comp[TS_MID_CAP];
+  if (blockIdx.x >= mid_ctas) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t t = (blockIdx.x - mid_ctas) * 4u + (uint32_t)warp;
+    if (t >= (uint32_t)T) return;
+    const uint2 r = ranges[t];
+    const uint32_t lo = min(r.x, capacity), hi = min(r.y, capacity), n = hi - lo;
+    if ((lo != r.x || hi != r.y) && lane == 0) ranges[t] = make_uint2(lo, hi);  // truncated frame (hint too small)
+    if (n == 0u || n > TS_SMALL_CAP) return;
+    sort_segment<TS_SMALL_CAP, 32>(s_comp + TS_SMALL_CAP * warp, ranges, t, comp, vals, lo, n, lane);
+  } else {
+    const uint32_t num = ctrl->num_mid;
+    for (uint32_t k = blockIdx.x; k < num; k += mid_ctas) {
+      const uint32_t t = mid_tiles[k];
+      const uint2 r = ranges[t];  // possibly clamped already by the tile's warp above: clamping is idempotent
+      const uint32_t lo = min(r.x, capacity), hi = min(r.y, capacity), n = hi - lo;
+      if (n > TS_SMALL_CAP) sort_segment<TS_MID_CAP, 128>(s_comp, ranges, t, comp, vals, lo, n, threadIdx.x);
+      __syncthreads();  // shared memory is reused by the next tile
+    }
+  }
 }
 
-// FROM_BACK: the list is stored from the end of `tiles` backwards (the two lists share one array of T words).
-template <int CAP, int THREADS, bool FROM_BACK>
-__global__ void __launch_bounds__(THREADS) tile_sort_list_kernel(uint2* ranges, const uint32_t* __restrict__ tiles,
-                                                                 int T, const unsigned int* __restrict__ count,
-                                                                 u64* comp, uint32_t* __restrict__ vals) {
+// LARGE: the list is stored from the end of `tiles` backwards (the two lists share one array of T words).
+__global__ void __launch_bounds__(512) tile_sort_large_kernel(uint2* ranges, const uint32_t* __restrict__ tiles, int T,
+                                                              const GsrControl* __restrict__ ctrl, u64* comp,
+                                                              uint32_t* __restrict__ vals) {
   extern __shared__ __align__(16) unsigned char ts_smem[];
-  const uint32_t num = *count;
+  const uint32_t num = ctrl->num_large;
   for (uint32_t k = blockIdx.x; k < num; k += gridDim.x) {
-    const uint32_t t = tiles[FROM_BACK ? (uint32_t)T - 1u - k : k];
-    const uint2 r = ranges[t];  // already clamped by the SMALL launch
+    const uint32_t t = tiles[(uint32_t)T - 1u - k];
+    const uint2 r = ranges[t];  // clamped by the launch before
     const uint32_t n = r.y - r.x;
     if (n > TS_SMALL_CAP)
-      sort_segment<CAP, THREADS>(reinterpret_cast<u64*>(ts_smem), ranges, t, comp, vals, r.x, n, threadIdx.x);
+      sort_segment<TS_LARGE_CAP, 512>(reinterpret_cast<u64*>(ts_smem), ranges, t, comp, vals, r.x, n, threadIdx.x);
     __syncthreads();  // shared memory is reused by the next tile
   }
 }
@@ -373,14 +399,14 @@ __global__ void __launch_bounds__(THREADS) tile_sort_list_kernel(uint2* ranges, 
 cudaError_t launch_tile_sort(int T, uint2* ranges, const uint32_t* large_tiles, const GsrControl* ctrl,
                              unsigned long long* comp, uint32_t* vals, uint32_t capacity, cudaStream_t s) {
   if (T <= 0 || capacity == 0) return cudaSuccess;
-  auto large = tile_sort_list_kernel<(int)TS_LARGE_CAP, 512, true>;
-  cudaError_t e = cudaFuncSetAttribute(large, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TS_LARGE_CAP * 8));
+  cudaError_t e = cudaFuncSetAttribute(tile_sort_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)(TS_LARGE_CAP * 8));
   if (e != cudaSuccess) return e;
-  tile_sort_small_kernel<<<T, 32, 0, s>>>(ranges, comp, vals, capacity);
-  tile_sort_list_kernel<(int)TS_MID_CAP, 128, false><<<148 * 6, 128, TS_MID_CAP * 8, s>>>(ranges, large_tiles, T,
-                                                                                         &ctrl->num_mid, comp, vals);
-  large<<<148 * 2, 512, TS_LARGE_CAP * 8, s>>>(ranges, large_tiles, T, &ctrl->num_large, comp, vals);
-  count_launch(3);
+  const uint32_t mid_ctas = 148u * 6u;
+  tile_sort_kernel<<<mid_ctas + (uint32_t)((T + 3) / 4), 128, 0, s>>>(ranges, large_tiles, T, ctrl, comp, vals, capacity,
+                                                                   mid_ctas);
+  tile_sort_large_kernel<<<148 * 2, 512, TS_LARGE_CAP * 8, s>>>(ranges, large_tiles, T, ctrl, comp, vals);
+  count_launch(2);
   return cudaGetLastError();
 }
 

@@ -59,3 +59,18 @@ def test_too_small_hint_reruns_to_the_same_lists(name):
         o = U.export(U.run_cuda_forward(cam, arrays, hint=hint))
         for k in ("ranges", "vals_sorted", "keys_sorted"):
             assert np.array_equal(o[k], base[k]), (hint, k)
+
+
+def test_global_onesweep_binning_still_passes_the_list_tests():
+    """GSR_BINNING=onesweep (read once per process) selects the global radix-sort binning: the bit-exact list tests
+    and this file's crowded / tied scenes must hold for it too."""
+    import os
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, GSR_BINNING="onesweep")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-p", "no:cacheprovider",
+                        os.path.join(here, "test_gpu_parity.py") + "::test_keys_sort_ranges_bit_exact",
+                        os.path.join(here, "test_gpu_tile_binning.py") + "::test_segmented_binning_equals_global_stable_sort"],
+                       env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
