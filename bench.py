@@ -505,12 +505,12 @@ def run_ours(args):
         s["share_of_kernel_time"] = s["ms_per_frame"] * s["calls"] / stage_sum
     dom = max(stages, key=lambda s: s["ms_per_frame"] * s["calls"])
     traffic, traffic_src = None, None
-    tp = os.path.join(ROOT, "profiles", "r1_v6_traffic.json")      # dram bytes per launch from the ncu --set full capture
+    tp = os.path.join(ROOT, "profiles", "r1_v7_traffic.json")      # dram bytes per launch from the ncu --set full capture
     if os.path.exists(tp):
         tj = json.load(open(tp))
         ent = tj.get(dom["stage"] + "_kernel") or tj.get({"sort": "onesweep_pass_kernel"}.get(dom["stage"], ""))
         if ent:
-            traffic, traffic_src = ent["dram_bytes_per_launch"], "profiles/r1_v6_traffic.json: " + tj.get("_source", "")
+            traffic, traffic_src = ent["dram_bytes_per_launch"], "profiles/r1_v7_traffic.json: " + tj.get("_source", "")
     roofline = {"kernel": dom["stage"], "bound": "hbm", "achieved": dom["GBps"], "peak": hbm_peak, "unit": "GB/s",
                 "frac": dom["hbm_frac"], "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": dom["algorithmic_bytes"], "ms_per_launch": dom["ms_per_frame"],

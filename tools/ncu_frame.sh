@@ -7,8 +7,9 @@ CMD="python bench.py --steps 2 --warmup 3 --views-per-rank 2 --streams 1 --no-e2
 mkdir -p gpurun_out
 $CMD > gpurun_out/${TAG}_plain.json 2> gpurun_out/${TAG}_plain.err || { echo "plain run failed"; tail -5 gpurun_out/${TAG}_plain.err; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1
-# one frame = 13 launches (preprocess, scan, duplicate, 6 sort passes, ranges, render fwd, render bwd, preprocess bwd);
-# skip the warm-up frames and capture the kernels of one whole frame with the full set
-ncu --set full --clock-control none --import-source on --launch-skip 130 -c 13 -f -o gpurun_out/${TAG}_full $CMD > gpurun_out/${TAG}_ncu2.log 2>&1
+# one frame = 8 launches of the library (preprocess, tile scan, scatter, tile sort, large-tile sort, render fwd,
+# render bwd, preprocess bwd); only the library's kernels are counted (-k regex on the base name), the window starts inside the timed
+# steady-state frames (after workload counters + warm-up), and any 8 consecutive launches hold each kernel once
+ncu --set full --clock-control none --import-source on -k regex:"^(preprocess|tile_|render_)" --launch-skip 104 -c 8 -f -o gpurun_out/${TAG}_full $CMD > gpurun_out/${TAG}_ncu2.log 2>&1
 ncu -i gpurun_out/${TAG}_full.ncu-rep --page raw --csv > gpurun_out/${TAG}_full_raw.csv 2>/dev/null
 tail -3 gpurun_out/${TAG}_ncu2.log
