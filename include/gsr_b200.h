@@ -142,8 +142,11 @@ size_t gsr_img_bytes(int32_t image_width, int32_t image_height);
 size_t gsr_binning_bytes(int64_t capacity, int32_t image_width, int32_t image_height);
 size_t gsr_backward_scratch_bytes(int32_t P);
 
-/* Forward: preprocess -> scan -> duplicate keys -> onesweep radix sort -> tile ranges ->
- * compositing.  Writes out_color (3,H,W), radii (P) int32, out_invdepth (1,H,W).
+/* Forward: preprocess (+ per-tile instance counts) -> tile scan (ranges) -> scatter of the
+ * (depth, index) composites into the tile segments -> per-tile sort -> compositing; the lists
+ * equal those of a global stable sort of (tile << 32 | depth, index) pairs.  With the
+ * environment variable GSR_BINNING=onesweep (read once per process): preprocess -> scan ->
+ * duplicate keys -> onesweep radix sort -> tile ranges -> compositing.  Writes out_color (3,H,W), radii (P) int32, out_invdepth (1,H,W).
  *
  * binning_hint = 0 reproduces upstream's behaviour: one blocking read of num_rendered
  * after the scan, then the binning buffer is sized exactly.  binning_hint > 0 sizes the
