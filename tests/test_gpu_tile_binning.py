@@ -74,3 +74,35 @@ def test_global_onesweep_binning_still_passes_the_list_tests():
                         os.path.join(here, "test_gpu_tile_binning.py") + "::test_segmented_binning_equals_global_stable_sort"],
                        env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("n", [1, 15, 16, 17, 255, 511, 512, 513, 1023, 1024, 1025, 2047, 2048, 2049, 4097, 8191, 8192,
+                               8193, 20000])
+def test_one_segment_of_exactly_n_instances(n):
+    """Every Gaussian lands in the same single tile, so that tile's segment holds exactly n instances: the size-class
+    boundaries of the per-tile sort (512 / 2048 / 8192), the power-of-two paddings on either side of them and the
+    skipped merges.  Expected order: ascending depth bits, ties by Gaussian index (numpy lexsort)."""
+    from gaussian_splatting_lightning_b200 import synthetic
+    import oracle
+    W = H = 64
+    c = synthetic.make_camera(W, H)
+    cam = oracle.Camera(H, W, c["tanfovx"], c["tanfovy"], c["viewmatrix"].numpy(), c["projmatrix"].numpy(),
+                        c["campos"].numpy(), bg=np.zeros(3, np.float32), sh_degree=0)
+    rng = np.random.default_rng(n)
+    focal = W / (2 * c["tanfovx"])
+    levels = max(2, n // 3)                                  # about three Gaussians per distinct depth
+    z = (2.0 + 18.0 * rng.integers(0, levels, n) / levels).astype(np.float32)
+    u, v = 24.0 + rng.uniform(-1, 1, n), 24.0 + rng.uniform(-1, 1, n)      # well inside tile (1, 1)
+    means = np.stack([(u - W / 2 + 0.5) / focal * z, (v - H / 2 + 0.5) / focal * z, z], -1).astype(np.float32)
+    arrays = dict(means3D=means, scales=np.full((n, 3), 1e-4, np.float32),
+                  rotations=np.tile(np.array([1, 0, 0, 0], np.float32), (n, 1)),
+                  opacities=np.full((n, 1), 0.01, np.float32), shs=rng.normal(size=(n, 1, 3)).astype(np.float32))
+    out = U.run_cuda_forward(cam, arrays)
+    st = U.export(out)
+    assert out["R"] == n
+    ranges = st["ranges"].view(np.uint32).reshape(-1, 2)
+    assert ranges[5].tolist() == [0, n] and np.count_nonzero(ranges) == 1
+    depth_bits = st["depths"].view(np.uint32)
+    want = np.lexsort((np.arange(n), depth_bits)).astype(np.uint32)
+    assert np.array_equal(st["vals_sorted"].view(np.uint32), want)
+    assert np.array_equal(st["keys_sorted"].view(np.uint64), (np.uint64(5) << np.uint64(32)) | depth_bits[want].astype(np.uint64))
