@@ -215,7 +215,8 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
   GSR_STAGE(ST_PREPROCESS, gsr::launch_preprocess(v, g, radii, geom, segmented ? img.tile_count : nullptr, stream),
             "preprocess kernel", debug, stream);
   if (segmented)
-    GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(P > 0 ? num_tiles : 0, img.tile_count, img.ranges, img.large_tiles, img.ctrl, stream),
+    GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(P > 0 ? num_tiles : 0, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
+                                             img.ctrl, stream),
               "tile scan kernel", debug, stream);
   else
     GSR_STAGE(ST_SCAN, gsr::launch_scan(P, geom, img.ctrl, stream), "scan kernel", debug, stream);
@@ -240,13 +241,11 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
     if (!bin_ptr) return fail(GSR_EALLOC, "allocator returned NULL");
     BinningState bin = BinningState::carve(bin_ptr, cap, num_tiles);
     if (cap > 0 && P > 0 && segmented) {
-      if (attempt > 0) {  // rebuild the un-truncated ranges, rewind the cursors
-        GSR_CUDA(cudaMemsetAsync(img.tile_cursor, 0, (size_t)num_tiles * 4 * GSR_TILE_COUNT_STRIDE, stream),
-                 "memset(tile cursors)");
-        GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(num_tiles, img.tile_count, img.ranges, img.large_tiles, img.ctrl, stream),
+      if (attempt > 0)  // rebuild the un-truncated ranges, rewind the cursors
+        GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(num_tiles, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
+                                                 img.ctrl, stream),
                   "tile scan kernel", debug, stream);
-      }
-      GSR_STAGE(ST_DUPLICATE, gsr::launch_tile_scatter(v, P, radii, geom, img.ranges, img.tile_cursor, bin.keys_a,
+      GSR_STAGE(ST_DUPLICATE, gsr::launch_tile_scatter(v, P, radii, geom, img.tile_cursor, bin.keys_a,
                                                        (uint32_t)cap, img.ctrl, bin.header, stream),
                 "tile scatter kernel", debug, stream);
       GSR_STAGE(ST_SORT, gsr::launch_tile_sort(num_tiles, img.ranges, img.large_tiles, img.ctrl, bin.keys_a, bin.vals_a, (uint32_t)cap,

@@ -94,7 +94,7 @@ struct ImgState {
   uint32_t* n_contrib;
   uint2* ranges;
   uint32_t* tile_count;   // instances per tile, counted by the preprocess kernel (tile_binning.cu)
-  uint32_t* tile_cursor;  // the scatter's per-tile cursors (same layout)
+  uint32_t* tile_cursor;  // the scatter's per-tile cursors (same layout), set to the segment starts by the tile scan
   uint32_t* large_tiles;  // lists of the tiles the MID (from the front) and LARGE (from the back) sort launches take
   GsrControl* ctrl;
   size_t ranges_off, bytes;
@@ -230,11 +230,11 @@ cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, 
 cudaError_t launch_preprocess(const GsrView& v, const GsrGaussiansDev& g, int32_t* radii, const GeomState& geom,
                               uint32_t* tile_count, cudaStream_t s);
 // tile-segmented binning (tile_binning.cu)
-cudaError_t launch_tile_scan(int T, const uint32_t* tile_count, uint2* ranges, uint32_t* large_tiles, GsrControl* ctrl,
-                             cudaStream_t s);
-cudaError_t launch_tile_scatter(const GsrView& v, int P, const int32_t* radii, const GeomState& geom, const uint2* ranges,
-                                uint32_t* cursor, unsigned long long* comp, uint32_t capacity, GsrControl* ctrl,
-                                BinningHeader* header, cudaStream_t s);
+cudaError_t launch_tile_scan(int T, const uint32_t* tile_count, uint2* ranges, uint32_t* tile_cursor,
+                             uint32_t* large_tiles, GsrControl* ctrl, cudaStream_t s);
+cudaError_t launch_tile_scatter(const GsrView& v, int P, const int32_t* radii, const GeomState& geom, uint32_t* cursor,
+                                unsigned long long* comp, uint32_t capacity, GsrControl* ctrl, BinningHeader* header,
+                                cudaStream_t s);
 cudaError_t launch_tile_sort(int T, uint2* ranges, const uint32_t* large_tiles, const GsrControl* ctrl,
                              unsigned long long* comp, uint32_t* vals, uint32_t capacity, cudaStream_t s);
 cudaError_t launch_export_segment_keys(int T, const uint2* ranges, const uint32_t* vals, const GeomState& geom,

@@ -7,8 +7,8 @@
 // sort is stable).  That result is produced here without a global sort:
 //   * the preprocess kernel counts the instances of every tile (one RED per instance);
 //   * K3' one CTA scans the T counts: ranges[t] = [first, last) directly (no K6), R = total;
-//   * K4' every Gaussian claims a slot in each of its tiles' segments with an atomic cursor (a second, zeroed
-//     counter array) and
+//   * K4' every Gaussian claims a slot in each of its tiles' segments with an atomic cursor (a second
+//     counter array the scan set to the segment starts) and
 //     stores the 64-bit composite (depth bits << 32 | Gaussian index) there, in arbitrary order;
 //   * K5' one CTA per tile (a second, list-driven launch for the tiles above 1024 instances) sorts the segment's composites ascending -- depth first, index breaks
 //     ties, which is exactly the stable order -- with a bitonic network in shared memory
@@ -26,8 +26,8 @@ namespace gsr {
 // instances go on the lists of the MID and LARGE sort launches (one array: MID from the front, LARGE from the
 // back).
 __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* __restrict__ count,
-                                                         uint2* __restrict__ ranges, uint32_t* __restrict__ large_tiles,
-                                                         GsrControl* ctrl) {
+                                                         uint2* __restrict__ ranges, uint32_t* __restrict__ cursor,
+                                                         uint32_t* __restrict__ large_tiles, GsrControl* ctrl) {
   constexpr int IPT = 8;
   __shared__ unsigned long long s_warp[32];
   __shared__ unsigned int s_mid, s_large;  // list cursors: shared atomics, the CTA is alone
@@ -67,9 +67,27 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* 
         const uint32_t lo32 = lo > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)lo;
         const uint32_t hi32 = hi > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)hi;
         ranges[k0 + q] = c[q] ? make_uint2(lo32, hi32) : make_uint2(0u, 0u);
-        if (c[q] > 2048u) large_tiles[T - 1 - (int)atomicAdd(&s_large, 1u)] = (uint32_t)(k0 + q);
-        else if (c[q] > 512u) large_tiles[atomicAdd(&s_mid, 1u)] = (uint32_t)(k0 + q);  // see launch_tile_sort
+        cursor[(size_t)(k0 + q) * GSR_TILE_COUNT_STRIDE] = lo32;  // the scatter's cursor starts at the segment
         run = hi;
+      }
+    }
+    // list appends, one shared atomic per warp and list (c[q] = 0 beyond T)
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int q = 0; q < IPT; ++q) {
+      const bool large = c[q] > 2048u, mid = c[q] > 512u && !large;
+      const uint32_t mm = __ballot_sync(0xffffffffu, mid), ml = __ballot_sync(0xffffffffu, large);
+      if (mm) {
+        uint32_t b = 0;
+        if (lane == __ffs(mm) - 1) b = atomicAdd(&s_mid, __popc(mm));
+        b = __shfl_sync(0xffffffffu, b, __ffs(mm) - 1);
+        if (mid) large_tiles[b + __popc(mm & lt)] = (uint32_t)(k0 + q);  // see launch_tile_sort
+      }
+      if (ml) {
+        uint32_t b = 0;
+        if (lane == __ffs(ml) - 1) b = atomicAdd(&s_large, __popc(ml));
+        b = __shfl_sync(0xffffffffu, b, __ffs(ml) - 1);
+        if (large) large_tiles[T - 1 - (int)(b + __popc(ml & lt))] = (uint32_t)(k0 + q);
       }
     }
     carry += total;
@@ -82,20 +100,19 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* 
   }
 }
 
-cudaError_t launch_tile_scan(int T, const uint32_t* tile_count, uint2* ranges, uint32_t* large_tiles, GsrControl* ctrl,
-                             cudaStream_t s) {
+cudaError_t launch_tile_scan(int T, const uint32_t* tile_count, uint2* ranges, uint32_t* tile_cursor,
+                             uint32_t* large_tiles, GsrControl* ctrl, cudaStream_t s) {
   if (T <= 0) return cudaSuccess;
-  tile_scan_kernel<<<1, 1024, 0, s>>>(T, tile_count, ranges, large_tiles, ctrl);
+  tile_scan_kernel<<<1, 1024, 0, s>>>(T, tile_count, ranges, tile_cursor, large_tiles, ctrl);
   count_launch();
   return cudaGetLastError();
 }
 
 // ---- K4': scatter the composites into the tile segments ------------------------------------------
-// The rect is walked four instances at a time: four independent atomics (and segment-base loads) are
-// in flight before the first store needs its slot.
+// The rect is walked four instances at a time: four independent atomics are in flight before the first
+// store needs its slot.
 __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii,
-                                                           const GsrRec* __restrict__ recs,
-                                                           const uint2* __restrict__ ranges, uint32_t* cursor,
+                                                           const GsrRec* __restrict__ recs, uint32_t* cursor,
                                                            unsigned long long* __restrict__ comp, uint32_t capacity,
                                                            GsrControl* ctrl, BinningHeader* header) {
   const int i = blockIdx.x * 256 + threadIdx.x;
@@ -112,22 +129,19 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int gx, int gy
   bool over = false;
   int x = x0, y = y0;
   for (int k0 = 0; k0 < area; k0 += 4) {
-    uint32_t slot[4], first[4];
+    uint32_t idx[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      slot[q] = 0u; first[q] = 0xFFFFFFFFu;
+      idx[q] = 0xFFFFFFFFu;
       if (k0 + q < area) {
-        const uint32_t t = (uint32_t)(y * gx + x);
-        slot[q] = atomicAdd(&cursor[t * GSR_TILE_COUNT_STRIDE], 1u);
-        first[q] = ranges[t].x;
+        idx[q] = atomicAdd(&cursor[(uint32_t)(y * gx + x) * GSR_TILE_COUNT_STRIDE], 1u);  // cursors start at ranges[t].x
         if (++x == x1) { x = x0; ++y; }
       }
     }
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       if (k0 + q < area) {
-        const unsigned long long idx = (unsigned long long)first[q] + slot[q];
-        if (idx < capacity) comp[idx] = c;
+        if (idx[q] < capacity) comp[idx[q]] = c;
         else over = true;
       }
     }
@@ -135,12 +149,12 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int gx, int gy
   if (over) ctrl->overflow = 1u;
 }
 
-cudaError_t launch_tile_scatter(const GsrView& v, int P, const int32_t* radii, const GeomState& geom, const uint2* ranges,
-                                uint32_t* cursor, unsigned long long* comp, uint32_t capacity, GsrControl* ctrl,
-                                BinningHeader* header, cudaStream_t s) {
+cudaError_t launch_tile_scatter(const GsrView& v, int P, const int32_t* radii, const GeomState& geom, uint32_t* cursor,
+                                unsigned long long* comp, uint32_t capacity, GsrControl* ctrl, BinningHeader* header,
+                                cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
-  tile_scatter_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, v.gx, v.gy, radii, geom.recs, ranges, cursor, comp, capacity,
-                                                      ctrl, header);
+  tile_scatter_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, v.gx, v.gy, radii, geom.recs, cursor, comp, capacity, ctrl,
+                                                      header);
   count_launch();
   return cudaGetLastError();
 }
