@@ -15,7 +15,8 @@
 //     (segments above 8192 instances: the same network in place in global memory) and writes the
 //     sorted point list.
 // HBM traffic: 8 B/instance written by K4', 8 read + 4 written by K5', against (8 + 24 * 6) for the
-// radix sort at 1080p; the instruction count falls from ~1150 to ~300 per 32 instances.
+// radix sort at 1080p; the instruction count falls from ~1150 to ~330 per 32 instances
+// (profiles/README.md, r1_v7).  Measured on C3: 0.342 -> 0.196 ms per frame for the whole binning.
 #include "gsr_math.cuh"
 
 namespace gsr {
@@ -342,8 +343,7 @@ __device__ __forceinline__ void bitonic_sort_global(volatile u64* a, uint32_t n,
 constexpr uint32_t TS_SMALL_CAP = 512, TS_MID_CAP = 2048, TS_LARGE_CAP = 8192;
 
 template <int CAP, int THREADS>
-__device__ __forceinline__ void sort_segment(u64* s_comp, uint2* ranges, uint32_t t, u64* comp, uint32_t* vals,
-                                             uint32_t lo, uint32_t n, int tid) {
+__device__ __forceinline__ void sort_segment(u64* s_comp, u64* comp, uint32_t* vals, uint32_t lo, uint32_t n, int tid) {
   ulonglong2* s2 = reinterpret_cast<ulonglong2*>(s_comp);
   u64* seg = comp + lo;
   if (n <= (uint32_t)CAP) {
@@ -381,14 +381,14 @@ __global__ void __launch_bounds__(128) tile_sort_kernel(uint2* ranges, const uin
     const uint32_t lo = min(r.x, capacity), hi = min(r.y, capacity), n = hi - lo;
     if ((lo != r.x || hi != r.y) && lane == 0) ranges[t] = make_uint2(lo, hi);  // truncated frame (hint too small)
     if (n == 0u || n > TS_SMALL_CAP) return;
-    sort_segment<TS_SMALL_CAP, 32>(s_comp + TS_SMALL_CAP * warp, ranges, t, comp, vals, lo, n, lane);
+    sort_segment<TS_SMALL_CAP, 32>(s_comp + TS_SMALL_CAP * warp, comp, vals, lo, n, lane);
   } else {
     const uint32_t num = ctrl->num_mid;
     for (uint32_t k = blockIdx.x; k < num; k += mid_ctas) {
       const uint32_t t = mid_tiles[k];
       const uint2 r = ranges[t];  // possibly clamped already by the tile's warp above: clamping is idempotent
       const uint32_t lo = min(r.x, capacity), hi = min(r.y, capacity), n = hi - lo;
-      if (n > TS_SMALL_CAP) sort_segment<TS_MID_CAP, 128>(s_comp, ranges, t, comp, vals, lo, n, threadIdx.x);
+      if (n > TS_SMALL_CAP) sort_segment<TS_MID_CAP, 128>(s_comp, comp, vals, lo, n, threadIdx.x);
       __syncthreads();  // shared memory is reused by the next tile
     }
   }
@@ -405,7 +405,7 @@ __global__ void __launch_bounds__(512) tile_sort_large_kernel(uint2* ranges, con
     const uint2 r = ranges[t];  // clamped by the launch before
     const uint32_t n = r.y - r.x;
     if (n > TS_SMALL_CAP)
-      sort_segment<TS_LARGE_CAP, 512>(reinterpret_cast<u64*>(ts_smem), ranges, t, comp, vals, r.x, n, threadIdx.x);
+      sort_segment<TS_LARGE_CAP, 512>(reinterpret_cast<u64*>(ts_smem), comp, vals, r.x, n, threadIdx.x);
     __syncthreads();  // shared memory is reused by the next tile
   }
 }
