@@ -216,7 +216,7 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
             "preprocess kernel", debug, stream);
   if (segmented)
     GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(P > 0 ? num_tiles : 0, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
-                                             img.ctrl, stream),
+                                             img.tile_scan_state, img.ctrl, stream),
               "tile scan kernel", debug, stream);
   else
     GSR_STAGE(ST_SCAN, gsr::launch_scan(P, geom, img.ctrl, stream), "scan kernel", debug, stream);
@@ -241,10 +241,13 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
     if (!bin_ptr) return fail(GSR_EALLOC, "allocator returned NULL");
     BinningState bin = BinningState::carve(bin_ptr, cap, num_tiles);
     if (cap > 0 && P > 0 && segmented) {
-      if (attempt > 0)  // rebuild the un-truncated ranges, rewind the cursors
+      if (attempt > 0) {  // rebuild the un-truncated ranges, rewind the cursors (scan state and list counters zeroed)
+        GSR_CUDA(cudaMemsetAsync(img.tile_scan_state, 0, img.tile_scan_state_bytes, stream), "memset(tile scan state)");
+        GSR_CUDA(cudaMemsetAsync(img.ctrl, 0, sizeof(GsrControl), stream), "memset(control)");
         GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(num_tiles, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
-                                                 img.ctrl, stream),
+                                                 img.tile_scan_state, img.ctrl, stream),
                   "tile scan kernel", debug, stream);
+      }
       GSR_STAGE(ST_DUPLICATE, gsr::launch_tile_scatter(v, P, radii, geom, img.tile_cursor, bin.keys_a,
                                                        (uint32_t)cap, img.ctrl, bin.header, stream),
                 "tile scatter kernel", debug, stream);

@@ -96,6 +96,8 @@ struct ImgState {
   uint32_t* tile_count;   // instances per tile, counted by the preprocess kernel (tile_binning.cu)
   uint32_t* tile_cursor;  // the scatter's per-tile cursors (same layout), set to the segment starts by the tile scan
   uint32_t* large_tiles;  // lists of the tiles the MID (from the front) and LARGE (from the back) sort launches take
+  unsigned long long* tile_scan_state;  // status words of the chained tile scan, one per 1024 tiles
+  size_t tile_scan_state_bytes;
   GsrControl* ctrl;
   size_t ranges_off, bytes;
   static ImgState carve(char* base, int W, int H) {
@@ -111,6 +113,8 @@ struct ImgState {
     s.tile_count = (uint32_t*)take(T * 4 * GSR_TILE_COUNT_STRIDE);
     s.tile_cursor = (uint32_t*)take(T * 4 * GSR_TILE_COUNT_STRIDE);
     s.large_tiles = (uint32_t*)take(T * 4);
+    s.tile_scan_state_bytes = ((T + 1023) / 1024 + 1) * 8;
+    s.tile_scan_state = (unsigned long long*)take(s.tile_scan_state_bytes);
     s.ctrl = (GsrControl*)take(sizeof(GsrControl));
     s.bytes = off;
     return s;
@@ -231,7 +235,7 @@ cudaError_t launch_preprocess(const GsrView& v, const GsrGaussiansDev& g, int32_
                               uint32_t* tile_count, cudaStream_t s);
 // tile-segmented binning (tile_binning.cu)
 cudaError_t launch_tile_scan(int T, const uint32_t* tile_count, uint2* ranges, uint32_t* tile_cursor,
-                             uint32_t* large_tiles, GsrControl* ctrl, cudaStream_t s);
+                             uint32_t* large_tiles, unsigned long long* state, GsrControl* ctrl, cudaStream_t s);
 cudaError_t launch_tile_scatter(const GsrView& v, int P, const int32_t* radii, const GeomState& geom, uint32_t* cursor,
                                 unsigned long long* comp, uint32_t capacity, GsrControl* ctrl, BinningHeader* header,
                                 cudaStream_t s);

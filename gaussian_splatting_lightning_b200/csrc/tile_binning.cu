@@ -6,7 +6,7 @@
 // ties in ascending Gaussian index (the duplicated list is emitted in Gaussian order and the radix
 // sort is stable).  That result is produced here without a global sort:
 //   * the preprocess kernel counts the instances of every tile (one RED per instance);
-//   * K3' one CTA scans the T counts: ranges[t] = [first, last) directly (no K6), R = total;
+//   * K3' a chained scan over the T counts (1024 tiles per CTA): ranges[t] = [first, last) directly (no K6), R = total;
 //   * K4' every Gaussian claims a slot in each of its tiles' segments with an atomic cursor (a second
 //     counter array the scan set to the segment starts) and
 //     stores the 64-bit composite (depth bits << 32 | Gaussian index) there, in arbitrary order;
@@ -21,90 +21,112 @@
 
 namespace gsr {
 
-// ---- K3': exclusive scan of the per-tile counts, one CTA ----------------------------------------
-// 8192 counts per round (eight per thread, all loads in flight together), the running total carried from
-// round to round.  Empty tiles get [0, 0) like the reference's zero-initialised ranges.  Tiles above 512
-// instances go on the lists of the MID and LARGE sort launches (one array: MID from the front, LARGE from the
-// back).
-__global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* __restrict__ count,
-                                                         uint2* __restrict__ ranges, uint32_t* __restrict__ cursor,
-                                                         uint32_t* __restrict__ large_tiles, GsrControl* ctrl) {
-  constexpr int IPT = 8;
-  __shared__ unsigned long long s_warp[32];
-  __shared__ unsigned int s_mid, s_large;  // list cursors: shared atomics, the CTA is alone
+// ---- K3': exclusive scan of the per-tile counts ---------------------------------------------------
+// Chained scan: CTA b takes the tiles [1024 b, 1024 b + 1024) (four per thread; eight CTAs at 1080p, so that eight
+// SMs share the strided counter loads and cursor stores), publishes its total in a 64-bit status word and walks
+// back over its predecessors' words (decoupled look-back; tile = blockIdx.x, in-order CTA dispatch keeps every
+// predecessor resident or done).  Empty tiles get [0, 0) like the reference's zero-initialised ranges.  Tiles above
+// 512 instances go on the lists of the MID and LARGE sort launches (one array: MID from the front, LARGE from the
+// back), one global atomic per CTA and list.
+namespace {
+constexpr unsigned long long TSCAN_AGG = 1ull << 62, TSCAN_INC = 2ull << 62, TSCAN_VAL = (1ull << 62) - 1;
+constexpr int TSCAN_TILES = 1024;
+}  // namespace
+
+__global__ void __launch_bounds__(256) tile_scan_kernel(int T, const uint32_t* __restrict__ count,
+                                                        uint2* __restrict__ ranges, uint32_t* __restrict__ cursor,
+                                                        uint32_t* __restrict__ large_tiles, unsigned long long* state,
+                                                        GsrControl* ctrl) {
+  constexpr int IPT = TSCAN_TILES / 256;
+  __shared__ unsigned long long s_warp[8];
+  __shared__ unsigned long long s_excl;
+  __shared__ unsigned int s_mid, s_large, s_mid_base, s_large_base;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned int blk = blockIdx.x;
   if (tid == 0) { s_mid = 0u; s_large = 0u; }
+  const int k0 = (int)blk * TSCAN_TILES + IPT * tid;
+  uint32_t c[IPT];
+#pragma unroll
+  for (int q = 0; q < IPT; ++q) c[q] = (k0 + q < T) ? count[(size_t)(k0 + q) * GSR_TILE_COUNT_STRIDE] : 0u;
+  unsigned long long sum = 0;
+#pragma unroll
+  for (int q = 0; q < IPT; ++q) sum += c[q];
+  unsigned long long incl = sum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
+  }
+  if (lane == 31) s_warp[warp] = incl;
   __syncthreads();
-  unsigned long long carry = 0;
-  for (int base = 0; base < T; base += 1024 * IPT) {
-    const int k0 = base + IPT * tid;
-    uint32_t c[IPT];
+  unsigned long long wbase = 0, total = 0;
 #pragma unroll
-    for (int q = 0; q < IPT; ++q) c[q] = (k0 + q < T) ? count[(size_t)(k0 + q) * GSR_TILE_COUNT_STRIDE] : 0u;
-    unsigned long long sum = 0;
+  for (int w = 0; w < 8; ++w) {
+    const unsigned long long x = s_warp[w];
+    if (w < warp) wbase += x;
+    total += x;
+  }
+  // list slots inside the CTA (c[q] = 0 beyond T): one shared atomic per warp and list
+  const uint32_t lt = (1u << lane) - 1u;
+  uint32_t slot[IPT];
 #pragma unroll
-    for (int q = 0; q < IPT; ++q) sum += c[q];
-    unsigned long long incl = sum;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, d);
-      if (lane >= d) incl += t;
-    }
-    __syncthreads();  // s_warp of the previous round has been read
-    if (lane == 31) s_warp[warp] = incl;
-    __syncthreads();
-    unsigned long long wbase = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < 32; ++w) {
-      const unsigned long long x = s_warp[w];
-      if (w < warp) wbase += x;
-      total += x;
-    }
-    unsigned long long run = carry + wbase + incl - sum;
-#pragma unroll
-    for (int q = 0; q < IPT; ++q) {
-      if (k0 + q < T) {
-        const unsigned long long lo = run, hi = run + c[q];
-        const uint32_t lo32 = lo > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)lo;
-        const uint32_t hi32 = hi > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)hi;
-        ranges[k0 + q] = c[q] ? make_uint2(lo32, hi32) : make_uint2(0u, 0u);
-        cursor[(size_t)(k0 + q) * GSR_TILE_COUNT_STRIDE] = lo32;  // the scatter's cursor starts at the segment
-        run = hi;
-      }
-    }
-    // list appends, one shared atomic per warp and list (c[q] = 0 beyond T)
-    const uint32_t lt = (1u << lane) - 1u;
-#pragma unroll
-    for (int q = 0; q < IPT; ++q) {
-      const bool large = c[q] > 2048u, mid = c[q] > 512u && !large;
-      const uint32_t mm = __ballot_sync(0xffffffffu, mid), ml = __ballot_sync(0xffffffffu, large);
-      if (mm) {
-        uint32_t b = 0;
-        if (lane == __ffs(mm) - 1) b = atomicAdd(&s_mid, __popc(mm));
-        b = __shfl_sync(0xffffffffu, b, __ffs(mm) - 1);
-        if (mid) large_tiles[b + __popc(mm & lt)] = (uint32_t)(k0 + q);  // see launch_tile_sort
-      }
-      if (ml) {
-        uint32_t b = 0;
-        if (lane == __ffs(ml) - 1) b = atomicAdd(&s_large, __popc(ml));
-        b = __shfl_sync(0xffffffffu, b, __ffs(ml) - 1);
-        if (large) large_tiles[T - 1 - (int)(b + __popc(ml & lt))] = (uint32_t)(k0 + q);
-      }
-    }
-    carry += total;
+  for (int q = 0; q < IPT; ++q) {
+    const bool large = c[q] > 2048u, mid = c[q] > 512u && !large;
+    const uint32_t mm = __ballot_sync(0xffffffffu, mid), ml = __ballot_sync(0xffffffffu, large);
+    uint32_t bm = 0, bl = 0;
+    if (mm && lane == __ffs(mm) - 1) bm = atomicAdd(&s_mid, __popc(mm));
+    if (ml && lane == __ffs(ml) - 1) bl = atomicAdd(&s_large, __popc(ml));
+    if (mm) bm = __shfl_sync(0xffffffffu, bm, __ffs(mm) - 1);
+    if (ml) bl = __shfl_sync(0xffffffffu, bl, __ffs(ml) - 1);
+    slot[q] = mid ? bm + __popc(mm & lt) : bl + __popc(ml & lt);
   }
   __syncthreads();
   if (tid == 0) {
-    ctrl->num_rendered = carry > 0xFFFFFFFFull ? 0xFFFFFFFFu : (unsigned int)carry;
-    ctrl->num_mid = s_mid;
-    ctrl->num_large = s_large;
+    unsigned long long excl = 0;
+    volatile unsigned long long* st = state;
+    if (blk == 0) {
+      st[0] = TSCAN_INC | total;
+    } else {
+      st[blk] = TSCAN_AGG | total;
+      long long p = (long long)blk - 1;
+      while (true) {
+        const unsigned long long w = st[p];
+        if (w & TSCAN_INC) { excl += w & TSCAN_VAL; break; }
+        if (w & TSCAN_AGG) { excl += w & TSCAN_VAL; --p; }
+      }
+      st[blk] = TSCAN_INC | (excl + total);
+    }
+    s_excl = excl;
+    if (blk == gridDim.x - 1) {
+      const unsigned long long R = excl + total;
+      ctrl->num_rendered = R > 0xFFFFFFFFull ? 0xFFFFFFFFu : (unsigned int)R;
+    }
+    s_mid_base = s_mid ? atomicAdd(&ctrl->num_mid, s_mid) : 0u;
+    s_large_base = s_large ? atomicAdd(&ctrl->num_large, s_large) : 0u;
+  }
+  __syncthreads();
+  unsigned long long run = s_excl + wbase + incl - sum;
+#pragma unroll
+  for (int q = 0; q < IPT; ++q) {
+    if (k0 + q < T) {
+      const unsigned long long lo = run, hi = run + c[q];
+      const uint32_t lo32 = lo > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)lo;
+      const uint32_t hi32 = hi > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)hi;
+      ranges[k0 + q] = c[q] ? make_uint2(lo32, hi32) : make_uint2(0u, 0u);
+      cursor[(size_t)(k0 + q) * GSR_TILE_COUNT_STRIDE] = lo32;  // the scatter's cursor starts at the segment
+      if (c[q] > 2048u) large_tiles[T - 1 - (int)(s_large_base + slot[q])] = (uint32_t)(k0 + q);
+      else if (c[q] > 512u) large_tiles[s_mid_base + slot[q]] = (uint32_t)(k0 + q);  // see launch_tile_sort
+      run = hi;
+    }
   }
 }
 
+// state: (T + 1023) / 1024 status words, zeroed; ctrl->num_mid / num_large zeroed.
 cudaError_t launch_tile_scan(int T, const uint32_t* tile_count, uint2* ranges, uint32_t* tile_cursor,
-                             uint32_t* large_tiles, GsrControl* ctrl, cudaStream_t s) {
+                             uint32_t* large_tiles, unsigned long long* state, GsrControl* ctrl, cudaStream_t s) {
   if (T <= 0) return cudaSuccess;
-  tile_scan_kernel<<<1, 1024, 0, s>>>(T, tile_count, ranges, tile_cursor, large_tiles, ctrl);
+  tile_scan_kernel<<<(T + TSCAN_TILES - 1) / TSCAN_TILES, 256, 0, s>>>(T, tile_count, ranges, tile_cursor, large_tiles,
+                                                                      state, ctrl);
   count_launch();
   return cudaGetLastError();
 }
