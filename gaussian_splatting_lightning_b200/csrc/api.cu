@@ -215,7 +215,7 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
   GSR_STAGE(ST_PREPROCESS, gsr::launch_preprocess(v, g, radii, geom, segmented ? img.tile_count : nullptr, stream),
             "preprocess kernel", debug, stream);
   if (segmented)
-    GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(P > 0 ? num_tiles : 0, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
+    GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(P > 0 ? v.gx : 0, v.gy, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
                                              img.tile_scan_state, img.ctrl, stream),
               "tile scan kernel", debug, stream);
   else
@@ -244,7 +244,7 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
       if (attempt > 0) {  // rebuild the un-truncated ranges, rewind the cursors (scan state and list counters zeroed)
         GSR_CUDA(cudaMemsetAsync(img.tile_scan_state, 0, img.tile_scan_state_bytes, stream), "memset(tile scan state)");
         GSR_CUDA(cudaMemsetAsync(img.ctrl, 0, sizeof(GsrControl), stream), "memset(control)");
-        GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(num_tiles, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
+        GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(v.gx, v.gy, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
                                                  img.tile_scan_state, img.ctrl, stream),
                   "tile scan kernel", debug, stream);
       }

@@ -85,9 +85,13 @@ struct GeomState {
 };
 
 // ---- image buffer carving ----------------------------------------------------------
-// Per-tile instance counters sit one per 32-byte sector: the L2 atomic unit serialises the updates of a sector,
-// and neighbouring tiles are updated together.
-constexpr int GSR_TILE_COUNT_STRIDE = 8;
+// Per-tile instance counters.  The tiles (2k, y) and (2k + 1, y) share ONE 64-bit word (low / high half): a splat
+// that covers both is counted -- and later given its two slots -- by a single 64-bit atomic.  One word per 32-byte
+// sector: the L2 atomic unit serialises the updates of a sector, and neighbouring tiles are updated together.
+constexpr int GSR_TILE_COUNT_STRIDE = 8;  // 32-bit words per TILE of storage (a pair uses one sector of its two)
+__host__ __device__ inline size_t gsr_tile_pair_word(int x, int y, int gx) {  // index of the pair's 64-bit word
+  return ((size_t)y * (size_t)((gx + 1) >> 1) + (size_t)(x >> 1)) * 4;
+}
 
 struct ImgState {
   float* final_T;
@@ -234,7 +238,7 @@ cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, 
 cudaError_t launch_preprocess(const GsrView& v, const GsrGaussiansDev& g, int32_t* radii, const GeomState& geom,
                               uint32_t* tile_count, cudaStream_t s);
 // tile-segmented binning (tile_binning.cu)
-cudaError_t launch_tile_scan(int T, const uint32_t* tile_count, uint2* ranges, uint32_t* tile_cursor,
+cudaError_t launch_tile_scan(int gx, int gy, const uint32_t* tile_count, uint2* ranges, uint32_t* tile_cursor,
                              uint32_t* large_tiles, unsigned long long* state, GsrControl* ctrl, cudaStream_t s);
 cudaError_t launch_tile_scatter(const GsrView& v, int P, const int32_t* radii, const GeomState& geom, uint32_t* cursor,
                                 unsigned long long* comp, uint32_t capacity, GsrControl* ctrl, BinningHeader* header,

@@ -158,9 +158,14 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreArgs a) {
       tile_rect(pixx, pixy, radius, a.v.gx, a.v.gy, x0, y0, x1, y1);
       area = (x1 - x0) * (y1 - y0);
       if (area == 0) alive = false;
-      if (a.tile_count)  // one RED per instance; issued here so that they fly under the SH copy
+      if (a.tile_count && area) {  // one 64-bit RED per pair of tiles (gsr_common.cuh); they fly under the SH copy
+        unsigned long long* cnt = reinterpret_cast<unsigned long long*>(a.tile_count);
         for (int y = y0; y < y1; ++y)
-          for (int x = x0; x < x1; ++x) atomicAdd(&a.tile_count[(y * a.v.gx + x) * GSR_TILE_COUNT_STRIDE], 1u);
+          for (int xp = x0 >> 1; xp <= (x1 - 1) >> 1; ++xp) {
+            const unsigned long long inc = (2 * xp >= x0 ? 1ull : 0ull) | (2 * xp + 1 < x1 ? 1ull << 32 : 0ull);
+            atomicAdd(cnt + gsr_tile_pair_word(2 * xp, y, a.v.gx), inc);
+          }
+      }
       opac = a.g.opacities[i] * hscale;  // rasterize.py:72
     }
   }

@@ -33,7 +33,7 @@ constexpr unsigned long long TSCAN_AGG = 1ull << 62, TSCAN_INC = 2ull << 62, TSC
 constexpr int TSCAN_TILES = 1024;
 }  // namespace
 
-__global__ void __launch_bounds__(256) tile_scan_kernel(int T, const uint32_t* __restrict__ count,
+__global__ void __launch_bounds__(256) tile_scan_kernel(int T, int gx, const uint32_t* __restrict__ count,
                                                         uint2* __restrict__ ranges, uint32_t* __restrict__ cursor,
                                                         uint32_t* __restrict__ large_tiles, unsigned long long* state,
                                                         GsrControl* ctrl) {
@@ -47,7 +47,10 @@ __global__ void __launch_bounds__(256) tile_scan_kernel(int T, const uint32_t* _
   const int k0 = (int)blk * TSCAN_TILES + IPT * tid;
   uint32_t c[IPT];
 #pragma unroll
-  for (int q = 0; q < IPT; ++q) c[q] = (k0 + q < T) ? count[(size_t)(k0 + q) * GSR_TILE_COUNT_STRIDE] : 0u;
+  for (int q = 0; q < IPT; ++q) {  // the tile's half of its pair's 64-bit word
+    const int t = k0 + q, y = t / gx, x = t - y * gx;
+    c[q] = (t < T) ? count[gsr_tile_pair_word(x, y, gx) * 2 + (x & 1)] : 0u;
+  }
   unsigned long long sum = 0;
 #pragma unroll
   for (int q = 0; q < IPT; ++q) sum += c[q];
@@ -113,7 +116,10 @@ __global__ void __launch_bounds__(256) tile_scan_kernel(int T, const uint32_t* _
       const uint32_t lo32 = lo > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)lo;
       const uint32_t hi32 = hi > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)hi;
       ranges[k0 + q] = c[q] ? make_uint2(lo32, hi32) : make_uint2(0u, 0u);
-      cursor[(size_t)(k0 + q) * GSR_TILE_COUNT_STRIDE] = lo32;  // the scatter's cursor starts at the segment
+      {
+        const int t = k0 + q, y = t / gx, x = t - y * gx;
+        cursor[gsr_tile_pair_word(x, y, gx) * 2 + (x & 1)] = lo32;  // the scatter's cursor starts at the segment
+      }
       if (c[q] > 2048u) large_tiles[T - 1 - (int)(s_large_base + slot[q])] = (uint32_t)(k0 + q);
       else if (c[q] > 512u) large_tiles[s_mid_base + slot[q]] = (uint32_t)(k0 + q);  // see launch_tile_sort
       run = hi;
@@ -122,18 +128,17 @@ __global__ void __launch_bounds__(256) tile_scan_kernel(int T, const uint32_t* _
 }
 
 // state: (T + 1023) / 1024 status words, zeroed; ctrl->num_mid / num_large zeroed.
-cudaError_t launch_tile_scan(int T, const uint32_t* tile_count, uint2* ranges, uint32_t* tile_cursor,
+cudaError_t launch_tile_scan(int gx, int gy, const uint32_t* tile_count, uint2* ranges, uint32_t* tile_cursor,
                              uint32_t* large_tiles, unsigned long long* state, GsrControl* ctrl, cudaStream_t s) {
+  const int T = gx * gy;
   if (T <= 0) return cudaSuccess;
-  tile_scan_kernel<<<(T + TSCAN_TILES - 1) / TSCAN_TILES, 256, 0, s>>>(T, tile_count, ranges, tile_cursor, large_tiles,
-                                                                      state, ctrl);
+  tile_scan_kernel<<<(T + TSCAN_TILES - 1) / TSCAN_TILES, 256, 0, s>>>(T, gx, tile_count, ranges, tile_cursor,
+                                                                      large_tiles, state, ctrl);
   count_launch();
   return cudaGetLastError();
 }
 
 // ---- K4': scatter the composites into the tile segments ------------------------------------------
-// The rect is walked four instances at a time: four independent atomics are in flight before the first
-// store needs its slot.
 __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii,
                                                            const GsrRec* __restrict__ recs, uint32_t* cursor,
                                                            unsigned long long* __restrict__ comp, uint32_t capacity,
@@ -148,25 +153,31 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int gx, int gy
   int x0, y0, x1, y1;
   tile_rect(a.x, a.y, (float)r, gx, gy, x0, y0, x1, y1);
   const unsigned long long c = ((unsigned long long)__float_as_uint(depth) << 32) | (unsigned long long)(uint32_t)i;
-  const int area = (x1 - x0) * (y1 - y0);
+  // walk the rect by PAIRS of tiles (2k, 2k + 1): one 64-bit atomic on the pair's cursor word returns the slots of
+  // both halves; four pairs at a time, so that four independent atomics are in flight before the first store
+  unsigned long long* cur = reinterpret_cast<unsigned long long*>(cursor);
+  const int xp0 = x0 >> 1, npx = ((x1 - 1) >> 1) - xp0 + 1, npairs = npx * (y1 - y0);
   bool over = false;
-  int x = x0, y = y0;
-  for (int k0 = 0; k0 < area; k0 += 4) {
-    uint32_t idx[4];
+  int xp = xp0, y = y0;
+  for (int k0 = 0; k0 < npairs; k0 += 4) {
+    unsigned long long old[4];
+    uint32_t use[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      idx[q] = 0xFFFFFFFFu;
-      if (k0 + q < area) {
-        idx[q] = atomicAdd(&cursor[(uint32_t)(y * gx + x) * GSR_TILE_COUNT_STRIDE], 1u);  // cursors start at ranges[t].x
-        if (++x == x1) { x = x0; ++y; }
+      use[q] = 0u;
+      old[q] = 0ull;
+      if (k0 + q < npairs) {
+        use[q] = (2 * xp >= x0 ? 1u : 0u) | (2 * xp + 1 < x1 ? 2u : 0u);
+        const unsigned long long inc = (unsigned long long)(use[q] & 1u) | ((unsigned long long)(use[q] >> 1) << 32);
+        old[q] = atomicAdd(cur + gsr_tile_pair_word(2 * xp, y, gx), inc);  // cursors start at ranges[t].x
+        if (++xp == xp0 + npx) { xp = xp0; ++y; }
       }
     }
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      if (k0 + q < area) {
-        if (idx[q] < capacity) comp[idx[q]] = c;
-        else over = true;
-      }
+      const uint32_t ilo = (uint32_t)old[q], ihi = (uint32_t)(old[q] >> 32);
+      if (use[q] & 1u) { if (ilo < capacity) comp[ilo] = c; else over = true; }
+      if (use[q] & 2u) { if (ihi < capacity) comp[ihi] = c; else over = true; }
     }
   }
   if (over) ctrl->overflow = 1u;
