@@ -16,7 +16,7 @@
 //     sorted point list.
 // HBM traffic: 8 B/instance written by K4', 8 read + 4 written by K5', against (8 + 24 * 6) for the
 // radix sort at 1080p; the instruction count falls from ~1150 to ~330 per 32 instances
-// (profiles/README.md, r1_v7).  Measured on C3: 0.342 -> 0.184 ms per frame for the whole binning.
+// (profiles/README.md, r1_v7).  Measured on C3: 0.342 -> 0.174 ms per frame for the whole binning.
 #include "gsr_math.cuh"
 
 namespace gsr {
