@@ -110,6 +110,17 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreArgs a) {
   float px = 0.f, py = 0.f, pz = 0.f, zview = 0.f;
   const float* __restrict__ view = a.v.view;
   const float* __restrict__ proj = a.v.proj;
+  // every input of the Gaussian is requested before the first one is used (one round trip instead of a chain
+  // mean -> cull -> scale / rotation -> opacity); a culled Gaussian's loads are wasted, culled Gaussians are few
+  float4 q_in = make_float4(1.f, 0.f, 0.f, 0.f);
+  float sc_in[3] = {0.f, 0.f, 0.f}, op_in = 0.f;
+  if (alive) {
+    if (!a.g.cov3D_precomp) {
+      q_in = reinterpret_cast<const float4*>(a.g.rotations)[i];
+      sc_in[0] = a.g.scales[3 * i]; sc_in[1] = a.g.scales[3 * i + 1]; sc_in[2] = a.g.scales[3 * i + 2];
+    }
+    op_in = a.g.opacities[i];
+  }
   if (alive) {
     px = a.g.means3D[3 * i]; py = a.g.means3D[3 * i + 1]; pz = a.g.means3D[3 * i + 2];
     zview = xform_col(view, 2, px, py, pz);
@@ -130,9 +141,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreArgs a) {
 #pragma unroll
       for (int k = 0; k < 6; ++k) s6[k] = a.g.cov3D_precomp[6 * (size_t)i + k];
     } else {
-      const float4 q = reinterpret_cast<const float4*>(a.g.rotations)[i];
-      cov3d_from_scale_rot(a.g.scales[3 * i], a.g.scales[3 * i + 1], a.g.scales[3 * i + 2], a.v.scale_modifier, q,
-                           s6);
+      cov3d_from_scale_rot(sc_in[0], sc_in[1], sc_in[2], a.v.scale_modifier, q_in, s6);
     }
     JacobianCtx jc;
     build_jacobian(view, px, py, pz, a.v.fx, a.v.fy, a.v.tanfovx, a.v.tanfovy, jc);
@@ -166,7 +175,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreArgs a) {
             atomicAdd(cnt + gsr_tile_pair_word(2 * xp, y, a.v.gx), inc);
           }
       }
-      opac = a.g.opacities[i] * hscale;  // rasterize.py:72
+      opac = op_in * hscale;  // rasterize.py:72
     }
   }
 
