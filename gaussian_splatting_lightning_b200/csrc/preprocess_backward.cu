@@ -107,9 +107,12 @@ __device__ __forceinline__ void sh_backward(const float* __restrict__ sh, float*
 template <bool ACC, bool DSH_ACC>
 __device__ __forceinline__ void backward_one(const PreBwdArgs& a, const int i, const int radius,
                                              const float* __restrict__ sh_row, float* __restrict__ dsh_row,
-                                             const bool sh_vec4) {
+                                             const bool sh_vec4, unsigned long long* sh_bar = nullptr) {
+  // sh_bar: the mbarrier behind which the warp's SH block is still arriving in shared memory; it is waited for
+  // at the first touch of the block, so that the geometry part and its loads run under the copy.
   const int M = a.g.M;
   if (!(radius > 0)) {
+    if (sh_bar) mbar_wait(sh_bar, 0);
     if (!DSH_ACC && dsh_row) {  // a stored (or bulk-reduced) row of a culled Gaussian is all zeros
       if (sh_vec4) for (int k = 0; k < 3 * M / 4; ++k) reinterpret_cast<float4*>(dsh_row)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
       else for (int k = 0; k < 3 * M; ++k) dsh_row[k] = 0.f;
@@ -239,6 +242,7 @@ __device__ __forceinline__ void backward_one(const PreBwdArgs& a, const int i, c
   if (a.xyz_grad_count) atomicAdd(a.xyz_grad_count + i, 1.f);
 
   // SH
+  if (sh_bar) mbar_wait(sh_bar, 0);
   if (sh_row) {
     const float* __restrict__ cam = a.v.campos;
     const float dirx = px - cam[0], diry = py - cam[1], dirz = pz - cam[2];
@@ -346,8 +350,9 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdAr
   if (bulk) {
     // rows live in the warp's shared block; 128-bit row accesses need 16-byte rows
     const bool vec4 = (M & 3) == 0;
-    if (bulk_in) mbar_wait(&bars[warp], 0);
-    if (i < P) backward_one<ACC, false>(a, i, radius, blk + (size_t)lane * M * 3, a.dL_dsh ? blk + (size_t)lane * M * 3 : nullptr, vec4);
+    if (i < P) backward_one<ACC, false>(a, i, radius, blk + (size_t)lane * M * 3, a.dL_dsh ? blk + (size_t)lane * M * 3 : nullptr, vec4,
+                                        bulk_in ? &bars[warp] : nullptr);
+    if (bulk_in) mbar_wait(&bars[warp], 0);  // every lane, also those without a row: the block is complete below
     if (a.dL_dsh) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // my generic-proxy row writes -> async proxy
       __syncwarp();

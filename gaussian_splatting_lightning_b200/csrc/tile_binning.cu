@@ -147,9 +147,9 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int gx, int gy
   if (i == 0 && header) { header->capacity = capacity; header->num_tiles = (uint32_t)(gx * gy); header->segmented = 1u; }
   if (i >= P) return;
   const int r = radii[i];
-  if (r <= 0) return;
-  const float4 a = recs[i].a;
+  const float4 a = recs[i].a;        // requested together with the radius (a culled Gaussian's row is stale, unused)
   const float depth = recs[i].c.w;
+  if (r <= 0) return;
   int x0, y0, x1, y1;
   tile_rect(a.x, a.y, (float)r, gx, gy, x0, y0, x1, y1);
   const unsigned long long c = ((unsigned long long)__float_as_uint(depth) << 32) | (unsigned long long)(uint32_t)i;
