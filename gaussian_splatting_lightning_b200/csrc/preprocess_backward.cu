@@ -134,6 +134,12 @@ __device__ __forceinline__ void backward_one(const PreBwdArgs& a, const int i, c
   const float4 g0 = reinterpret_cast<const float4*>(a.grad_acc)[3 * (size_t)i];      // S0 S1 S2 S3
   const float4 g1 = reinterpret_cast<const float4*>(a.grad_acc)[3 * (size_t)i + 1];  // S4 S5 dr dg
   const float4 g2 = reinterpret_cast<const float4*>(a.grad_acc)[3 * (size_t)i + 2];  // db dinvz - -
+  // the inputs of the last sections are requested now, with everything else (one round trip, under the SH copy)
+  const bool want_sr = !a.g.cov3D_precomp && (a.dL_dscales || a.dL_drot);
+  const float4 q_in = want_sr ? reinterpret_cast<const float4*>(a.g.rotations)[i] : make_float4(1.f, 0.f, 0.f, 0.f);
+  const float sc0 = want_sr ? a.g.scales[3 * (size_t)i] : 0.f, sc1 = want_sr ? a.g.scales[3 * (size_t)i + 1] : 0.f,
+              sc2 = want_sr ? a.g.scales[3 * (size_t)i + 2] : 0.f;
+  const unsigned cl_in = sh_row ? a.clamped[i] : 0u;
   const float* __restrict__ view = a.v.view;
   const float* __restrict__ proj = a.v.proj;
   const float fx = a.v.fx, fy = a.v.fy;
@@ -248,7 +254,7 @@ __device__ __forceinline__ void backward_one(const PreBwdArgs& a, const int i, c
     const float dirx = px - cam[0], diry = py - cam[1], dirz = pz - cam[2];
     const float len = sqrtf(dirx * dirx + diry * diry + dirz * dirz);
     const float x = dirx / len, y = diry / len, z = dirz / len;
-    const unsigned cl = a.clamped[i];
+    const unsigned cl = cl_in;
     const float g3[3] = {(cl & 1u) ? 0.f : g1.z, (cl & 2u) ? 0.f : g1.w, (cl & 4u) ? 0.f : g2.x};
     float ddir[3];
     switch (a.v.deg) {
@@ -270,12 +276,11 @@ __device__ __forceinline__ void backward_one(const PreBwdArgs& a, const int i, c
   // cov3D -> scale, rotation
   if (!a.g.cov3D_precomp) {
     if (!a.dL_dscales && !a.dL_drot) return;
-    const float4 q = reinterpret_cast<const float4*>(a.g.rotations)[i];
+    const float4 q = q_in;
     float R[3][3];
     quat_to_R(q, R);
     const float mod = a.v.scale_modifier;
-    const float s[3] = {mod * a.g.scales[3 * (size_t)i], mod * a.g.scales[3 * (size_t)i + 1],
-                        mod * a.g.scales[3 * (size_t)i + 2]};
+    const float s[3] = {mod * sc0, mod * sc1, mod * sc2};
     const float Gm[3][3] = {{dS[0], 0.5f * dS[1], 0.5f * dS[2]},
                             {0.5f * dS[1], dS[3], 0.5f * dS[4]},
                             {0.5f * dS[2], 0.5f * dS[4], dS[5]}};
@@ -320,7 +325,7 @@ __device__ __forceinline__ void backward_one(const PreBwdArgs& a, const int i, c
 // Everything is per warp (no CTA barrier).  Falls back to per-lane global accesses when the block
 // is not 16-byte sized / aligned (odd M, unaligned tensors, ragged last warp).
 template <bool ACC>
-__global__ void __launch_bounds__(256) preprocess_backward_kernel(const PreBwdArgs a) {
+__global__ void __launch_bounds__(256, 3) preprocess_backward_kernel(const PreBwdArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) unsigned long long bars[8];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
