@@ -279,7 +279,7 @@ def run_ours(args):
             bufs.zero_()        # per-step buffers: gradient sum and the statistics DELTAS of this step's views
         vstreams.run(len(cams), lambda j: one_view(cams[j], fwd_only))
         if world > 1 and not fwd_only:
-            bufs.all_reduce()   # sum(flat), sum(stats), max(max_radii) over the ranks
+            bufs.all_reduce()   # sum(flat + stats) in one collective, max(max_radii) over the ranks
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):

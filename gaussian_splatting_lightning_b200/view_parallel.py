@@ -14,7 +14,7 @@ plus the step's densification-statistics deltas, taken per view BEFORE the views
     stats[1] = number of views with radii > 0                                   (xyz_grad_count delta)
     max_radii = max over views of radii                                         (max_radii2D candidate)
 
-One exchange per step: all_reduce(sum) of `flat`, all_reduce(sum) of `stats`, all_reduce(max) of
+One exchange per step: ONE all_reduce(sum) of `flat` + `stats` (adjacent sections of one storage), all_reduce(max) of
 `max_radii`.  Every rank then applies the identical optimiser / densification update, so the
 replicas stay bit-identical.  There is no collective inside the render path.
 
@@ -46,9 +46,15 @@ class StepBuffers:
         self.P, self.M = P, M
         self.widths = dict(dL_dmeans3D=3, dL_dsh=3 * M, dL_dopacity=1, dL_dscales=3, dL_drotations=4)
         self.floats_per_gaussian = sum(self.widths.values())
-        self.flat = torch.zeros(P * self.floats_per_gaussian, device=device, dtype=dtype)
-        self.stats = torch.zeros(2, P, device=device, dtype=dtype)
-        self.max_radii = torch.zeros(P, device=device, dtype=dtype)
+        # one storage [flat | stats | max_radii], sections on 128-byte boundaries: one memset per step, and the two
+        # summed sections leave in ONE all-reduce
+        pad = lambda n: (n + 31) // 32 * 32
+        n_flat, n_stats = pad(P * self.floats_per_gaussian), pad(2 * P)
+        self._store = torch.zeros(n_flat + n_stats + P, device=device, dtype=dtype)
+        self._summed = self._store[:n_flat + n_stats]
+        self.flat = self._store[:P * self.floats_per_gaussian]
+        self.stats = self._store[n_flat:n_flat + 2 * P].view(2, P)
+        self.max_radii = self._store[n_flat + n_stats:]
         self._views: Dict[str, torch.Tensor] = {}
         o = 0
         for name, w in self.widths.items():
@@ -66,17 +72,14 @@ class StepBuffers:
         return dict(max_radii2D=self.max_radii, xyz_grad_accum=self.stats[0], xyz_grad_count=self.stats[1])
 
     def zero_(self) -> None:
-        self.flat.zero_()
-        self.stats.zero_()
-        self.max_radii.zero_()
+        self._store.zero_()
 
     # -- the one exchange step --------------------------------------------------------------------
     def all_reduce(self, group=None, async_op: bool = False):
         """Sum gradients and statistics deltas, max the radii, over the ranks of `group`."""
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
             return []
-        works = [dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op),
-                 dist.all_reduce(self.stats, op=dist.ReduceOp.SUM, group=group, async_op=async_op),
+        works = [dist.all_reduce(self._summed, op=dist.ReduceOp.SUM, group=group, async_op=async_op),
                  dist.all_reduce(self.max_radii, op=dist.ReduceOp.MAX, group=group, async_op=async_op)]
         return [w for w in works if w is not None]
 
