@@ -106,3 +106,19 @@ def test_world2_exchange_matches_single_process_sum():
         w_acc[vis] += norm[vis, None]                                # gaussian_model.py:178-181
         w_cnt[vis] += 1
     assert torch.equal(max_r, w_max) and torch.allclose(acc, w_acc, atol=1e-6) and torch.equal(cnt, w_cnt)
+
+
+def test_step_buffers_share_one_storage():
+    """flat | stats | max_radii are 128-byte aligned sections of one storage: one memset clears the step,
+    the two summed sections are adjacent (one all-reduce)."""
+    buf = StepBuffers(10, 16, "cpu")
+    base = buf.flat.data_ptr()
+    assert (buf.stats.data_ptr() - base) % 128 == 0 and (buf.max_radii.data_ptr() - base) % 128 == 0
+    assert buf.flat.data_ptr() < buf.stats.data_ptr() < buf.max_radii.data_ptr()
+    assert buf.stats.shape == (2, 10) and buf.stats.is_contiguous() and buf.max_radii.shape == (10,)
+    assert buf._summed.data_ptr() == base
+    assert buf._summed.data_ptr() + 4 * buf._summed.numel() == buf.max_radii.data_ptr()
+    buf.flat.fill_(1.0); buf.stats.fill_(2.0); buf.max_radii.fill_(3.0)
+    assert float(buf._summed.sum()) == 590 + 40 and float(buf.max_radii.sum()) == 30   # sections do not overlap
+    buf.zero_()
+    assert not buf.flat.any() and not buf.stats.any() and not buf.max_radii.any()
