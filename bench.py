@@ -46,23 +46,31 @@ def parse_args():
     ap.add_argument("--workload", default="C3", choices=list(synthetic.CONFIGS))
     ap.add_argument("--views-per-rank", type=int, default=8)
     ap.add_argument("--streams", type=int, default=3, help="CUDA streams the views of a step are spread over")
+    ap.add_argument("--partition", default="block", choices=["block", "interleaved"],
+                    help="which of the step's N*views-per-rank views a rank owns (see view_index)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
 
-def view_index(rank: int, j: int, vpr: int) -> int:
-    """global view g -> orbit slot: 0, +1, -1, +2, -2, ... around view 0."""
-    g = rank * vpr + j
+def view_index(rank: int, j: int, vpr: int, world: int = 1, partition: str = "block") -> int:
+    """global view g -> orbit slot: 0, +1, -1, +2, -2, ... around view 0.
+
+    The views get lighter away from view 0 (fewer Gaussians in the frustum).  "block" (default): rank r owns
+    g = r*vpr .. r*vpr + vpr - 1, so rank 0 renders exactly the N = 1 views whatever N and the max-over-ranks
+    timing of the weak-scaling bench is never flattered by lighter views.  "interleaved": g = j*N + r, the
+    assignment of view_parallel.partition_views (rank r owns k = r mod N) -- the balanced split of a FIXED
+    set of N*vpr views, for the strong-scaling runs of C4 (64 cameras per step)."""
+    g = rank * vpr + j if partition == "block" else j * world + rank
     return ((g + 1) // 2) * (1 if g % 2 else -1) % ORBIT_VIEWS
 
 
-def make_cameras(W, H, rank, vpr, device):
+def make_cameras(W, H, rank, vpr, device, world=1, partition="block"):
     from gaussian_splatting_lightning_b200.rasterizer import GaussianRasterizationSettings
     cams = []
     bg = torch.zeros(3, device=device)
     for j in range(vpr):
-        c = synthetic.make_camera(W, H, k=view_index(rank, j, vpr), num_views=ORBIT_VIEWS)
+        c = synthetic.make_camera(W, H, k=view_index(rank, j, vpr, world, partition), num_views=ORBIT_VIEWS)
         cams.append(dict(host=c, settings=GaussianRasterizationSettings(
             image_height=H, image_width=W, tanfovx=c["tanfovx"], tanfovy=c["tanfovy"], bg=bg, scale_modifier=1.0,
             viewmatrix=c["viewmatrix"].to(device), projmatrix=c["projmatrix"].to(device), sh_degree=3,
@@ -245,7 +253,7 @@ def run_ours(args):
     vpr = args.views_per_rank
     scene_cpu = synthetic.make_scene(P, deg, W, H, seed=0)
     scene = {k: v.to(device) for k, v in scene_cpu.items()}
-    cams = make_cameras(W, H, rank, vpr, device)
+    cams = make_cameras(W, H, rank, vpr, device, world, args.partition)
     for c in cams:
         c["settings"] = c["settings"]._replace(sh_degree=deg)
     g = torch.Generator(device="cpu").manual_seed(1234 + rank)
@@ -530,7 +538,7 @@ def run_ours(args):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {P} Gaussians, SH degree {deg}, {W}x{H}, fwd+bwd + densification "
                                f"stats, {vpr} views per GPU per step" + (", NCCL all-reduce of 59 floats/Gaussian + stats" if world > 1 else ""),
-                   "views_per_rank": vpr, "frames_per_step": vpr * world, "streams_per_rank": args.streams, "parallelism": f"view-parallel x{world}",
+                   "views_per_rank": vpr, "frames_per_step": vpr * world, "streams_per_rank": args.streams, "parallelism": f"view-parallel x{world}", "partition": args.partition,
                    "l2": (lambda mb: f"inputs ({mb:.0f} MB of Gaussian parameters + {48 * P / 1e6:.0f} MB records) "
                           + ("exceed the 126 MB L2; no flush" if mb > 126 else
                              "fit the 126 MB L2: a parity-test size, not a bench line"))((44 + 12 * M) * P / 1e6),
