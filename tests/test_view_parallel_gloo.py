@@ -122,3 +122,21 @@ def test_step_buffers_share_one_storage():
     assert float(buf._summed.sum()) == 590 + 40 and float(buf.max_radii.sum()) == 30   # sections do not overlap
     buf.zero_()
     assert not buf.flat.any() and not buf.stats.any() and not buf.max_radii.any()
+
+
+def test_bench_partitions_cover_the_same_views():
+    """bench.py --partition block / interleaved split the SAME global views; interleaved is partition_views."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location(
+        "gsr_bench", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    for world, vpr in ((1, 8), (2, 32), (4, 16), (8, 8)):
+        block = [[bench.view_index(r, j, vpr, world, "block") for j in range(vpr)] for r in range(world)]
+        inter = [[bench.view_index(r, j, vpr, world, "interleaved") for j in range(vpr)] for r in range(world)]
+        assert sorted(sum(block, [])) == sorted(sum(inter, [])) and len(set(sum(block, []))) == world * vpr
+        assert block[0] == [bench.view_index(0, j, vpr) for j in range(vpr)]          # rank 0 = the N = 1 views
+        slot = [bench.view_index(0, g, world * vpr) for g in range(world * vpr)]       # global view g -> orbit slot
+        for r in range(world):
+            assert inter[r] == [slot[g] for g in partition_views(world * vpr, world, r)]
