@@ -42,6 +42,21 @@ class GaussianRasterizationSettings(NamedTuple):
 # Last num_rendered per (device, W, H): sizes the binning buffer of the next frame up front so
 # that the frame is enqueued without a device->host round trip (gsr_forward's binning_hint).
 _hint = {}
+_recent = {}
+# How often the hint was too small and gsr_forward re-ran binning + compositing (bench.py reports it per region).
+counters = {"forward_calls": 0, "hint_retries": 0}
+
+
+def _bucket(n: int) -> int:
+    """Binning capacity rounded up to 4-8 steps per octave.  Every view has its own R; sizing the binning buffer to
+    R * 1.125 exactly made every request a different size, which the caching allocator answers with splits and, in
+    the end, new cudaMalloc calls inside steady-state steps (measured: reserved memory grew from 18.4 to 20.6 GB over
+    200 C3 steps and the regions that saw cudaMalloc calls ran at 13.4 ms per step instead of 12.1 --
+    tools/diag_regions.py).  Bucketed sizes repeat, so freed blocks are reused as they are."""
+    if n <= 65536:
+        return 65536
+    step = 1 << (n.bit_length() - 3)
+    return (n + step - 1) // step * step
 
 
 def _sync_mode() -> bool:
@@ -104,7 +119,15 @@ def forward_raw(rs: GaussianRasterizationSettings, means3D, sh, colors_precomp, 
         if alloc.error is not None:
             raise alloc.error
         N.check(rc, "gsr_forward")
-        _hint[key] = int(R.value * 1.125) + 4096
+        counters["forward_calls"] += 1
+        if 0 < binning_hint < R.value:
+            counters["hint_retries"] += 1
+        # the largest of the last 8 frames at this resolution: the views of a step differ in R, and a hint that is too
+        # small costs a second binning + compositing pass while one that is too large costs only memory
+        recent = _recent.setdefault(key, [])
+        recent.append(_bucket(int(R.value * 1.125) + 4096))
+        del recent[:-8]
+        _hint[key] = max(recent)
     return (int(R.value), color, radii, alloc.buffers[N.GSR_BUF_GEOM], alloc.buffers[N.GSR_BUF_BINNING],
             alloc.buffers[N.GSR_BUF_IMG], invdepth, int(cap.value))
 
@@ -198,7 +221,10 @@ def accumulate_gradients_into(grads, stats=None):
     (StepBuffers.densify_stats()).  Their backward then ADDS the parameter gradients straight into
     those tensors inside the preprocess-backward kernel (GSR_GRADS_ACCUMULATE) and updates the
     densification statistics there, and hands autograd None for the inputs it covered -- so autograd
-    neither allocates per-view gradient tensors nor runs its own accumulation kernels.  Point
+    neither allocates per-view gradient tensors nor runs its own accumulation kernels.  Only LEAF inputs
+    are covered: an input that is the result of an activation (exp / sigmoid / normalize / cat, the way the
+    unchanged GSLightningModule calls the rasterizer) gets its gradient through autograd as usual, so the
+    chain to the raw parameters is never cut.  Point
     `param.grad` at the same tensors (training.parameter_groups_on) and the optimiser sees the sum over
     the views.  The dummy means2D leaf still receives its gradient through autograd when it requires one.
     """
@@ -218,6 +244,11 @@ class _RasterizeGaussians(torch.autograd.Function):
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                 raster_settings):
         ctx.sink = (_sink.grads, _sink.stats) if _sink.grads is not None else None
+        # The sink may take over the gradient of an input only when that input is a LEAF: for an activation
+        # (the reference passes exp(_scaling), sigmoid(_opacity), normalize(_rotation), cat(dc, rest):
+        # gs_lightning_module.py:337-348) autograd has to receive the gradient to carry it on to the parameters.
+        ctx.leaf = tuple(t is None or t.is_leaf for t in (means3D, means2D, sh, colors_precomp, opacities, scales,
+                                                          rotations, cov3Ds_precomp))
         num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepths, _cap = forward_raw(
             raster_settings, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
         ctx.raster_settings = raster_settings
@@ -252,7 +283,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                           dL_dcov3D=(P, 6), dL_dsh=(P, M, 3), dL_dscales=(P, 3), dL_drotations=(P, 4))
             acc, fresh = {}, {}
             for n in want:
-                if n in sink_grads:
+                if n in sink_grads and ctx.leaf[1 if n == "dL_dmeans2D" else _SINK_INPUT[n]]:
                     acc[n] = sink_grads[n]
                 else:
                     acc[n] = fresh[n] = torch.zeros(shapes[n], dtype=torch.float32, device=means3D.device)

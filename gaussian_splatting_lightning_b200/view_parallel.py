@@ -5,7 +5,7 @@ views of the optimiser step and accumulates their gradients -- straight from the
 kernel, GSR_GRADS_ACCUMULATE -- into ONE flat fp32 buffer laid out for a single all-reduce:
 
     flat = [ dL_dmeans3D (P,3) | dL_dsh (P,M,3) | dL_dopacity (P,1) | dL_dscales (P,3) | dL_drotations (P,4) ]
-           = 59 floats per Gaussian at SH degree 3
+           = 59 floats per Gaussian at SH degree 3, every section padded to a 128-byte boundary
 
 plus the step's densification-statistics deltas, taken per view BEFORE the views are summed
 (gs_lightning/modules/gaussian_model.py:174-181, gs_lightning/lightning/gs_lightning_module.py:192-195):
@@ -39,28 +39,38 @@ def partition_views(num_views: int, world_size: int, rank: int) -> List[int]:
 
 
 class StepBuffers:
-    """The per-step exchange buffers of one rank."""
+    """The per-step exchange buffers of one rank.
+
+    ONE storage [grad sections | stats | max_radii]; EVERY section starts on a 128-byte boundary whatever P is
+    (after the first densify / prune P is almost never a multiple of 4, and gsr_backward needs a 16-byte aligned
+    dL_drotations and takes the bulk-reduction path for dL_dsh only when that block is 16-byte aligned).  The
+    padding floats stay zero and travel with the all-reduce (< 128 bytes per section).
+    """
+
+    ALIGN = 32   # floats: 128 bytes
 
     def __init__(self, num_gaussians: int, sh_coeffs: int, device, dtype=torch.float32):
         P, M = int(num_gaussians), int(sh_coeffs)
         self.P, self.M = P, M
         self.widths = dict(dL_dmeans3D=3, dL_dsh=3 * M, dL_dopacity=1, dL_dscales=3, dL_drotations=4)
         self.floats_per_gaussian = sum(self.widths.values())
-        # one storage [flat | stats | max_radii], sections on 128-byte boundaries: one memset per step, and the two
-        # summed sections leave in ONE all-reduce
-        pad = lambda n: (n + 31) // 32 * 32
-        n_flat, n_stats = pad(P * self.floats_per_gaussian), pad(2 * P)
-        self._store = torch.zeros(n_flat + n_stats + P, device=device, dtype=dtype)
-        self._summed = self._store[:n_flat + n_stats]
-        self.flat = self._store[:P * self.floats_per_gaussian]
-        self.stats = self._store[n_flat:n_flat + 2 * P].view(2, P)
-        self.max_radii = self._store[n_flat + n_stats:]
-        self._views: Dict[str, torch.Tensor] = {}
+        pad = lambda n: (n + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        self.offsets: Dict[str, int] = {}
         o = 0
         for name, w in self.widths.items():
+            self.offsets[name] = o
+            o += pad(P * w)
+        n_flat, n_stats = o, 2 * pad(P)
+        self._store = torch.zeros(n_flat + n_stats + pad(P), device=device, dtype=dtype)
+        self._summed = self._store[:n_flat + n_stats]
+        self.flat = self._store[:n_flat]                         # the gradient sections incl. their padding
+        self._stats2 = self._store[n_flat:n_flat + n_stats].view(2, pad(P))
+        self.stats = self._stats2[:, :P]                         # rows start 128-byte aligned
+        self.max_radii = self._store[n_flat + n_stats:n_flat + n_stats + P]
+        self._views: Dict[str, torch.Tensor] = {}
+        for name, w in self.widths.items():
             shape = (P, M, 3) if name == "dL_dsh" else (P, w)
-            self._views[name] = self.flat[o:o + P * w].view(shape)
-            o += P * w
+            self._views[name] = self.flat[self.offsets[name]:self.offsets[name] + P * w].view(shape)
 
     # -- what the rasterizer backward writes into -------------------------------------------------
     def grads(self) -> Dict[str, torch.Tensor]:
@@ -71,20 +81,33 @@ class StepBuffers:
         """pass as backward_raw(..., stats=...)."""
         return dict(max_radii2D=self.max_radii, xyz_grad_accum=self.stats[0], xyz_grad_count=self.stats[1])
 
-    def zero_(self) -> None:
-        self._store.zero_()
+    def zero_(self, keep_max_radii: bool = False) -> None:
+        """Clear the step.  keep_max_radii: leave the radii candidates alone (deferred max exchange, see all_reduce)."""
+        (self._summed if keep_max_radii else self._store).zero_()
 
     # -- the one exchange step --------------------------------------------------------------------
-    def all_reduce(self, group=None, async_op: bool = False):
-        """Sum gradients and statistics deltas, max the radii, over the ranks of `group`."""
+    def all_reduce(self, group=None, async_op: bool = False, max_radii: bool = True):
+        """Sum gradients and statistics deltas (ONE collective over adjacent sections) and max the radii over the
+        ranks of `group`.
+
+        max_radii=False defers the second collective: max commutes with the steps, so a rank may keep folding its OWN
+        views' radii into `max_radii` step after step (zero_(keep_max_radii=True)) and call all_reduce_max_radii()
+        only when densification reads max_radii2D (every `densify_interval` steps in the reference,
+        gs_lightning_module.py:197-214) -- the result is the same maximum."""
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
             return []
-        works = [dist.all_reduce(self._summed, op=dist.ReduceOp.SUM, group=group, async_op=async_op),
-                 dist.all_reduce(self.max_radii, op=dist.ReduceOp.MAX, group=group, async_op=async_op)]
+        works = [dist.all_reduce(self._summed, op=dist.ReduceOp.SUM, group=group, async_op=async_op)]
+        if max_radii:
+            works.append(dist.all_reduce(self.max_radii, op=dist.ReduceOp.MAX, group=group, async_op=async_op))
         return [w for w in works if w is not None]
 
-    def exchanged_bytes(self) -> int:
-        return (self.flat.numel() + self.stats.numel() + self.max_radii.numel()) * self.flat.element_size()
+    def all_reduce_max_radii(self, group=None, async_op: bool = False):
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return None
+        return dist.all_reduce(self.max_radii, op=dist.ReduceOp.MAX, group=group, async_op=async_op)
+
+    def exchanged_bytes(self, max_radii: bool = True) -> int:
+        return (self._summed.numel() + (self.max_radii.numel() if max_radii else 0)) * self.flat.element_size()
 
     # -- consumers ----------------------------------------------------------------------------------
     def apply_densify_stats(self, max_radii2D: torch.Tensor, xyz_grad_accum: torch.Tensor,

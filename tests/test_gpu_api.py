@@ -187,3 +187,88 @@ def test_ply_checkpoint_and_collated_cameras_through_the_render_path(tmp_path):
                                                                    opacities=d["opacities"], scales=d["scales"],
                                                                    rotations=d["rotations"])[0]
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("P", [5001, 5002, 5003])
+def test_step_buffers_with_P_not_a_multiple_of_4(P):
+    """after a densify / prune P % 4 != 0; every section of the step buffer must still satisfy
+    gsr_backward's alignment (dL_drotations 16 bytes) -- through render_step and accumulate_gradients_into."""
+    from gaussian_splatting_lightning_b200.rasterizer import GaussianRasterizer, accumulate_gradients_into, backward_raw
+    from gaussian_splatting_lightning_b200.view_parallel import StepBuffers, render_step
+    W, H, deg = 160, 96, 3
+    scene = {k: v.to(U.DEV) for k, v in U.synthetic.make_scene(P, deg, W, H, seed=P).items()}
+    cams = [U.settings_from_camera(U.synthetic_case(8, deg, W, H, view_k=k, num_views=8)[0]) for k in (0, 1)]
+    g = torch.Generator().manual_seed(3)
+    dC = torch.randn(3, H, W, generator=g).to(U.DEV)
+    bufs = StepBuffers(P, (deg + 1) ** 2, U.DEV)
+    for v in bufs.grads().values():
+        assert v.data_ptr() % 128 == 0
+    render_step(cams, scene, dC, None, bufs, exchange=False)
+    step_sum = {n: t.clone() for n, t in bufs.grads().items()}
+    # the same two views one at a time through the plain (non-accumulating) backward
+    want = None
+    for rs in cams:
+        from gaussian_splatting_lightning_b200.rasterizer import forward_raw
+        R, color, radii, geom, binning, img, invd, cap = forward_raw(rs, scene["means3D"], scene["shs"], None,
+                                                                    scene["opacities"], scene["scales"], scene["rotations"], None)
+        gr = backward_raw(rs, scene["means3D"], radii, scene["shs"], None, scene["opacities"], scene["scales"],
+                          scene["rotations"], None, dC, None, geom, binning, img, R)
+        named = dict(dL_dopacity=gr[2], dL_dmeans3D=gr[3], dL_dsh=gr[5], dL_dscales=gr[6], dL_drotations=gr[7])
+        want = named if want is None else {n: want[n] + named[n] for n in named}
+    for n, w in want.items():
+        s = max(1.0, float(w.abs().max()))
+        assert float((step_sum[n] - w).abs().max()) / s <= 2e-5, n
+    # and through the autograd API with the fused accumulation
+    bufs.zero_()
+    params = {k: scene[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    for rs in cams:
+        with accumulate_gradients_into(bufs.grads(), bufs.densify_stats()):
+            color, radii, invd = GaussianRasterizer(rs)(means3D=params["means3D"], means2D=None, shs=params["shs"],
+                                                        opacities=params["opacities"], scales=params["scales"],
+                                                        rotations=params["rotations"])
+        (color * dC).sum().backward()
+    for n, w in want.items():
+        s = max(1.0, float(w.abs().max()))
+        assert float((bufs.grads()[n] - w).abs().max()) / s <= 2e-5, n
+    assert all(p.grad is None for p in params.values())      # leaves: the sink took their gradients
+
+
+def test_sink_does_not_cut_the_chain_through_activations():
+    """the reference passes ACTIVATIONS to the rasterizer (exp(_scaling), sigmoid(_opacity),
+    normalize(_rotation), cat(dc, rest): gs_lightning_module.py:337-348).  Inside accumulate_gradients_into the raw
+    parameters must still receive their gradients through autograd -- the sink only takes over leaf inputs."""
+    from gaussian_splatting_lightning_b200.rasterizer import GaussianRasterizer, accumulate_gradients_into
+    from gaussian_splatting_lightning_b200.view_parallel import StepBuffers
+    P, W, H, deg = 6000, 160, 96, 3
+    scene = {k: v.to(U.DEV) for k, v in U.synthetic.make_scene(P, deg, W, H, seed=77).items()}
+    rs = U.settings_from_camera(U.synthetic_case(8, deg, W, H)[0])
+    g = torch.Generator().manual_seed(5)
+    dC = torch.randn(3, H, W, generator=g).to(U.DEV)
+
+    def raw_params():
+        return dict(xyz=scene["means3D"].clone().requires_grad_(True),
+                    scaling=scene["scales"].log().requires_grad_(True),
+                    opacity=torch.logit(scene["opacities"]).requires_grad_(True),
+                    rotation=(scene["rotations"] * 1.7).requires_grad_(True),
+                    dc=scene["shs"][:, :1].clone().requires_grad_(True),
+                    rest=scene["shs"][:, 1:].clone().requires_grad_(True))
+
+    def render(p):
+        return GaussianRasterizer(rs)(means3D=p["xyz"], means2D=None, shs=torch.cat([p["dc"], p["rest"]], 1),
+                                      opacities=torch.sigmoid(p["opacity"]), scales=torch.exp(p["scaling"]),
+                                      rotations=torch.nn.functional.normalize(p["rotation"]))[0]
+
+    a = raw_params()
+    (render(a) * dC).sum().backward()
+    b = raw_params()
+    bufs = StepBuffers(P, (deg + 1) ** 2, U.DEV)
+    with accumulate_gradients_into(bufs.grads(), bufs.densify_stats()):
+        img = render(b)
+    (img * dC).sum().backward()
+    for k in a:
+        # xyz IS a leaf input of the rasterizer: its gradient went into the sink instead
+        got = bufs.grads()["dL_dmeans3D"] if k == "xyz" else b[k].grad
+        assert got is not None, k
+        s = max(1.0, float(a[k].grad.abs().max()))
+        assert float((a[k].grad - got).abs().max()) / s <= 2e-5, k
+    assert b["xyz"].grad is None and float(bufs.densify_stats()["xyz_grad_count"].sum()) > 0

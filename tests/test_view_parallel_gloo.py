@@ -6,6 +6,7 @@ import os
 import socket
 
 import numpy as np
+import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
@@ -70,14 +71,33 @@ def test_partition_covers_every_view_once():
 
 def test_flat_layout_is_one_contiguous_buffer():
     buf = StepBuffers(10, 16, "cpu")
-    assert buf.floats_per_gaussian == 59 and buf.flat.numel() == 590
+    # sections padded to 32 floats: 30 -> 32, 480, 10 -> 32, 30 -> 32, 40 -> 64
+    assert buf.floats_per_gaussian == 59 and buf.flat.numel() == 32 + 480 + 32 + 32 + 64
     off = 0
     for n in GRAD_FIELDS:
         v = buf.grads()[n]
         assert v.is_contiguous() and v.data_ptr() == buf.flat.data_ptr() + 4 * off
-        off += v.numel()
+        off += (v.numel() + 31) // 32 * 32
     assert off == buf.flat.numel()
-    assert buf.exchanged_bytes() == (590 + 20 + 10) * 4
+    assert buf.exchanged_bytes() == (640 + 64 + 10) * 4 and buf.exchanged_bytes(max_radii=False) == (640 + 64) * 4
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 5001, 5002, 5003, 4096])
+def test_every_section_is_128_byte_aligned_whatever_P(P):
+    """After a densify / prune P is rarely a multiple of 4; gsr_backward needs dL_drotations 16-byte aligned
+    (csrc/api.cu) and takes the bulk-reduction path for dL_dsh only when that block is aligned."""
+    buf = StepBuffers(P, 16, "cpu")
+    base = buf.flat.data_ptr()
+    assert base % 64 == 0          # torch CPU allocations are 64-byte aligned; CUDA ones 512
+    for n, v in buf.grads().items():
+        assert (v.data_ptr() - base) % 128 == 0 and v.is_contiguous(), n
+    for t in (buf.stats[0], buf.stats[1], buf.max_radii):
+        assert (t.data_ptr() - base) % 128 == 0 and t.is_contiguous() and t.numel() == P
+    # sections do not overlap: fill each with its own value, read the others back
+    for i, v in enumerate(list(buf.grads().values()) + [buf.stats[0], buf.stats[1], buf.max_radii]):
+        v.fill_(float(i + 1))
+    for i, v in enumerate(list(buf.grads().values()) + [buf.stats[0], buf.stats[1], buf.max_radii]):
+        assert bool((v == float(i + 1)).all())
 
 
 def test_world2_exchange_matches_single_process_sum():
@@ -115,11 +135,13 @@ def test_step_buffers_share_one_storage():
     base = buf.flat.data_ptr()
     assert (buf.stats.data_ptr() - base) % 128 == 0 and (buf.max_radii.data_ptr() - base) % 128 == 0
     assert buf.flat.data_ptr() < buf.stats.data_ptr() < buf.max_radii.data_ptr()
-    assert buf.stats.shape == (2, 10) and buf.stats.is_contiguous() and buf.max_radii.shape == (10,)
+    assert buf.stats.shape == (2, 10) and buf.stats[0].is_contiguous() and buf.max_radii.shape == (10,)
     assert buf._summed.data_ptr() == base
     assert buf._summed.data_ptr() + 4 * buf._summed.numel() == buf.max_radii.data_ptr()
     buf.flat.fill_(1.0); buf.stats.fill_(2.0); buf.max_radii.fill_(3.0)
-    assert float(buf._summed.sum()) == 590 + 40 and float(buf.max_radii.sum()) == 30   # sections do not overlap
+    assert float(buf._summed.sum()) == 640 + 40 and float(buf.max_radii.sum()) == 30   # sections do not overlap
+    buf.zero_(keep_max_radii=True)
+    assert not buf.flat.any() and not buf.stats.any() and float(buf.max_radii.sum()) == 30
     buf.zero_()
     assert not buf.flat.any() and not buf.stats.any() and not buf.max_radii.any()
 
