@@ -50,6 +50,8 @@ def parse_args():
                     help="which of the step's N*views-per-rank views a rank owns (see view_index)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the secondary blocks (single view per step, C1, C4 strong scaling, C5 render only)")
     return ap.parse_args()
 
 
@@ -202,7 +204,7 @@ def stage_model(P, M, Pvis, R, L, A, HW, T, passes):
         binning = {"scan": dict(bytes=4 * T + 8 * T),                  # tile scan: counts in, ranges out
                    "duplicate": dict(bytes=4 * P + 36 * Pvis + 12 * R),  # scatter: radii, record, 4 B cursor + 8 B composite
                    "sort": dict(bytes=8 * T + 12 * R),                  # per-tile sort: composite in, point list out
-                   "tile_ranges": dict(bytes=0)}
+                   "tile_ranges": dict(bytes=12 * T)}                   # tile order (LPT): ranges in, order out
     return {
         "preprocess": dict(bytes=52 * P + (12 * M + 67) * Pvis),
         **binning,
@@ -212,32 +214,290 @@ def stage_model(P, M, Pvis, R, L, A, HW, T, passes):
     }
 
 
-def workload_counters(cams, scene, device):
-    """P_vis, R, L, A averaged over this rank's views, from radii / n_contrib of the CUDA forward
-    (the oracle's definitions: L = sum over tiles of the max n_contrib, A = sum over pixels)."""
-    from gaussian_splatting_lightning_b200.rasterizer import export_state, forward_raw
-    acc = dict(Pvis=0.0, R=0.0, L=0.0, A=0.0)
-    for c in cams:
+# which roofline bounds a stage: the compositing kernels are bound by FP32 instruction issue, the
+# per-Gaussian kernels by HBM bytes, the binning stages by latency / L2 transactions (reported against HBM bytes)
+STAGE_BOUND = {"render_forward": "fp32_issue", "render_backward": "fp32_issue"}
+DENSIFY_INTERVAL = 100   # gs_lightning/lightning/gs_lightning_module.py:32,198: densification reads max_radii2D every 100 steps
+NCU_COUNTS = os.path.join(ROOT, "profiles", "ncu_counts.json")   # per-launch counters of the committed ncu capture
+
+
+class Rig:
+    """One workload on one rank: replicated scene, this rank's cameras, step buffers, view streams."""
+
+    def __init__(self, workload, vpr, streams, device, rank, world, partition, seed_grad=1234):
+        from gaussian_splatting_lightning_b200.view_parallel import StepBuffers, ViewStreams
+        self.workload, self.vpr, self.world, self.rank, self.device = workload, vpr, world, rank, device
+        self.P, self.deg, self.W, self.H = synthetic.config(workload)
+        self.M = (self.deg + 1) ** 2
+        self.scene_cpu = synthetic.make_scene(self.P, self.deg, self.W, self.H, seed=0)
+        self.scene = {k: v.to(device) for k, v in self.scene_cpu.items()}
+        self.cams = make_cameras(self.W, self.H, rank, vpr, device, world, partition)
+        for c in self.cams:
+            c["settings"] = c["settings"]._replace(sh_degree=self.deg)
+        g = torch.Generator(device="cpu").manual_seed(seed_grad + rank)
+        self.dL_dcolor = torch.randn(3, self.H, self.W, generator=g).to(device)
+        self.dL_dinv = torch.randn(1, self.H, self.W, generator=g).to(device)
+        # per-step exchange buffers: flat gradient buffer [means3D 3 | sh 3M | opacity 1 | scales 3 | rot 4]
+        # (59 floats per Gaussian at M = 16) + densification-statistics deltas (view_parallel.py)
+        self.bufs = StepBuffers(self.P, self.M, device)
+        self.acc_into, self.stat_into = self.bufs.grads(), self.bufs.densify_stats()
+        self.n_streams = streams
+        self.steps_done = 0
+        self.vstreams = ViewStreams(device, streams)   # independent views of a step round-robin over CUDA streams
+
+    def one_view(self, c, fwd_only=False):
+        from gaussian_splatting_lightning_b200.rasterizer import backward_raw, forward_raw
+        rs, sc = c["settings"], self.scene
+        R, color, radii, geom, binning, img, invd, cap = forward_raw(
+            rs, sc["means3D"], sc["shs"], None, sc["opacities"], sc["scales"], sc["rotations"], None)
+        if fwd_only:
+            return color
+        # gradients += into the flat all-reduce buffer and the view's densification statistics
+        # (gaussian_model.py:174-181), both fused into the preprocess backward kernel
+        backward_raw(rs, sc["means3D"], radii, sc["shs"], None, sc["opacities"], sc["scales"], sc["rotations"], None,
+                     self.dL_dcolor, self.dL_dinv, geom, binning, img, R, accumulate_into=self.acc_into,
+                     stats=self.stat_into)
+        return color
+
+    def step(self, fwd_only=False):
+        if not fwd_only:
+            # per-step buffers: gradient sum and statistics DELTAS of this step's views; the radii candidates stay
+            # (max commutes with the steps: their exchange is deferred to densification time, StepBuffers.all_reduce)
+            self.bufs.zero_(keep_max_radii=self.world > 1)
+        self.vstreams.run(len(self.cams), lambda j: self.one_view(self.cams[j], fwd_only))
+        if self.world > 1 and not fwd_only:
+            self.bufs.all_reduce(max_radii=False)   # sum(flat + stats): ONE collective per step
+            self.steps_done += 1
+            if self.steps_done % DENSIFY_INTERVAL == 0:
+                self.bufs.all_reduce_max_radii()    # the deferred max, when densification would read max_radii2D
+
+    def free(self):
+        for k in list(self.__dict__):
+            delattr(self, k)
+        torch.cuda.empty_cache()
+
+
+def timed(fn, steps, warmup, device, world):
+    """`steps` calls of fn between barrier + synchronize, CUDA events, max over ranks -> (ms, t0, t1)."""
+    import torch.distributed as dist
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t1 = time.time()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item()), t0, t1
+
+
+def regions(fn, steps, n, device, world, warmup=0):
+    """n timed regions of `steps` steps each -> (median ms, sorted list of ms, [(t0, t1)])."""
+    out = [timed(fn, steps, warmup if i == 0 else 0, device, world) for i in range(n)]
+    ms = sorted(o[0] for o in out)
+    return ms[len(ms) // 2] if len(ms) % 2 else 0.5 * (ms[len(ms) // 2 - 1] + ms[len(ms) // 2]), ms, [(o[1], o[2]) for o in out]
+
+
+def workload_counters(rig):
+    """P_vis, R, L, A averaged over this rank's views, from radii / n_contrib of the CUDA forward (the oracle's
+    definitions: L = sum over tiles of the max n_contrib, A = sum over pixels), and what the backward compositing
+    kernel really evaluates, counted from the forward's hit words (rasterizer.hit_word_stats)."""
+    from gaussian_splatting_lightning_b200.rasterizer import export_state, forward_raw, hit_word_stats
+    acc = dict(Pvis=0.0, R=0.0, L=0.0, A=0.0, visits_both=0.0, visits_single=0.0, pairs_evaluated=0.0)
+    first = None
+    sc = rig.scene
+    for c in rig.cams:
         rs = c["settings"]
         R, color, radii, geom, binning, img, invd, cap = forward_raw(
-            rs, scene["means3D"], scene["shs"], None, scene["opacities"], scene["scales"], scene["rotations"], None,
-            binning_hint=0)
-        st = export_state(rs, scene["means3D"].shape[0], radii, geom, binning, img, R, cap)
+            rs, sc["means3D"], sc["shs"], None, sc["opacities"], sc["scales"], sc["rotations"], None, binning_hint=0)
+        st = export_state(rs, rig.P, radii, geom, binning, img, R, cap)
         nc = st["n_contrib"].to(torch.int64)
         H, W = nc.shape
         gy, gx = (H + 15) // 16, (W + 15) // 16
-        pad = torch.zeros((gy * 16, gx * 16), dtype=torch.int64, device=device)
+        pad = torch.zeros((gy * 16, gx * 16), dtype=torch.int64, device=rig.device)
         pad[:H, :W] = nc
         tile_max = pad.view(gy, 16, gx, 16).amax(dim=(1, 3))
+        hw = hit_word_stats(rs, binning, st["n_contrib"], st["ranges"], cap)
         acc["Pvis"] += float((radii > 0).sum()); acc["R"] += float(R)
         acc["L"] += float(tile_max.sum()); acc["A"] += float(nc.sum())
+        for k in ("visits_both", "visits_single", "pairs_evaluated"):
+            acc[k] += float(hw[k])
+        if first is None:
+            first = dict(hw, R=float(R))
         del st
-    return {k: v / len(cams) for k, v in acc.items()}
+    out = {k: v / len(rig.cams) for k, v in acc.items()}
+    out["view0"] = first
+    return out
+
+
+class E2E:
+    """The same step through the public autograd API with HOST inputs: per view a pinned-host ground-truth image and
+    the camera are copied host->device (copy stream, a ring of streams+1 slots like a prefetching loader, inside the
+    timed region) and the loss is read back device->host.  The parameters are leaves whose .grad are views of the
+    step's flat gradient buffer (training.parameter_groups_on); the rasterizer backward adds into it in-kernel
+    (rasterizer.accumulate_gradients_into).  The activations and optimizer.step of GSLightningModule.training_step are
+    NOT part of this region (they are torch elementwise kernels + one fused Adam launch: e2e.neighbours times Adam)."""
+
+    def __init__(self, rig):
+        from gaussian_splatting_lightning_b200.training import l1_loss, parameter_groups_on, photometric_loss
+        self.rig = rig
+        dev, H, W, vpr = rig.device, rig.H, rig.W, rig.vpr
+        self.params = {k: rig.scene[k].clone().requires_grad_(True)
+                       for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+        self.gt_host = [torch.rand(3, H, W).pin_memory() for _ in rig.cams]
+        self.cam_host = [torch.cat([c["host"]["viewmatrix"].reshape(-1), c["host"]["projmatrix"].reshape(-1),
+                                    c["host"]["campos"].reshape(-1), torch.zeros(3)]).pin_memory() for c in rig.cams]
+        self.loss_host = torch.zeros(vpr).pin_memory()
+        parameter_groups_on(rig.bufs, self.params)
+        self.copy_stream = torch.cuda.Stream(dev)
+        self.n_slots = rig.n_streams + 1
+        self.slots = [dict(cam=torch.empty(38, device=dev), gt=torch.empty(3, H, W, device=dev),
+                           ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(self.n_slots)]
+        self.loss_fns = {"l1": l1_loss, "full": lambda c_, g_: photometric_loss(c_[None], g_[None], 0.2)[0]}
+        self.loss_kind = "l1"
+        self.h2d_bytes_per_step = vpr * (3 * H * W * 4 + 38 * 4)
+        self.d2h_bytes_per_step = vpr * 4
+
+    def upload(self, j):
+        """this step's host inputs of view j -> device, on the copy stream; every byte is copied inside the timed region"""
+        sl = self.slots[j % self.n_slots]
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(sl["free"])           # the view that used this slot last is done with it
+            sl["cam"].copy_(self.cam_host[j], non_blocking=True)
+            sl["gt"].copy_(self.gt_host[j], non_blocking=True)
+            sl["ready"].record(self.copy_stream)
+
+    def view(self, j):
+        from gaussian_splatting_lightning_b200.rasterizer import GaussianRasterizer, accumulate_gradients_into
+        rig, p = self.rig, self.params
+        st = torch.cuda.current_stream()                 # ViewStreams.run: view j on stream j mod n
+        if j + self.n_slots - 1 < rig.vpr:
+            self.upload(j + self.n_slots - 1)            # its slot was freed by view j-1; overlaps the rendering
+        sl = self.slots[j % self.n_slots]
+        st.wait_event(sl["ready"])
+        cam_d, gt = sl["cam"], sl["gt"]
+        rs = rig.cams[j]["settings"]._replace(viewmatrix=cam_d[0:16].view(4, 4), projmatrix=cam_d[16:32].view(4, 4),
+                                              campos=cam_d[32:35], bg=cam_d[35:38])
+        sp = torch.zeros_like(p["means3D"], requires_grad=True)
+        with accumulate_gradients_into(rig.acc_into, rig.stat_into):
+            color, radii, invd = GaussianRasterizer(rs)(
+                means3D=p["means3D"], means2D=sp, shs=p["shs"], colors_precomp=None, opacities=p["opacities"],
+                scales=p["scales"], rotations=p["rotations"], cov3D_precomp=None)
+        loss = self.loss_fns[self.loss_kind](color, gt)
+        loss.backward()
+        self.loss_host[j].copy_(loss.detach(), non_blocking=True)
+        sl["free"].record(st)
+
+    def step(self):
+        rig = self.rig
+        main = torch.cuda.current_stream()
+        rig.bufs.zero_(keep_max_radii=rig.world > 1)
+        for j in range(min(self.n_slots - 1, rig.vpr)):
+            self.upload(j)
+        rig.vstreams.run(rig.vpr, self.view)
+        if rig.world > 1:
+            rig.bufs.all_reduce(max_radii=False)
+        main.synchronize()                               # the step's result (losses) is on the host
+        return float(self.loss_host.sum())
+
+
+def ev_ms(fn, reps=20):
+    for _ in range(3):
+        fn()
+    a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); a_.record()
+    for _ in range(reps):
+        fn()
+    b_.record(); torch.cuda.synchronize()
+    return a_.elapsed_time(b_) / reps
+
+
+def neighbours(rig, e2e):
+    """The training-step neighbours of the path, each one launch, HBM bound."""
+    from gaussian_splatting_lightning_b200.training import FusedAdam, densify_fold, fused_ssim, l1_loss
+    device, P, H, W = rig.device, rig.P, rig.H, rig.W
+    params, bufs = e2e.params, rig.bufs
+    hbm_pk = peaks()[0]
+    opt = FusedAdam([{"params": [params[k]], "lr": lr} for k, lr in
+                     (("means3D", 1.6e-4), ("shs", 2.5e-3), ("opacities", 5e-2), ("scales", 5e-3), ("rotations", 1e-3))],
+                    lr=0.0, eps=1e-15)
+    n_par = sum(p_.numel() for p_ in params.values())
+    img_a, img_b = torch.rand(3, H, W, device=device, requires_grad=True), torch.rand(3, H, W, device=device)
+    run_stats = [torch.zeros(P, device=device) for _ in range(3)]
+    out = []
+    for name, fn, nbytes in (
+            ("adam (5 groups, one launch, zero_grad fused)", lambda: opt.step(zero_grad=True), 32 * n_par),
+            ("l1_loss value + unit gradient", lambda: l1_loss(img_a, img_b), 12 * 3 * H * W),
+            ("densify_fold", lambda: densify_fold(bufs.max_radii, bufs.stats[0], bufs.stats[1], *run_stats), 32 * P)):
+        ms_ = ev_ms(fn)
+        out.append({"kernel": name, "ms": ms_, "algorithmic_bytes": nbytes, "GBps": nbytes / (ms_ * 1e6),
+                    "hbm_frac": nbytes / (ms_ * 1e6) / hbm_pk})
+    # fused SSIM (value + gradient, one launch) next to the reference's own CUDA kernels (oracle/_ref, compiled from
+    # /root/reference/submodules/fused-ssim by oracle/build_ref.py) on the same image pair: fusedssim + fusedssim_backward
+    im_a, im_b = img_a.detach()[None].clone().requires_grad_(True), img_b[None]
+    ms_ = ev_ms(lambda: fused_ssim(im_a, im_b))
+    ent = {"kernel": "fused_ssim value + gradient (one launch)", "ms": ms_, "algorithmic_bytes": 12 * 3 * H * W,
+           "GBps": 12 * 3 * H * W / (ms_ * 1e6), "hbm_frac": 12 * 3 * H * W / (ms_ * 1e6) / hbm_pk}
+    try:
+        from oracle import build_ref
+        if build_ref.available():
+            ref_mod = build_ref.load()
+            dmap = torch.full_like(im_b, 1.0 / im_b.numel())
+
+            def ref_ssim():
+                _m, d1, d2, d3 = ref_mod.fusedssim(0.01 ** 2, 0.03 ** 2, im_a.detach(), im_b, True)
+                ref_mod.fusedssim_backward(0.01 ** 2, 0.03 ** 2, im_a.detach(), im_b, dmap, d1, d2, d3)
+            ent["reference_cuda_ms"] = ev_ms(ref_ssim)
+            ent["reference"] = "submodules/fused-ssim fusedssim + fusedssim_backward (oracle/_ref), same GPU"
+    except Exception as ex:  # the checker is optional on the box
+        ent["reference"] = f"unavailable: {ex}"
+    out.append(ent)
+    return out
+
+
+def extra_block(workload, vpr, streams, partition, steps, device, rank, world, fwd_only=False, with_e2e=False, n_regions=3):
+    """A secondary measurement of the same path (BASELINE.json's other configurations / usages): median of n_regions
+    regions of `steps` steps, same timing rules as the headline."""
+    rig = Rig(workload, vpr, streams, device, rank, world, partition)
+    for _ in range(3):
+        rig.step(fwd_only)
+    med, ms, _ = regions(lambda: rig.step(fwd_only), steps, n_regions, device, world)
+    frames = steps * vpr * world
+    out = {"workload": f"{workload}: {rig.P} Gaussians, SH degree {rig.deg}, {rig.W}x{rig.H}", "views_per_rank": vpr,
+           "streams_per_rank": streams, "partition": partition, "n_gpus": world, "steps": steps,
+           "what": "render only (forward)" if fwd_only else "forward + backward + densification stats"
+                   + (", one NCCL all-reduce of the step buffer per step" if world > 1 else ""),
+           "value": frames / (med / 1e3), "unit": UNIT, "ms_per_step": med / steps,
+           "regions_ms_per_step": [round(m / steps, 3) for m in ms]}
+    if not fwd_only:
+        medf, _, _ = regions(lambda: rig.step(True), steps, n_regions, device, world, warmup=2)
+        out["forward_only"] = {"value": frames / (medf / 1e3), "unit": UNIT, "ms_per_step": medf / steps}
+    if with_e2e:
+        e = E2E(rig)
+        mede, _, _ = regions(e.step, steps, n_regions, device, world, warmup=2)
+        out["e2e"] = {"value": frames / (mede / 1e3), "unit": UNIT, "h2d_bytes_per_step": e.h2d_bytes_per_step,
+                      "d2h_bytes_per_step": e.d2h_bytes_per_step}
+        del e
+    rig.free()
+    return out
 
 
 def run_ours(args):
     from gaussian_splatting_lightning_b200 import _native as N
-    from gaussian_splatting_lightning_b200.rasterizer import GaussianRasterizer, backward_raw, forward_raw
+    from gaussian_splatting_lightning_b200 import rasterizer as RZ
+    from gaussian_splatting_lightning_b200.view_parallel import ViewStreams
     import torch.distributed as dist
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -248,111 +508,53 @@ def run_ours(args):
     device = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
-    P, deg, W, H = synthetic.config(args.workload)
-    M = (deg + 1) ** 2
     vpr = args.views_per_rank
-    scene_cpu = synthetic.make_scene(P, deg, W, H, seed=0)
-    scene = {k: v.to(device) for k, v in scene_cpu.items()}
-    cams = make_cameras(W, H, rank, vpr, device, world, args.partition)
-    for c in cams:
-        c["settings"] = c["settings"]._replace(sh_degree=deg)
-    g = torch.Generator(device="cpu").manual_seed(1234 + rank)
-    dL_dcolor = torch.randn(3, H, W, generator=g).to(device)
-    dL_dinv = torch.randn(1, H, W, generator=g).to(device)
-
-    # per-step exchange buffers: flat gradient buffer [means3D 3 | sh 3M | opacity 1 | scales 3 | rot 4]
-    # (59 floats per Gaussian at M = 16) + densification-statistics deltas (view_parallel.py)
-    from gaussian_splatting_lightning_b200.view_parallel import StepBuffers
-    bufs = StepBuffers(P, M, device)
-    acc_into, stat_into = bufs.grads(), bufs.densify_stats()
-
-    def one_view(c, fwd_only=False):
-        rs = c["settings"]
-        R, color, radii, geom, binning, img, invd, cap = forward_raw(
-            rs, scene["means3D"], scene["shs"], None, scene["opacities"], scene["scales"], scene["rotations"], None)
-        if fwd_only:
-            return color
-        # gradients += into the flat all-reduce buffer and the view's densification statistics
-        # (gaussian_model.py:174-181), both fused into the preprocess backward kernel
-        backward_raw(rs, scene["means3D"], radii, scene["shs"], None, scene["opacities"], scene["scales"],
-                     scene["rotations"], None, dL_dcolor, dL_dinv, geom, binning, img, R,
-                     accumulate_into=acc_into, stats=stat_into)
-        return color
-
-    from gaussian_splatting_lightning_b200.view_parallel import ViewStreams
-    vstreams = ViewStreams(device, args.streams)   # independent views of a step round-robin over CUDA streams
-
-    def step(fwd_only=False):
-        if not fwd_only:
-            bufs.zero_()        # per-step buffers: gradient sum and the statistics DELTAS of this step's views
-        vstreams.run(len(cams), lambda j: one_view(cams[j], fwd_only))
-        if world > 1 and not fwd_only:
-            bufs.all_reduce()   # sum(flat + stats) in one collective, max(max_radii) over the ranks
-
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
-            fn()
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0 = time.time()
-        e0.record()
-        for _ in range(steps):
-            fn()
-        e1.record()
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        t1 = time.time()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=device)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item()), t0, t1
-
-    counters = workload_counters(cams, scene, device)
+    rig = Rig(args.workload, vpr, args.streams, device, rank, world, args.partition)
+    P, deg, W, H, M = rig.P, rig.deg, rig.W, rig.H, rig.M
+    counters = workload_counters(rig)
     K, Wm = args.steps, max(args.warmup, 3)
+    REGIONS = 5
 
     # ---- headline: fwd+bwd, inputs resident in HBM -------------------------------------------------
-    # The timed region (exactly K steps, barrier + synchronize on both sides, CUDA events, max over
-    # ranks) is measured ATTEMPTS times with nvidia-smi sampling clocks concurrently, and once more
-    # with no poller at all.  The poller is another driver client: on some boxes its queries were
-    # measured to stall this process's launches for whole regions (43.8 and 90.7 ms per step against
-    # 19.4 ms).  value = the fastest sampled attempt; if even that is > 10 % slower than the unsampled
-    # region the unsampled one is reported and `clocks` says so.  All attempts are listed.
-    ATTEMPTS = 3
+    # REGIONS timed regions of exactly K steps each (barrier + synchronize on both sides, CUDA events, max over
+    # ranks) with nvidia-smi sampling clocks concurrently; value = the MEDIAN region, min / max listed beside it.
+    # One more region runs first with the poller already up and is not counted: the poller is another driver
+    # client and its start was measured to stall this process's launches (82 ms per step for one region,
+    # tools/diag_regions.py --poller).  Instrumented per region: binning-hint retries, cudaMalloc calls.
     for _ in range(Wm):
-        step()
+        rig.step()
     torch.cuda.synchronize()
     l0 = N.launch_count()
-    ms_clean, _, _ = timed(step, K, 0)
+    ms_unsampled, _, _ = timed(rig.step, K, 0, device, world)
     launches = N.launch_count() - l0
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    attempts = [timed(step, K, 0) for _ in range(ATTEMPTS)]
-    best = min(attempts, key=lambda a: a[0])
-    clocks = sampler.stop(best[1], best[2]) if rank == 0 else None
-    ms_total = best[0]
+    timed(rig.step, K, 0, device, world)
+    per_region = []
+    for _ in range(REGIONS):
+        c0, m0 = dict(RZ.counters), torch.cuda.memory_stats(device).get("num_device_alloc", 0)
+        ms_, t0_, t1_ = timed(rig.step, K, 0, device, world)
+        per_region.append(dict(ms=ms_, t0=t0_, t1=t1_, hint_retries=RZ.counters["hint_retries"] - c0["hint_retries"],
+                               cuda_mallocs=torch.cuda.memory_stats(device).get("num_device_alloc", 0) - m0))
+    order = sorted(per_region, key=lambda r: r["ms"])
+    ms_total = order[len(order) // 2]["ms"]
+    clocks = sampler.stop(min(r["t0"] for r in per_region), max(r["t1"] for r in per_region)) if rank == 0 else None
     if clocks is not None:
-        clocks["sampled_attempts_ms_per_step"] = [round(a[0] / K, 3) for a in attempts]
-        clocks["unsampled_ms_per_step"] = round(ms_clean / K, 3)
-        clocks["value_from"] = "fastest sampled attempt"
-    if ms_total > 1.10 * ms_clean:
-        ms_total = ms_clean
-        if clocks is not None:
-            clocks["value_from"] = ("unsampled region (every sampled attempt was > 10 % slower: the nvidia-smi poller "
-                                    "stalled launches); clocks are those of the adjacent sampled attempts")
+        clocks["regions_ms_per_step"] = [round(r["ms"] / K, 3) for r in per_region]
+        clocks["unsampled_ms_per_step"] = round(ms_unsampled / K, 3)
+        clocks["value_from"] = f"median of {REGIONS} sampled regions of {K} steps"
+        clocks["min_ms_per_step"], clocks["max_ms_per_step"] = round(order[0]["ms"] / K, 3), round(order[-1]["ms"] / K, 3)
+        clocks["hint_retries_per_region"] = [r["hint_retries"] for r in per_region]
+        clocks["cuda_mallocs_per_region"] = [r["cuda_mallocs"] for r in per_region]
     # per-stage CUDA events (on the launching stream, inside the C library) in a second pass of the same steps
     # (views one after another on ONE stream here, so that a stage's events bracket that stage alone)
-    vstreams_timed, vstreams = vstreams, ViewStreams(device, 1)
+    vstreams_timed, rig.vstreams = rig.vstreams, ViewStreams(device, 1)
     N.profile_reset(); N.profile_enable(True)
-    timed(step, K, 0)
+    timed(rig.step, K, 0, device, world)
     prof = N.profile_read(); N.profile_enable(False)
-    vstreams = vstreams_timed
-    ms_fwd = min(timed(lambda: step(True), K, 2 if a == 0 else 0)[0] for a in range(ATTEMPTS))  # fastest of the attempts, like value
+    rig.vstreams = vstreams_timed
+    ms_fwd, fwd_regions, _ = regions(lambda: rig.step(True), K, 3, device, world, warmup=2)
 
     frames = K * vpr * world
     value = frames / (ms_total / 1e3)
@@ -361,141 +563,83 @@ def run_ours(args):
     # ---- e2e: public API, host buffers (pinned GT image + camera) -> loss on the host -------------
     e2e = None
     if not args.no_e2e:
-        params = {k: scene[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
-        gt_host = [torch.rand(3, H, W).pin_memory() for _ in cams]
-        cam_host = [torch.cat([c["host"]["viewmatrix"].reshape(-1), c["host"]["projmatrix"].reshape(-1),
-                               c["host"]["campos"].reshape(-1), torch.zeros(3)]).pin_memory() for c in cams]
-        loss_host = torch.zeros(vpr).pin_memory()
-
-        # .grad of the parameters = their slices of the step's flat gradient buffer: the backward kernel adds
-        # into it (accumulate_gradients_into), the one all-reduce sends it, FusedAdam would read it
-        from gaussian_splatting_lightning_b200.rasterizer import accumulate_gradients_into
-        from gaussian_splatting_lightning_b200.training import l1_loss, parameter_groups_on
-        parameter_groups_on(bufs, params)
-        copy_stream = torch.cuda.Stream(device)
-        n_slots = args.streams + 1
-        slots = [dict(cam=torch.empty(38, device=device), gt=torch.empty(3, H, W, device=device),
-                      ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(n_slots)]
-
-        def upload(j):
-            """this step's host inputs of view j -> device, on the copy stream (a ring of streams+1 slots, the
-            way a prefetching data loader hands batches over); every byte is copied inside the timed region"""
-            sl = slots[j % n_slots]
-            with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(sl["free"])           # the view that used this slot last is done with it
-                sl["cam"].copy_(cam_host[j], non_blocking=True)
-                sl["gt"].copy_(gt_host[j], non_blocking=True)
-                sl["ready"].record(copy_stream)
-
-        from gaussian_splatting_lightning_b200.training import photometric_loss
-        loss_fns = {"l1": l1_loss, "full": lambda c_, g_: photometric_loss(c_[None], g_[None], 0.2)[0]}
-
-        def e2e_view(j):
-            loss_fn = loss_fns[e2e_loss[0]]
-            st = torch.cuda.current_stream()                 # ViewStreams.run: view j on stream j mod n
-            if j + n_slots - 1 < vpr:
-                upload(j + n_slots - 1)                      # its slot was freed by view j-1; overlaps the rendering
-            sl = slots[j % n_slots]
-            st.wait_event(sl["ready"])
-            cam_d, gt = sl["cam"], sl["gt"]
-            rs = cams[j]["settings"]._replace(viewmatrix=cam_d[0:16].view(4, 4), projmatrix=cam_d[16:32].view(4, 4),
-                                              campos=cam_d[32:35], bg=cam_d[35:38])
-            sp = torch.zeros_like(params["means3D"], requires_grad=True)
-            with accumulate_gradients_into(acc_into, stat_into):
-                color, radii, invd = GaussianRasterizer(rs)(
-                    means3D=params["means3D"], means2D=sp, shs=params["shs"], colors_precomp=None,
-                    opacities=params["opacities"], scales=params["scales"], rotations=params["rotations"],
-                    cov3D_precomp=None)
-            loss = loss_fn(color, gt)
-            loss.backward()
-            loss_host[j].copy_(loss.detach(), non_blocking=True)
-            sl["free"].record(st)
-
-        def e2e_step():
-            main = torch.cuda.current_stream()
-            bufs.zero_()
-            for j in range(min(n_slots - 1, vpr)):
-                upload(j)
-            vstreams.run(vpr, e2e_view)
-            if world > 1:
-                bufs.all_reduce()
-            main.synchronize()                               # the step's result (losses) is on the host
-            return float(loss_host.sum())
-
-        e2e_loss = ["l1"]
-        ms_e2e, _, _ = timed(e2e_step, K, 2)
-        e2e_loss[0] = "full"     # the reference's training loss: 0.8 L1 + 0.2 (1 - SSIM), one fused kernel
-        ms_e2e_full, _, _ = timed(e2e_step, K, 2)
-        e2e_loss[0] = "l1"
-        h2d = vpr * (3 * H * W * 4 + 38 * 4)
-        e2e = {"value": frames / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": vpr * 4,
-               "what": "GaussianRasterizer autograd API + fused L1 loss (training.l1_loss) with fused gradient accumulation "
-                       "(accumulate_gradients_into) on the same CUDA streams as `value`; per view: pinned GT image and "
-                       "camera H2D (copy stream, ring of streams+1 slots, inside the timed region), loss D2H",
+        E = E2E(rig)
+        ms_e2e, e2e_regions, _ = regions(E.step, K, 3, device, world, warmup=2)
+        E.loss_kind = "full"     # the reference's training loss: 0.8 L1 + 0.2 (1 - SSIM), one fused kernel
+        ms_e2e_full, _, _ = regions(E.step, K, 3, device, world, warmup=2)
+        E.loss_kind = "l1"
+        e2e = {"value": frames / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": E.h2d_bytes_per_step,
+               "d2h_bytes_per_step": E.d2h_bytes_per_step, "regions_ms_per_step": [round(m / K, 3) for m in e2e_regions],
+               "what": "GaussianRasterizer autograd API (through the `_C` torch extension) + fused L1 loss (training.l1_loss) "
+                       "with fused gradient accumulation (accumulate_gradients_into) on the same CUDA streams as `value`; "
+                       "per view: pinned GT image and camera H2D (copy stream, ring of streams+1 slots, inside the timed "
+                       "region), loss D2H.  Parameters are leaf tensors; the activations and optimizer.step of the "
+                       "reference's training_step are outside this region (Adam is timed in `neighbours`)",
                "with_reference_training_loss": {"value": frames / (ms_e2e_full / 1e3), "unit": UNIT, "what": "same, with "
                    "the loss of GSLightningModule.calculate_loss: 0.8 L1 + 0.2 (1 - fused_ssim) (training.photometric_loss)"}}
-        # ---- the training-step neighbours of the path (SURVEY 8(f) rows 1-2), each one launch, HBM bound --------
-        from gaussian_splatting_lightning_b200.training import FusedAdam, densify_fold
+        e2e["neighbours"] = neighbours(rig, E)
+        del E
 
-        def ev_ms(fn, reps=20):
-            for _ in range(3):
-                fn()
-            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            torch.cuda.synchronize(); a_.record()
-            for _ in range(reps):
-                fn()
-            b_.record(); torch.cuda.synchronize()
-            return a_.elapsed_time(b_) / reps
+    # ---- per-stage roofline (rank 0 computes; the other ranks only take part in the extras) --------
+    line = None
+    if rank == 0:
+        line = headline(args, rig, counters, prof, clocks, value, fwd_value, ms_total, ms_fwd, e2e, launches, K, Wm, world)
+    cpu_scene, cam0 = rig.scene_cpu, rig.cams[0]["host"]
+    rig.free()
 
-        hbm_pk = peaks()[0]
-        opt = FusedAdam([{"params": [params[k]], "lr": lr} for k, lr in
-                         (("means3D", 1.6e-4), ("shs", 2.5e-3), ("opacities", 5e-2), ("scales", 5e-3), ("rotations", 1e-3))],
-                        lr=0.0, eps=1e-15)
-        n_par = sum(p_.numel() for p_ in params.values())
-        img_a, img_b = torch.rand(3, H, W, device=device, requires_grad=True), torch.rand(3, H, W, device=device)
-        run_stats = [torch.zeros(P, device=device) for _ in range(3)]
-        neighbours = []
-        for name, fn, nbytes in (
-                ("adam (6 groups, one launch, zero_grad fused)", lambda: opt.step(zero_grad=True), 32 * n_par),
-                ("l1_loss value + unit gradient", lambda: l1_loss(img_a, img_b), 12 * 3 * H * W),
-                ("densify_fold", lambda: densify_fold(bufs.max_radii, bufs.stats[0], bufs.stats[1], *run_stats), 32 * P)):
-            ms_ = ev_ms(fn)
-            neighbours.append({"kernel": name, "ms": ms_, "algorithmic_bytes": nbytes, "GBps": nbytes / (ms_ * 1e6),
-                               "hbm_frac": nbytes / (ms_ * 1e6) / hbm_pk})
-        # fused SSIM (value + gradient, one launch) next to the reference's own CUDA kernels (oracle/_ref, compiled from
-        # /root/reference/submodules/fused-ssim by oracle/build_ref.py) on the same image pair: fusedssim + fusedssim_backward
-        from gaussian_splatting_lightning_b200.training import fused_ssim
-        im_a, im_b = img_a.detach()[None].clone().requires_grad_(True), img_b[None]
-        ms_ = ev_ms(lambda: fused_ssim(im_a, im_b))
-        ent = {"kernel": "fused_ssim value + gradient (one launch)", "ms": ms_, "algorithmic_bytes": 12 * 3 * H * W,
-               "GBps": 12 * 3 * H * W / (ms_ * 1e6), "hbm_frac": 12 * 3 * H * W / (ms_ * 1e6) / hbm_pk}
-        try:
-            from oracle import build_ref
-            if build_ref.available():
-                ref_mod = build_ref.load()
-                dmap = torch.full_like(im_b, 1.0 / im_b.numel())
+    # ---- the other configurations and usages north_star / BASELINE.json name, carried in the same line ----------
+    if not args.no_extras:
+        extras = {}
+        S = max(2, min(K, 3))
+        # the reference trains ONE view per step (gs_lightning_module.py:139-140): single-view latency, one stream
+        extras["single_view_per_step"] = extra_block(args.workload, 1, 1, "block", 8 * S, device, rank, world, with_e2e=True)
+        # BASELINE.json configs[0]: the reference Python rasterizer's CPU-runnable case, on the GPU path
+        extras["c1"] = extra_block("C1", 1, 1, "block", 50, device, rank, world)
+        # configs[3]: 3M Gaussians, 64 cameras per step at 1600x1200 split over the ranks (STRONG scaling, the
+        # library's own interleaved view assignment), NCCL all-reduce of the step buffer
+        if 64 % world == 0:
+            extras["c4_strong"] = dict(extra_block("C4", 64 // world, args.streams, "interleaved", S, device, rank, world),
+                                       scaling="strong", frames_per_step=64)
+        # configs[4]: 6M Gaussians, 3840x2160, 8 views per GPU, render only (replicas, no collective)
+        extras["c5_render_only"] = extra_block("C5", 8, args.streams, "block", S, device, rank, world, fwd_only=True)
+        if line is not None:
+            line["extras"] = extras
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_oracle_frames_per_s(args.workload, cpu_scene, cam0, 6)   # ~11 s of CPU work
+        line["reference_python_rasterizer_c1"] = reference_python_c1()
+        emit(line)
+    if world > 1:
+        dist.destroy_process_group()
 
-                def ref_ssim():
-                    _m, d1, d2, d3 = ref_mod.fusedssim(0.01 ** 2, 0.03 ** 2, im_a.detach(), im_b, True)
-                    ref_mod.fusedssim_backward(0.01 ** 2, 0.03 ** 2, im_a.detach(), im_b, dmap, d1, d2, d3)
-                ent["reference_cuda_ms"] = ev_ms(ref_ssim)
-                ent["reference"] = "submodules/fused-ssim fusedssim + fusedssim_backward (oracle/_ref), same GPU"
-        except Exception as ex:  # the checker is optional on the box
-            ent["reference"] = f"unavailable: {ex}"
-        neighbours.append(ent)
-        e2e["neighbours"] = neighbours
-        del params, opt
 
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+def ffi_name():
+    from gaussian_splatting_lightning_b200 import _native
+    return "torch C++ extension _C" if _native.ext() is not None else "ctypes"
 
-    # ---- per-stage roofline ------------------------------------------------------------------------
+
+def reference_python_c1():
+    """north_star's reported baseline: the reference's own gs_lightning Python rasterizer on BASELINE.json configs[0]
+    (C1).  /root/reference does not travel to the GPU box, so the number is the one measured in the build container by
+    tools/time_reference_python.py (committed with its output, profiles/reference_python_c1.json)."""
+    p = os.path.join(ROOT, "profiles", "reference_python_c1.json")
+    if os.path.exists(p):
+        return json.load(open(p))
+    return None
+
+
+def headline(args, rig, counters, prof, clocks, value, fwd_value, ms_total, ms_fwd, e2e, launches, K, Wm, world):
+    """The JSON line of rank 0: per-stage roofline from the CUDA-event stage times and the workload counters."""
+    P, deg, W, H, M, vpr = rig.P, rig.deg, rig.W, rig.H, rig.M, rig.vpr
     hbm_peak, peak_src, sm_max = peaks()
     T = ((W + 15) // 16) * ((H + 15) // 16)
     passes = (32 + max(1, (T - 1).bit_length()) + 7) // 8
     model = stage_model(P, M, counters["Pvis"], counters["R"], counters["L"], counters["A"], H * W, T, passes)
+    ncu = json.load(open(NCU_COUNTS)) if os.path.exists(NCU_COUNTS) else {"kernels": {}}
+    sm_mhz = (clocks or {}).get("sm_mhz") or sm_max
+    issue_peak = 148 * 4 * sm_mhz * 1e6            # warp instructions per second: 4 schedulers per SM, one issue per clock
+    v0 = counters["view0"]
+    visit_scale = ((counters["visits_both"] + counters["visits_single"]) / max(1.0, v0["visits_both"] + v0["visits_single"]))
     stages, stage_sum = [], 0.0
     for name, (tot_ms, calls) in prof.items():
         if calls == 0:
@@ -503,54 +647,80 @@ def run_ours(args):
         avg_ms = tot_ms / calls
         stage_sum += tot_ms
         m = model[name]
-        s = {"stage": name, "ms_per_frame": avg_ms, "calls": calls, "algorithmic_bytes": m["bytes"],
-             "GBps": m["bytes"] / (avg_ms * 1e6), "hbm_frac": m["bytes"] / (avg_ms * 1e6) / hbm_peak}
-        if "flops" in m:
-            s["TFLOPs_fp32"] = m["flops"] / (avg_ms * 1e9)
-            s["Gex2_per_s"] = m["ex2"] / (avg_ms * 1e6)
+        s = {"stage": name, "bound": STAGE_BOUND.get(name, "hbm"), "ms_per_frame": avg_ms, "calls": calls,
+             "algorithmic_bytes": m["bytes"], "GBps": m["bytes"] / (avg_ms * 1e6),
+             "hbm_frac": m["bytes"] / (avg_ms * 1e6) / hbm_peak}
+        k = ncu["kernels"].get(name)
+        if k:
+            # ncu counters of ONE launch on view 0 (profiles/): DRAM traffic against the algorithmic bytes, and -- for
+            # the issue-bound kernels -- warp instructions per launch, scaled from view 0 to the mean view of the step
+            # by the number of (warp, entry) visits counted from the hit words
+            s["dram_traffic_bytes_view0"] = k.get("dram_bytes")
+            if k.get("dram_bytes") and k.get("algorithmic_bytes_view0"):
+                s["traffic_over_algorithmic"] = k["dram_bytes"] / k["algorithmic_bytes_view0"]
+            if k.get("inst") and s["bound"] == "fp32_issue":
+                inst = k["inst"] * visit_scale
+                s["warp_inst_per_launch"] = inst
+                s["Gwarp_inst_per_s"] = inst / (avg_ms * 1e6)
+                s["issue_frac"] = inst / (avg_ms * 1e-3) / issue_peak
+                s["ncu_issue_active_pct"] = k.get("issue_active_pct")
+                s["ncu_fma_pipe_cycles_pct"] = k.get("fma_pipe_cycles_pct")
+        if name == "render_backward":
+            # FP32 work actually done: 75 flop (SURVEY 8(d) convention) per (pixel, splat) pair the kernel EVALUATES
+            # (hit words), not per pair of A = sum(n_contrib), which also counts what the culling skipped
+            s["pairs_evaluated"] = counters["pairs_evaluated"]
+            s["pairs_A_convention"] = counters["A"]
+            s["TFLOPs_fp32_evaluated"] = 75 * counters["pairs_evaluated"] / (avg_ms * 1e9)
         stages.append(s)
     for s in stages:
         s["share_of_kernel_time"] = s["ms_per_frame"] * s["calls"] / stage_sum
     dom = max(stages, key=lambda s: s["ms_per_frame"] * s["calls"])
-    traffic, traffic_src = None, None
-    tp = os.path.join(ROOT, "profiles", "r1_v7_traffic.json")      # dram bytes per launch from the ncu --set full capture
-    if os.path.exists(tp):
-        tj = json.load(open(tp))
-        ent = tj.get(dom["stage"] + "_kernel") or tj.get({"sort": "onesweep_pass_kernel"}.get(dom["stage"], ""))
-        if ent:
-            traffic, traffic_src = ent["dram_bytes_per_launch"], "profiles/r1_v7_traffic.json: " + tj.get("_source", "")
-    roofline = {"kernel": dom["stage"], "bound": "hbm", "achieved": dom["GBps"], "peak": hbm_peak, "unit": "GB/s",
-                "frac": dom["hbm_frac"], "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": dom["algorithmic_bytes"], "ms_per_launch": dom["ms_per_frame"],
-                "note": "the compositing kernels are FP32-issue bound, not HBM bound: see stages[].TFLOPs_fp32"}
-    fp32_peak = 148 * 128 * 2 * (clocks["sm_mhz"] or sm_max) * 1e6 / 1e12 if clocks else None
-    if "TFLOPs_fp32" in dom and fp32_peak:
-        roofline["fp32"] = {"achieved_TFLOPs": dom["TFLOPs_fp32"], "peak_TFLOPs_at_observed_clock": fp32_peak,
-                            "frac": dom["TFLOPs_fp32"] / fp32_peak}
-
-    cpu_baseline = None
-    if world == 1 and not args.no_cpu_baseline:
-        cpu_baseline = cpu_oracle_frames_per_s(args.workload, scene_cpu, cams[0]["host"], 6)   # ~11 s of CPU work
-
-    line = {
+    fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
+    if dom["bound"] == "fp32_issue" and "issue_frac" in dom:
+        roofline = {"kernel": dom["stage"], "bound": "fp32_issue", "achieved": dom["Gwarp_inst_per_s"],
+                    "peak": issue_peak / 1e9, "unit": "Gwarp-inst/s", "frac": dom["issue_frac"],
+                    "traffic": dom.get("dram_traffic_bytes_view0"),
+                    "peak_source": f"148 SMs x 4 schedulers x {sm_mhz:.0f} MHz (observed SM clock)",
+                    "inst_source": ncu.get("_source"), "ms_per_launch": dom["ms_per_frame"],
+                    "warp_inst_per_launch": dom["warp_inst_per_launch"],
+                    "hbm": {"achieved_GBps": dom["GBps"], "peak_GBps": hbm_peak, "frac": dom["hbm_frac"],
+                            "algorithmic_bytes_per_launch": dom["algorithmic_bytes"], "peak_source": peak_src},
+                    "note": "the dominant kernel is bound by FP32 instruction issue (SURVEY.md 8(d)), so `frac` is its "
+                            "issue-slot utilisation: warp instructions per launch (ncu smsp__inst_executed.sum of the "
+                            "committed capture, scaled by visits) / CUDA-event duration / issue peak; its HBM fraction "
+                            "is kept under `hbm`; the HBM-bound stages carry hbm_frac in stages[]"}
+        if "TFLOPs_fp32_evaluated" in dom:
+            roofline["fp32"] = {"achieved_TFLOPs": dom["TFLOPs_fp32_evaluated"], "peak_TFLOPs_at_observed_clock": fp32_peak,
+                                "frac": dom["TFLOPs_fp32_evaluated"] / fp32_peak,
+                                "note": "75 flop x pairs EVALUATED (hit words); the A-based figure of round 1 read 1.135"}
+    else:
+        roofline = {"kernel": dom["stage"], "bound": "hbm", "achieved": dom["GBps"], "peak": hbm_peak, "unit": "GB/s",
+                    "frac": dom["hbm_frac"], "traffic": dom.get("dram_traffic_bytes_view0"), "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": dom["algorithmic_bytes"], "ms_per_launch": dom["ms_per_frame"]}
+    hbm_stages = [s for s in stages if s["bound"] == "hbm" and s["stage"] in ("preprocess", "preprocess_backward")]
+    if hbm_stages:
+        top = max(hbm_stages, key=lambda s: s["ms_per_frame"])
+        roofline["hbm_bound_kernel"] = {"kernel": top["stage"], "achieved_GBps": top["GBps"], "peak_GBps": hbm_peak,
+                                        "frac": top["hbm_frac"], "traffic_over_algorithmic": top.get("traffic_over_algorithmic")}
+    return {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
         "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {P} Gaussians, SH degree {deg}, {W}x{H}, fwd+bwd + densification "
                                f"stats, {vpr} views per GPU per step" + (", NCCL all-reduce of 59 floats/Gaussian + stats" if world > 1 else ""),
-                   "views_per_rank": vpr, "frames_per_step": vpr * world, "streams_per_rank": args.streams, "parallelism": f"view-parallel x{world}", "partition": args.partition,
+                   "views_per_rank": vpr, "frames_per_step": vpr * world, "streams_per_rank": args.streams,
+                   "parallelism": f"view-parallel x{world}", "partition": args.partition,
+                   "ffi": ffi_name(),
                    "l2": (lambda mb: f"inputs ({mb:.0f} MB of Gaussian parameters + {48 * P / 1e6:.0f} MB records) "
                           + ("exceed the 126 MB L2; no flush" if mb > 126 else
                              "fit the 126 MB L2: a parity-test size, not a bench line"))((44 + 12 * M) * P / 1e6),
                    "num_rendered_mean": counters["R"], "visible_mean": counters["Pvis"],
-                   "pairs_A_mean": counters["A"], "list_entries_L_mean": counters["L"]},
+                   "pairs_A_mean": counters["A"], "list_entries_L_mean": counters["L"],
+                   "pairs_evaluated_mean": counters["pairs_evaluated"], "view0": counters["view0"]},
         "forward_only": {"value": fwd_value, "unit": UNIT, "ms_per_step": ms_fwd / K},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "stages": stages,
-        "cpu_baseline": cpu_baseline,
+        "cpu_baseline": None,
     }
-    emit(line)
-    if world > 1:
-        dist.destroy_process_group()
 
 
 def cpu_oracle_frames_per_s(workload, scene_cpu, cam_host, repeats):

@@ -142,6 +142,37 @@ def lib():
     return L
 
 
+EXT_PATH = os.path.join(_HERE, "_C.so")
+_ext = None
+_ext_tried = False
+
+
+def ext():
+    """`_C`, the thin torch C++ extension over the C-ABI (csrc/torch_ext.cpp) -- the FFI layer of the rasterizer calls.
+    GSR_FFI=ctypes selects the ctypes binding of the same C-ABI instead (kept as the second binding; the tests run the
+    parity cases through both).  Returns None when ctypes is selected or `_C.so` has not been built."""
+    global _ext, _ext_tried
+    if os.environ.get("GSR_FFI", "") == "ctypes":
+        return None
+    if _ext_tried:
+        return _ext
+    _ext_tried = True
+    lib()   # fail loudly first if the CUDA library itself is missing
+    if os.path.exists(EXT_PATH):
+        import importlib.util
+        spec = importlib.util.spec_from_file_location(__package__ + "._C", EXT_PATH)
+        m = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(m)
+        import sys
+        sys.modules[__package__ + "._C"] = m
+        _ext = m
+    else:
+        import warnings
+        warnings.warn(f"{EXT_PATH} has not been built (python -m gaussian_splatting_lightning_b200.build); "
+                      "using the ctypes binding of libgsr_b200.so")
+    return _ext
+
+
 def profile_enable(on: bool) -> None:
     lib().gsr_profile_enable(int(on))
 

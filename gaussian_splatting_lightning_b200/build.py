@@ -86,6 +86,36 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+EXT = os.path.join(HERE, "_C.so")
+
+
+def build_torch_ext(force: bool = False) -> str:
+    """`_C`: the thin torch C++ extension over the C-ABI (csrc/torch_ext.cpp), compiled with g++ against the torch
+    headers of this interpreter and linked to libgsr_b200.so next to it (rpath $ORIGIN).  In-tree, like the library."""
+    import sysconfig
+
+    import torch
+    from torch.utils import cpp_extension as ce
+    src = os.path.join(CSRC, "torch_ext.cpp")
+    deps = [src, os.path.join(CSRC, "..", "..", "include", "gsr_b200.h"), LIB, os.path.abspath(__file__)]
+    if not force and not _stale(EXT, deps):
+        return EXT
+    tlib = ce.library_paths()[0]
+    cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
+    cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden", src, "-o", EXT,
+           "-DTORCH_EXTENSION_NAME=_C", "-DTORCH_API_INCLUDE_EXTENSION_H",
+           f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
+           *[f"-I{i}" for i in ce.include_paths()], f"-I{sysconfig.get_paths()['include']}", f"-I{cuda_inc}",
+           f"-L{tlib}", "-ltorch", "-ltorch_cpu", "-ltorch_cuda", "-ltorch_python", "-lc10", "-lc10_cuda",
+           f"-L{HERE}", "-lgsr_b200", "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{tlib}",
+           f"-L{os.path.join(os.path.dirname(cuda_inc), 'lib64')}", "-lcudart"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"g++ failed on torch_ext.cpp:\n{' '.join(cmd)}\n{r.stdout}\n{r.stderr}")
+    return EXT
+
+
 if __name__ == "__main__":
     p = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
     print(p)
+    print(build_torch_ext(force="--force" in sys.argv))

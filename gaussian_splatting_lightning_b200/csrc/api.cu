@@ -156,6 +156,10 @@ int make_gaussians(const GsrGaussians* g, int deg, GsrGaussiansDev* d) {
 }
 
 __global__ void set_u32_kernel(unsigned int* p, unsigned int v) { *p = v; }
+__global__ void iota_u32_kernel(unsigned int* p, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = (unsigned int)i;
+}
 
 }  // namespace
 
@@ -216,10 +220,14 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
             "preprocess kernel", debug, stream);
   if (segmented)
     GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(P > 0 ? v.gx : 0, v.gy, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
-                                             img.tile_scan_state, img.ctrl, stream),
+                                             img.tile_scan_state, img.ctrl, img.tile_order, stream),
               "tile scan kernel", debug, stream);
   else
     GSR_STAGE(ST_SCAN, gsr::launch_scan(P, geom, img.ctrl, stream), "scan kernel", debug, stream);
+  if (!segmented || P == 0) {  // the tile scan writes the compositing kernels' tile order; without it: raster order
+    iota_u32_kernel<<<(num_tiles + 255) / 256, 256, 0, stream>>>(img.tile_order, num_tiles);
+    gsr::count_launch();
+  }
 
   Mailbox* mail = nullptr;
   rc = get_mailbox(&mail);
@@ -245,7 +253,7 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
         GSR_CUDA(cudaMemsetAsync(img.tile_scan_state, 0, img.tile_scan_state_bytes, stream), "memset(tile scan state)");
         GSR_CUDA(cudaMemsetAsync(img.ctrl, 0, sizeof(GsrControl), stream), "memset(control)");
         GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(v.gx, v.gy, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
-                                                 img.tile_scan_state, img.ctrl, stream),
+                                                 img.tile_scan_state, img.ctrl, img.tile_order, stream),
                   "tile scan kernel", debug, stream);
       }
       GSR_STAGE(ST_DUPLICATE, gsr::launch_tile_scatter(v, P, radii, geom, img.tile_cursor, bin.keys_a,
@@ -269,8 +277,8 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
       GSR_STAGE(ST_RANGES, gsr::launch_tile_ranges(bin.keys_a, &img.ctrl->num_rendered, (uint32_t)cap, img.ranges, stream),
                 "tile ranges kernel", debug, stream);
     }
-    GSR_STAGE(ST_RENDER_FWD, gsr::launch_render_forward(v, img.ranges, bin.vals_a, geom.recs, out_color, out_invdepth, img.final_T,
-                                         img.n_contrib, bin.hits, stream),
+    GSR_STAGE(ST_RENDER_FWD, gsr::launch_render_forward(v, img.ranges, img.tile_order, bin.vals_a, geom.recs, out_color,
+                                                        out_invdepth, img.final_T, img.n_contrib, bin.hits, stream),
               "render forward kernel", debug, stream);
     if (R < 0) {
       GSR_CUDA(cudaEventSynchronize(mail->ev), "read num_rendered");
@@ -322,7 +330,7 @@ int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, con
 
   GSR_CUDA(cudaMemsetAsync(grad_acc, 0, (size_t)P * 12 * sizeof(float), stream), "memset(grad accumulators)");
   if (num_rendered > 0)
-    GSR_STAGE(ST_RENDER_BWD, gsr::launch_render_backward(v, img.ranges, binning_, geom.recs, img.final_T, img.n_contrib, dL_dcolor,
+    GSR_STAGE(ST_RENDER_BWD, gsr::launch_render_backward(v, img.ranges, img.tile_order, binning_, geom.recs, img.final_T, img.n_contrib, dL_dcolor,
                                           dL_dinvdepth, grad_acc, stream),
               "render backward kernel", debug, stream);
   GSR_STAGE(ST_PREPROCESS_BWD, gsr::launch_preprocess_backward(v, g, radii, geom, grad_acc, out, stream),

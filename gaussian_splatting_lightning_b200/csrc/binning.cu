@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, int gx, int gy, c
     if (r <= 0) continue;
     uint32_t off = (i == 0) ? 0u : offsets[i - 1];
     const float4 a = recs[i].a;
-    const float depth = recs[i].c.w;
+    const float depth = recs[i].d.w;
     int x0, y0, x1, y1;
     tile_rect(a.x, a.y, (float)r, gx, gy, x0, y0, x1, y1);
     const uint32_t dbits32 = __float_as_uint(depth);

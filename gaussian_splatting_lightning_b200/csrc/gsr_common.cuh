@@ -3,7 +3,7 @@
 // HBM layout of the three scratch buffers (opaque uint8 tensors to the caller; the
 // forward writes them, the backward only reads them):
 //
-//   geom (per Gaussian, P)     GsrRec recs[P]           48 B  packed record the tile kernels gather
+//   geom (per Gaussian, P)     GsrRec recs[P]           64 B  packed record the tile kernels gather
 //                              float  cov3D[6P]         24 B  kept for the backward
 //                              u8     clamped[P]         1 B  bit c set: SH colour channel c was clamped at 0
 //                              u32    tiles_touched[P]   4 B
@@ -25,13 +25,18 @@
 #define GSR_TILE_PIX 256
 #define GSR_NEAR 0.2f
 
-// One packed per-Gaussian record (AoS, 48 B, 16-byte aligned): everything the forward and
-// backward compositing kernels need, fetched with three 128-bit loads.
-struct __align__(16) GsrRec {
-  float4 a;  // {mean2D.x, mean2D.y, conic.A, conic.B}
-  float4 b;  // {conic.C, opacity (AA-scaled), r, g}
-  float4 c;  // {b, 1/z_view, tau = ln(255*opacity), z_view}
+// One packed per-Gaussian record (AoS, 64 B = two 32-byte sectors, 64-byte aligned): everything the forward and
+// backward compositing kernels need, ALREADY in the form they keep in shared memory, so that staging a batch is a pure
+// copy (four 16-byte cp.async per entry, issued a whole batch ahead of its use) with no arithmetic.  The quadratic form
+// is pre-scaled into the log2 domain (render_common.cuh):
+//   hA = conic.A * log2(e)/2, hB = conic.B * log2(e), hC = conic.C * log2(e)/2, tau2 = ln(255 * opacity) * log2(e)
+struct __align__(64) GsrRec {
+  float4 a;  // {mean2D.x, mean2D.y, hA, hB}
+  float4 b;  // {hC, -opacity (AA-scaled), r, g}
+  float4 c;  // {b, 1/z_view, tau2, bits(Gaussian index)}
+  float4 d;  // {kx, ky, tauM, z_view}: the cull plane of the forward (make_cull_plane) + the depth the sort keys use
 };
+static_assert(sizeof(GsrRec) == 64, "GsrRec is two sectors");
 
 // Per-frame device-side control block (zeroed by one memset at the start of a frame).
 struct GsrControl {
@@ -100,6 +105,7 @@ struct ImgState {
   uint32_t* tile_count;   // instances per tile, counted by the preprocess kernel (tile_binning.cu)
   uint32_t* tile_cursor;  // the scatter's per-tile cursors (same layout), set to the segment starts by the tile scan
   uint32_t* large_tiles;  // lists of the tiles the MID (from the front) and LARGE (from the back) sort launches take
+  uint32_t* tile_order;   // the tiles by descending list length: blockIdx -> tile of the compositing kernels
   unsigned long long* tile_scan_state;  // status words of the chained tile scan, one per 1024 tiles
   size_t tile_scan_state_bytes;
   GsrControl* ctrl;
@@ -117,6 +123,7 @@ struct ImgState {
     s.tile_count = (uint32_t*)take(T * 4 * GSR_TILE_COUNT_STRIDE);
     s.tile_cursor = (uint32_t*)take(T * 4 * GSR_TILE_COUNT_STRIDE);
     s.large_tiles = (uint32_t*)take(T * 4);
+    s.tile_order = (uint32_t*)take(T * 4);
     s.tile_scan_state_bytes = ((T + 1023) / 1024 + 1) * 8;
     s.tile_scan_state = (unsigned long long*)take(s.tile_scan_state_bytes);
     s.ctrl = (GsrControl*)take(sizeof(GsrControl));
@@ -238,8 +245,11 @@ cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, 
 cudaError_t launch_preprocess(const GsrView& v, const GsrGaussiansDev& g, int32_t* radii, const GeomState& geom,
                               uint32_t* tile_count, cudaStream_t s);
 // tile-segmented binning (tile_binning.cu)
+// order (may be NULL): receives the tiles by (approximately) descending list length, blockIdx -> tile of the
+// compositing kernels
 cudaError_t launch_tile_scan(int gx, int gy, const uint32_t* tile_count, uint2* ranges, uint32_t* tile_cursor,
-                             uint32_t* large_tiles, unsigned long long* state, GsrControl* ctrl, cudaStream_t s);
+                             uint32_t* large_tiles, unsigned long long* state, GsrControl* ctrl, uint32_t* order,
+                             cudaStream_t s);
 cudaError_t launch_tile_scatter(const GsrView& v, int P, const int32_t* radii, const GeomState& geom, uint32_t* cursor,
                                 unsigned long long* comp, uint32_t capacity, GsrControl* ctrl, BinningHeader* header,
                                 cudaStream_t s);
@@ -259,13 +269,14 @@ cudaError_t launch_onesweep(unsigned long long* keys_a, uint32_t* vals_a, unsign
                             const gsr_sort::Workspace& ws, bool hist_ready, cudaStream_t s);
 cudaError_t launch_tile_ranges(const unsigned long long* keys_sorted, const unsigned int* d_n, uint32_t capacity,
                                uint2* ranges, cudaStream_t s);
-cudaError_t launch_render_forward(const GsrView& v, const uint2* ranges, const uint32_t* point_list,
-                                  const GsrRec* recs, float* out_color, float* out_invdepth, float* final_T,
-                                  uint32_t* n_contrib, uint32_t* hits, cudaStream_t s);
+// tile_order (may be NULL = raster order): blockIdx -> tile
+cudaError_t launch_render_forward(const GsrView& v, const uint2* ranges, const uint32_t* tile_order,
+                                  const uint32_t* point_list, const GsrRec* recs, float* out_color, float* out_invdepth,
+                                  float* final_T, uint32_t* n_contrib, uint32_t* hits, cudaStream_t s);
 // binning: the forward's binning buffer (header + sorted point list + hit words).
 // grad_acc: (P,12) floats, ten raw pixel sums per Gaussian (render_backward.cu) + 2 pad.
-cudaError_t launch_render_backward(const GsrView& v, const uint2* ranges, const void* binning, const GsrRec* recs,
-                                   const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
+cudaError_t launch_render_backward(const GsrView& v, const uint2* ranges, const uint32_t* tile_order, const void* binning,
+                                   const GsrRec* recs, const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
                                    const float* dL_dinvdepth, float* grad_acc, cudaStream_t s);
 struct PreBwdOut {
   float* dL_dmeans2D; float* dL_dcolors; float* dL_dopacity; float* dL_dmeans3D; float* dL_dcov3D; float* dL_dsh;

@@ -9,9 +9,10 @@
 //     UBLKCP) into shared memory behind an mbarrier while all threads do projection, EWA
 //     covariance and culling in registers; SH evaluation then reads the thread's row with
 //     128-bit shared loads.  This replaces upstream's 48 stride-192-B scalar loads per thread.
-//   * outputs: radii, tiles_touched, a packed 48-byte record per Gaussian (GsrRec), cov3D,
+//   * outputs: radii, tiles_touched, a packed 64-byte record per Gaussian (GsrRec), cov3D,
 //     clamp bits.
 #include "gsr_math.cuh"
+#include "render_common.cuh"
 
 namespace gsr {
 
@@ -209,12 +210,18 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreArgs a) {
     a.radii[i] = alive ? (int32_t)radius : 0;
     a.tiles_touched[i] = alive ? (uint32_t)area : 0u;
     if (alive) {
+      // the record is written in the form the compositing kernels stage (gsr_common.cuh): log2-domain quadratic
+      // form, negated opacity, the Gaussian's own index, the forward's cull plane
       GsrRec r;
-      r.a = make_float4(pixx, pixy, cA, cB);
-      r.b = make_float4(cC, opac, rgb[0], rgb[1]);
+      const float hA = cA * GSR_HALF_LOG2E, hB = cB * GSR_LOG2E, hC = cC * GSR_HALF_LOG2E;
       // tau: a pixel can only receive alpha >= 1/255 from this splat where power >= -tau.
       const float tau = opac > 0.f ? logf(255.f * opac) : -1.f;
-      r.c = make_float4(rgb[2], 1.f / zview, tau, zview);
+      const float tau2 = tau * GSR_LOG2E;
+      r.a = make_float4(pixx, pixy, hA, hB);
+      r.b = make_float4(hC, -opac, rgb[0], rgb[1]);
+      r.c = make_float4(rgb[2], 1.f / zview, tau2, __uint_as_float((uint32_t)i));
+      r.d = make_cull_plane(hA, hB, hC, tau2);
+      r.d.w = zview;
       a.recs[i] = r;
 #pragma unroll
       for (int k = 0; k < 6; ++k) a.cov3D[6 * (size_t)i + k] = s6[k];
@@ -251,13 +258,13 @@ __global__ void __launch_bounds__(256) export_geom_kernel(int P, const int32_t* 
   if (i >= P) return;
   const bool vis = radii[i] > 0;
   GsrRec r;
-  r.a = r.b = r.c = make_float4(0.f, 0.f, 0.f, 0.f);
+  r.a = r.b = r.c = r.d = make_float4(0.f, 0.f, 0.f, 0.f);
   if (vis) r = g.recs[i];
-  if (depths) depths[i] = r.c.w;
+  if (depths) depths[i] = r.d.w;
   if (means2D) { means2D[2 * i] = r.a.x; means2D[2 * i + 1] = r.a.y; }
-  if (conic_opacity) {
-    conic_opacity[4 * i] = r.a.z; conic_opacity[4 * i + 1] = r.a.w;
-    conic_opacity[4 * i + 2] = r.b.x; conic_opacity[4 * i + 3] = r.b.y;
+  if (conic_opacity) {  // back from the log2 domain (two roundings: the parity tests compare these at 1e-6 relative)
+    conic_opacity[4 * i] = r.a.z / GSR_HALF_LOG2E; conic_opacity[4 * i + 1] = r.a.w / GSR_LOG2E;
+    conic_opacity[4 * i + 2] = r.b.x / GSR_HALF_LOG2E; conic_opacity[4 * i + 3] = vis ? -r.b.y : 0.f;
   }
   if (rgb) { rgb[3 * i] = r.b.z; rgb[3 * i + 1] = r.b.w; rgb[3 * i + 2] = r.c.x; }
   if (cov3D)

@@ -37,16 +37,13 @@
 
 namespace gsr {
 
-namespace {
-
-}  // namespace
-
-__global__ void __launch_bounds__(128, 8) render_backward_kernel(
-    const GsrView v, const uint2* __restrict__ ranges, const char* __restrict__ binning,
+__global__ void __launch_bounds__(128, 7) render_backward_kernel(
+    const GsrView v, const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+    const char* __restrict__ binning,
     const GsrRec* __restrict__ recs, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
     const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth, float* __restrict__ grad_acc) {
-  __shared__ float4 sRec[GSR_REC_PLANES][256];  // staged batch, planes as described in render_common.cuh
-  __shared__ uint32_t sHit[8][8];               // [chunk of the batch][sub-tile column]
+  __shared__ float4 sRec[2][3][GSR_BATCH];      // two staged batches, planes 0-2 of render_common.cuh
+  __shared__ uint32_t sHit[2][GSR_BATCH / 32][8];   // [buffer][chunk of the batch][sub-tile column]
   __shared__ uint32_t s_warp_max[4];
   // reduction over the warp's lanes by transposition through shared memory: RED_STRIDE = 36 floats per row keeps the
   // rows 16-byte aligned and the 128-bit row reads of a quarter warp on 32 distinct banks
@@ -55,7 +52,7 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
   __shared__ uint32_t sRedId[4][4];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tile = blockIdx.x;
+  const int tile = tile_order ? (int)tile_order[blockIdx.x] : (int)blockIdx.x;
   const int tx = tile % v.gx, ty = tile / v.gx;
   const int sx0 = tx * GSR_TILE + (warp & 1) * 8, sy0 = ty * GSR_TILE + (warp >> 1) * 8;
   const int pxi = sx0 + (lane & 7), pyA = sy0 + (lane >> 3), pyB = pyA + 4;
@@ -63,10 +60,15 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
   const float pxf = (float)pxi;
   const int colA = (warp >> 1) * 4 + (warp & 1), colB = colA + 2;
   const uint2 range = ranges[tile];
-  float* red = sRed[warp];
-  const uint32_t red_addr = (uint32_t)__cvta_generic_to_shared(red) + (uint32_t)lane * 4u;
-  uint32_t* red_id = sRedId[warp];
+  // shared-memory addresses the hit loop uses, pinned in registers (keep_u32)
+  const uint32_t aRed = (uint32_t)__cvta_generic_to_shared(sRed[warp]);
+  const uint32_t aPark0 = keep_u32(aRed + (uint32_t)lane * 4u);                       // column of this lane, slot 0
+  const uint32_t aRow = keep_u32(aRed + (uint32_t)lane * (RED_STRIDE * 4u));           // row this lane adds at a flush
+  const uint32_t aId = keep_u32((uint32_t)__cvta_generic_to_shared(sRedId[warp]));
   const int red_visit = lane / 10, red_sum = lane - red_visit * 10;   // the row lane `lane` adds at a flush
+  float* const acc_col = grad_acc + red_sum;
+  const uint32_t aIdMine = keep_u32(aId + (uint32_t)red_visit * 4u);
+  uint32_t aPark = aPark0;                                             // parking address of the next visit
   int nslot = 0;                                                       // visits parked in the buffer (warp-uniform)
 
 // add the parked rows: lane l < 10 nslot owns row l = (visit, sum) and issues its red.global.add
@@ -74,20 +76,20 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
   {                                                                                                       \
     __syncwarp();                                                                                         \
     if (lane < nslot * 10) {                                                                              \
-      const float4* row = reinterpret_cast<const float4*>(red + lane * RED_STRIDE);                       \
-      const float4 r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3], r4 = row[4], r5 = row[5], r6 = row[6],  \
-                   r7 = row[7];                                                                           \
+      const float4 r0 = lds128<0>(aRow), r1 = lds128<16>(aRow), r2 = lds128<32>(aRow), r3 = lds128<48>(aRow),  \
+                   r4 = lds128<64>(aRow), r5 = lds128<80>(aRow), r6 = lds128<96>(aRow), r7 = lds128<112>(aRow); \
       const float t0 = (r0.x + r0.y) + (r0.z + r0.w), t1 = (r1.x + r1.y) + (r1.z + r1.w);                 \
       const float t2 = (r2.x + r2.y) + (r2.z + r2.w), t3 = (r3.x + r3.y) + (r3.z + r3.w);                 \
       const float t4 = (r4.x + r4.y) + (r4.z + r4.w), t5 = (r5.x + r5.y) + (r5.z + r5.w);                 \
       const float t6 = (r6.x + r6.y) + (r6.z + r6.w), t7 = (r7.x + r7.y) + (r7.z + r7.w);                 \
       const float sum = ((t0 + t1) + (t2 + t3)) + ((t4 + t5) + (t6 + t7));                                \
-      atomicAdd(grad_acc + (size_t)red_id[red_visit] * 12 + red_sum, sum);                                \
+      atomicAdd(acc_col + (size_t)lds32u<0>(aIdMine) * 12, sum);                                          \
     }                                                                                                     \
     __syncwarp();                                                                                         \
     nslot = 0;                                                                                            \
+    aPark = aPark0;                                                                                       \
   }
-  const uint32_t aRec = (uint32_t)__cvta_generic_to_shared(sRec);
+  const uint32_t aRec = keep_u32((uint32_t)__cvta_generic_to_shared(sRec));
 
   // the binning buffer describes itself (BinningHeader): sorted point list + hit words
   const BinningHeader* hdr = reinterpret_cast<const BinningHeader*>(binning);
@@ -165,26 +167,50 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
     s6 = w * dp0##S; s7 = w * dp1##S; s8 = w * dp2##S; s9 = w * dp3##S;                                  \
   }
 
-  const int nb = ((int)max_last + 255) / 256;
-  for (int b = nb - 1; b >= 0; --b) {
-    const int base = b * 256;
-    const int cnt = min(256, (int)max_last - base);
-    __syncthreads();
-#pragma unroll
-    for (int j = tid; j < 256; j += 128) {
-      if (j < cnt) {
-        const uint32_t g = point_list[range.x + base + j];
-        const GsrRec* r = recs + g;
-        float hA, hB, hC, tau2;
-        stage_record(sRec, j, r->a, r->b, r->c, g, hA, hB, hC, tau2);
-      }
+  // Batches of GSR_BATCH entries from the back of the list, double buffered (render_common.cuh): a thread copies ONE
+  // entry per batch (three 16-byte cp.async from the entry's record; its Gaussian index was loaded a batch earlier) and
+  // the first 32 threads one hit word each, so the copies of the next batch are in flight while the warps replay this
+  // one; one barrier per batch.
+  const int nb = ((int)max_last + GSR_BATCH - 1) / GSR_BATCH;
+  const uint32_t* __restrict__ plist = point_list + range.x;
+  const uint32_t aMine = aRec + (uint32_t)tid * 16u;
+  const uint32_t aHit = (uint32_t)__cvta_generic_to_shared(sHit);
+  const uint32_t aHitA = keep_u32(aHit + (uint32_t)colA * 4u);   // column A of chunk 0, buffer 0 (column B = +8 bytes)
+  auto issue = [&](int b, int k, uint32_t gidx) {     // batch b (entries b * GSR_BATCH ...) into buffer k & 1
+    if (b * GSR_BATCH + tid < (int)max_last) {
+      const GsrRec* r = recs + gidx;
+      const uint32_t dst = aMine + (uint32_t)(k & 1) * (3u * GSR_PLANE);
+      cp_async16(dst, &r->a);
+      cp_async16(dst + GSR_PLANE, &r->b);
+      cp_async16(dst + 2 * GSR_PLANE, &r->c);
     }
-    if (tid < 64 && (tid >> 3) * 32 < cnt) sHit[tid >> 3][tid & 7] = hit_rows[(size_t)((base >> 5) + (tid >> 3)) * 8 + (tid & 7)];
-    __syncthreads();
+    // hit words of the batch's chunks: [chunk of the batch][sub-tile column]
+    if (tid < (GSR_BATCH / 32) * 8 && b * GSR_BATCH + (tid >> 3) * 32 < (int)max_last)
+      cp_async4(aHit + (uint32_t)(k & 1) * (GSR_BATCH / 32) * 32u + (uint32_t)tid * 4u,
+                hit_rows + (size_t)(b * (GSR_BATCH / 32) + (tid >> 3)) * 8 + (tid & 7));
+    cp_async_commit();
+  };
+  uint32_t gnext = 0;
+  {
+    const int e0 = (nb - 1) * GSR_BATCH + tid;
+    issue(nb - 1, 0, e0 < (int)max_last ? plist[e0] : 0u);
+    if (nb > 1) gnext = plist[(nb - 2) * GSR_BATCH + tid];
+  }
+  for (int b = nb - 1, k = 0; b >= 0; --b, ++k) {
+    const int base = b * GSR_BATCH;
+    const int cnt = min(GSR_BATCH, (int)max_last - base);
+    cp_async_wait_all();     // this thread's copies of batch b have landed ...
+    __syncthreads();         // ... everybody's have, and buffer (k + 1) & 1 (read by the previous batch) is free
+    if (b > 0) {
+      issue(b - 1, k + 1, gnext);
+      if (b > 1) gnext = plist[(b - 2) * GSR_BATCH + tid];
+    }
     if ((int)warp_last <= base) continue;  // nothing in this batch reaches the warp's pixels
+    const uint32_t aBuf = keep_u32(aRec + (uint32_t)(k & 1) * (3u * GSR_PLANE));
+    const uint32_t aHitBuf = keep_u32(aHitA + (uint32_t)(k & 1) * (GSR_BATCH / 32) * 32u);
 
     for (int c0 = ((min(cnt, (int)warp_last - base) - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
-      const uint32_t maskA = sHit[c0 >> 5][colA], maskB = sHit[c0 >> 5][colB];
+      const uint32_t maskA = lds32u<0>(aHitBuf + (uint32_t)c0), maskB = lds32u<8>(aHitBuf + (uint32_t)c0);  // (c0 / 32) * 32 B
       uint32_t mask = maskA | maskB;
       const uint32_t both = maskA & maskB;
       while (mask) {
@@ -193,7 +219,7 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
         mask ^= bitm;
         const int j = c0 + bit;
         const uint32_t idx = (uint32_t)(base + j);
-        const uint32_t addr = aRec + (uint32_t)j * 16u;
+        const uint32_t addr = aBuf + (uint32_t)j * 16u;
         const float4 ra = lds128<0>(addr);                    // {mean.x, mean.y, hA, hB}
         const float4 rb = lds128<GSR_PLANE>(addr);            // {hC, -opacity, r, g}
         const float4 rc = lds128<2 * GSR_PLANE>(addr);        // {b, 1/z, tau2, bits(gaussian id)}
@@ -268,28 +294,32 @@ __global__ void __launch_bounds__(128, 8) render_backward_kernel(
         // park the lane's ten sums in the warp's transposition buffer (row = visit slot * 10 + sum, column = lane);
         // every third visit the warp adds the 30 rows, one row per lane (GSR_BWD_FLUSH)
         {
-          const uint32_t dst = red_addr + (uint32_t)nslot * (10u * RED_STRIDE * 4u);
+          const uint32_t dst = aPark;
           sts32<0 * RED_STRIDE * 4>(dst, s0); sts32<1 * RED_STRIDE * 4>(dst, s1); sts32<2 * RED_STRIDE * 4>(dst, s2);
           sts32<3 * RED_STRIDE * 4>(dst, s3); sts32<4 * RED_STRIDE * 4>(dst, s4); sts32<5 * RED_STRIDE * 4>(dst, s5);
           sts32<6 * RED_STRIDE * 4>(dst, s6); sts32<7 * RED_STRIDE * 4>(dst, s7); sts32<8 * RED_STRIDE * 4>(dst, s8);
           sts32<9 * RED_STRIDE * 4>(dst, s9);
-          red_id[nslot] = __float_as_uint(rc.w);   // every lane stores the same word: one wavefront, no predicate
+          asm volatile("st.shared.f32 [%0], %1;" : : "r"(aId + (uint32_t)nslot * 4u), "f"(rc.w) : "memory");  // every lane
+          // stores the same word (the Gaussian index): one wavefront, no predicate
+          aPark += 10u * RED_STRIDE * 4u;
           if (++nslot == 3) GSR_BWD_FLUSH()
         }
       }
     }
   }
   if (nslot) GSR_BWD_FLUSH()
+  cp_async_wait_all();
 #undef GSR_BWD_FLUSH
 #undef GSR_BWD_ONE
 }
 
-cudaError_t launch_render_backward(const GsrView& v, const uint2* ranges, const void* binning, const GsrRec* recs,
+cudaError_t launch_render_backward(const GsrView& v, const uint2* ranges, const uint32_t* tile_order, const void* binning,
+                                   const GsrRec* recs,
                                    const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
                                    const float* dL_dinvdepth, float* grad_acc, cudaStream_t s) {
   const int tiles = v.gx * v.gy;
   if (tiles <= 0) return cudaSuccess;
-  render_backward_kernel<<<tiles, 128, 0, s>>>(v, ranges, (const char*)binning, recs, final_T, n_contrib, dL_dpix,
+  render_backward_kernel<<<tiles, 128, 0, s>>>(v, ranges, tile_order, (const char*)binning, recs, final_T, n_contrib, dL_dpix,
                                                dL_dinvdepth, grad_acc);
   count_launch();
   return cudaGetLastError();

@@ -73,6 +73,18 @@ template <int OFF>
 __device__ __forceinline__ void sts32(uint32_t addr, float v) {
   asm volatile("st.shared.f32 [%0+%1], %2;" : : "r"(addr), "n"(OFF), "f"(v) : "memory");
 }
+// A value the compiler must keep in a register: without this ptxas REMATERIALISES shared-memory addresses inside the hit
+// loops (S2R tid, S2R cta id, shifts, LEA, IMAD: 16 instructions per visit in render_backward_kernel's r2 SASS) rather
+// than hold them -- cheap by its cost model, but the loops are bound by instruction issue.
+__device__ __forceinline__ uint32_t keep_u32(uint32_t v) {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v));
+  return r;
+}
+template <int OFF>
+__device__ __forceinline__ void sts32u(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u32 [%0+%1], %2;" : : "r"(addr), "n"(OFF), "r"(v) : "memory");
+}
 // index of the most significant set bit (x != 0)
 __device__ __forceinline__ int msb_index(uint32_t x) {
   int r;
@@ -122,22 +134,29 @@ __device__ __forceinline__ f32x2 lds1x64(uint32_t addr) {
   return v;
 }
 
-// Staged batch: planes of 256 float4, plane p of entry j at byte offset p*4096 + j*16.  Opacity is stored negated
-// because the loops carry -alpha and -T (T (1 - alpha) = fma(-T, -alpha, -T) negated, alpha T = (-alpha)(-T): exact,
-// and no packed negation exists).  The packed instructions take a scalar register as a broadcast operand
-// (SASS `R.F32`), so per-splat values need no duplication: pk2(v, v) costs nothing.
+// ---- staged batches ----------------------------------------------------------------------------------------------
+// A batch of GSR_BATCH list entries lives in shared memory as planes of float4: plane p of entry j at byte offset
+// p * GSR_PLANE + j * 16 -- exactly the four words of the Gaussian's GsrRec (gsr_common.cuh), which the preprocess kernel
+// already wrote in this form, so staging is four 16-byte cp.async per entry and no arithmetic:
 //   plane 0 {mean.x, mean.y, hA, hB}   plane 1 {hC, -opacity, r, g}   plane 2 {b, 1/z, tau2, bits(gaussian id)}
-//   forward only: plane 3 = cull plane (make_cull_plane)
-#define GSR_PLANE 4096
-#define GSR_REC_PLANES 3
+//   plane 3 {kx, ky, tauM, z}  (forward only: the cull plane, make_cull_plane)
+// Opacity is stored negated because the loops carry -alpha and -T (T (1 - alpha) = fma(-T, -alpha, -T) negated,
+// alpha T = (-alpha)(-T): exact, and no packed negation exists).  The packed instructions take a scalar register as a
+// broadcast operand (SASS `R.F32`), so per-splat values need no duplication: pk2(v, v) costs nothing.
+// Two buffers: the copies of batch b + 1 are in flight while the warps composite batch b (ONE barrier per batch).
+#define GSR_BATCH 128
+#define GSR_PLANE (GSR_BATCH * 16)
 
-// a, b, c: the GsrRec words {mean2D.xy, conic.A, conic.B}, {conic.C, opacity, r, g}, {b, 1/z, tau, z}
-__device__ __forceinline__ void stage_record(float4 (*sRec)[256], int j, const float4 a, const float4 b, const float4 c,
-                                             uint32_t gid, float& hA, float& hB, float& hC, float& tau2) {
-  hA = a.z * GSR_HALF_LOG2E; hB = a.w * GSR_LOG2E; hC = b.x * GSR_HALF_LOG2E; tau2 = c.z * GSR_LOG2E;
-  sRec[0][j] = make_float4(a.x, a.y, hA, hB);
-  sRec[1][j] = make_float4(hC, -b.y, b.z, b.w);
-  sRec[2][j] = make_float4(c.x, c.y, tau2, __uint_as_float(gid));
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" : : "r"(smem_addr), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t smem_addr, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" : : "r"(smem_addr), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" : : : "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" : : : "memory"); }
+__device__ __forceinline__ void sts128(uint32_t addr, float x, float y, float z, float w) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" : : "r"(addr), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
 }
 
 // e = hA dx^2 + hC dy^2 + hB dx dy with a FIXED rounding sequence: the forward and the backward

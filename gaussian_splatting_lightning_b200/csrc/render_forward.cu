@@ -35,7 +35,8 @@
 
 namespace gsr {
 
-__global__ void __launch_bounds__(128) render_forward_kernel(const GsrView v, const uint2* __restrict__ ranges,
+__global__ void __launch_bounds__(128, 9) render_forward_kernel(const GsrView v, const uint2* __restrict__ ranges,
+                                                             const uint32_t* __restrict__ tile_order,
                                                              const uint32_t* __restrict__ point_list,
                                                              const GsrRec* __restrict__ recs,
                                                              float* __restrict__ out_color,
@@ -43,10 +44,10 @@ __global__ void __launch_bounds__(128) render_forward_kernel(const GsrView v, co
                                                              float* __restrict__ final_T,
                                                              uint32_t* __restrict__ n_contrib,
                                                              uint32_t* __restrict__ hits) {
-  __shared__ float4 sRec[GSR_REC_PLANES + 1][256];  // staged batch (render_common.cuh); last plane = cull plane
+  __shared__ float4 sRec[2][4][GSR_BATCH];  // two staged batches of four planes (render_common.cuh); plane 3 = cull plane
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tile = blockIdx.x;
+  const int tile = tile_order ? (int)tile_order[blockIdx.x] : (int)blockIdx.x;
   const int tx = tile % v.gx, ty = tile / v.gx;
   // warp -> 8x8 block = sub-tiles A (upper 8x4) and B (lower 8x4); lane -> one pixel in each
   const int sx0 = tx * GSR_TILE + (warp & 1) * 8, sy0 = ty * GSR_TILE + (warp >> 1) * 8;
@@ -92,32 +93,53 @@ __global__ void __launch_bounds__(128) render_forward_kernel(const GsrView v, co
     ok##S##_bits |= ok ? bitm : 0u;                                                         \
   }
 
-  for (int base = 0; base < n; base += 256) {
-    if (__syncthreads_and(thrA == NEG_INF && thrB == NEG_INF)) break;
-    const int cnt = min(256, n - base);
-#pragma unroll
-    for (int j = tid; j < 256; j += 128) {
-      if (j < cnt) {
-        const uint32_t g = point_list[range.x + base + j];
-        const GsrRec* r = recs + g;
-        float hA, hB, hC, tau2;
-        stage_record(sRec, j, r->a, r->b, r->c, g, hA, hB, hC, tau2);
-        sRec[GSR_REC_PLANES][j] = make_cull_plane(hA, hB, hC, tau2);
-      } else {
-        // padding: never a hit.  The geometry planes the culling test reads are zeroed too: stale shared memory
-        // (another kernel's data) may hold -inf / NaN patterns, and -inf <= -inf would let a padded entry pass.
-        sRec[0][j] = make_float4(0.f, 0.f, 0.f, 0.f);
-        sRec[1][j] = make_float4(0.f, 0.f, 0.f, 0.f);
-        sRec[GSR_REC_PLANES][j] = make_float4(0.f, 0.f, NEG_INF, 0.f);
-      }
+  // Batches of GSR_BATCH entries, double buffered: a thread copies ONE entry per batch (four 16-byte cp.async from the
+  // entry's 64-byte record, whose Gaussian index it loaded a batch earlier), so the copies of batch b + 1 and the index
+  // loads of batch b + 2 are in flight while the warps composite batch b; one barrier per batch.
+  const int nb = (n + GSR_BATCH - 1) / GSR_BATCH;
+  const uint32_t* __restrict__ plist = point_list + range.x;
+  const uint32_t aMine = aRec + (uint32_t)tid * 16u;            // this thread's entry slot in buffer 0, plane 0
+  auto issue = [&](int b, uint32_t gidx) {                       // stage entry b * GSR_BATCH + tid into buffer b & 1
+    const uint32_t dst = aMine + (uint32_t)(b & 1) * (4u * GSR_PLANE);
+    if (b * GSR_BATCH + tid < n) {
+      const GsrRec* r = recs + gidx;
+      cp_async16(dst, &r->a);
+      cp_async16(dst + GSR_PLANE, &r->b);
+      cp_async16(dst + 2 * GSR_PLANE, &r->c);
+      cp_async16(dst + 3 * GSR_PLANE, &r->d);
+    } else {
+      // padding: never a hit.  The geometry planes the culling test reads are zeroed too: stale shared memory
+      // (another kernel's data) may hold -inf / NaN patterns, and -inf <= -inf would let a padded entry pass.
+      sts128(dst, 0.f, 0.f, 0.f, 0.f);
+      sts128(dst + GSR_PLANE, 0.f, 0.f, 0.f, 0.f);
+      sts128(dst + 3 * GSR_PLANE, 0.f, 0.f, NEG_INF, 0.f);
     }
-    __syncthreads();
+    cp_async_commit();
+  };
+  uint32_t gnext = 0;
+  if (nb > 0) {
+    issue(0, tid < n ? plist[tid] : 0u);
+    if (GSR_BATCH + tid < n) gnext = plist[GSR_BATCH + tid];
+  }
+  for (int b = 0; b < nb; ++b) {
+    const int base = b * GSR_BATCH;
+    cp_async_wait_all();                                         // this thread's copies of batch b have landed ...
+    if (__syncthreads_and(thrA == NEG_INF && thrB == NEG_INF)) break;   // ... and after the barrier everybody's have
+    if (b + 1 < nb) {                                            // buffer (b + 1) & 1 was read by batch b - 1: free now
+      issue(b + 1, gnext);
+      if (base + 2 * GSR_BATCH + tid < n) gnext = plist[base + 2 * GSR_BATCH + tid];
+    }
+    const int cnt = min(GSR_BATCH, n - base);
     if (__all_sync(0xffffffffu, thrA == NEG_INF && thrB == NEG_INF)) continue;  // warp saturated: only the barriers
+    const uint32_t aBuf = aRec + (uint32_t)(b & 1) * (4u * GSR_PLANE);
+    const float4* sGeo = &sRec[b & 1][0][0];
+    const float4* sHC = &sRec[b & 1][1][0];
+    const float4* sCull = &sRec[b & 1][3][0];
 
     for (int c0 = 0; c0 < cnt; c0 += 32) {
       // one splat per lane against the warp's two sub-tiles
-      const float4 geo = sRec[0][c0 + lane], cull = sRec[GSR_REC_PLANES][c0 + lane];   // {mean.x, mean.y, hA, hB}
-      const float hCl = sRec[1][c0 + lane].x;
+      const float4 geo = sGeo[c0 + lane], cull = sCull[c0 + lane];   // {mean.x, mean.y, hA, hB}, {kx, ky, tauM, -}
+      const float hCl = sHC[c0 + lane].x;
       const bool allA = __all_sync(0xffffffffu, thrA == NEG_INF), allB = __all_sync(0xffffffffu, thrB == NEG_INF);
       if (allA && allB) break;
       const uint32_t maskA = __ballot_sync(0xffffffffu, !allA && subtile_may_contribute(geo, hCl, cull, stA));
@@ -129,7 +151,7 @@ __global__ void __launch_bounds__(128) render_forward_kernel(const GsrView v, co
         const int bit = __ffs(mask) - 1;
         const uint32_t bitm = mask & (0u - mask);
         mask ^= bitm;
-        const uint32_t addr = aRec + (uint32_t)(c0 + bit) * 16u;
+        const uint32_t addr = aBuf + (uint32_t)(c0 + bit) * 16u;
         const float4 ra = lds128<0>(addr);                    // {mean.x, mean.y, hA, hB}
         const float4 rb = lds128<GSR_PLANE>(addr);            // {hC, -opacity, r, g}
         const float2 rc = lds64<2 * GSR_PLANE>(addr);         // {b, 1/z}
@@ -185,6 +207,7 @@ __global__ void __launch_bounds__(128) render_forward_kernel(const GsrView v, co
     }
   }
 #undef GSR_FWD_ONE
+  cp_async_wait_all();   // a CTA that left the list early must not retire under its own in-flight copies
 
   const size_t HW = (size_t)v.H * v.W;
   const float* __restrict__ bg = v.bg;
@@ -210,12 +233,12 @@ __global__ void __launch_bounds__(128) render_forward_kernel(const GsrView v, co
   }
 }
 
-cudaError_t launch_render_forward(const GsrView& v, const uint2* ranges, const uint32_t* point_list,
-                                  const GsrRec* recs, float* out_color, float* out_invdepth, float* final_T,
-                                  uint32_t* n_contrib, uint32_t* hits, cudaStream_t s) {
+cudaError_t launch_render_forward(const GsrView& v, const uint2* ranges, const uint32_t* tile_order,
+                                  const uint32_t* point_list, const GsrRec* recs, float* out_color, float* out_invdepth,
+                                  float* final_T, uint32_t* n_contrib, uint32_t* hits, cudaStream_t s) {
   const int tiles = v.gx * v.gy;
   if (tiles <= 0) return cudaSuccess;
-  render_forward_kernel<<<tiles, 128, 0, s>>>(v, ranges, point_list, recs, out_color, out_invdepth, final_T,
+  render_forward_kernel<<<tiles, 128, 0, s>>>(v, ranges, tile_order, point_list, recs, out_color, out_invdepth, final_T,
                                               n_contrib, hits);
   count_launch();
   return cudaGetLastError();

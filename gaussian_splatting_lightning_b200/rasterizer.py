@@ -97,10 +97,41 @@ class _Frame:
             N.ptr(self.scales), N.ptr(self.rotations), N.ptr(self.cov3D))
 
 
+def _next_hint(key, binning_hint, R):
+    counters["forward_calls"] += 1
+    if 0 < binning_hint < R:
+        counters["hint_retries"] += 1
+    # the largest of the last 8 frames at this resolution: the views of a step differ in R, and a hint that is too
+    # small costs a second binning + compositing pass while one that is too large costs only memory
+    recent = _recent.setdefault(key, [])
+    recent.append(_bucket(int(R * 1.125) + 4096))
+    del recent[:-8]
+    _hint[key] = max(recent)
+
+
 def forward_raw(rs: GaussianRasterizationSettings, means3D, sh, colors_precomp, opacities, scales, rotations,
                 cov3Ds_precomp, binning_hint: Optional[int] = None):
     """_C.rasterize_gaussians: returns (num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer,
     invdepths, binning_capacity)."""
+    ext = N.ext()
+    if ext is not None:
+        if not means3D.is_cuda:
+            raise RuntimeError("gaussian_splatting_lightning_b200 rasterizes on CUDA devices only (no CPU fallback)")
+        H, W = int(rs.image_height), int(rs.image_width)
+        key = (means3D.device.index, W, H)
+        if binning_hint is None:
+            binning_hint = 0 if _sync_mode() else _hint.get(key, 0)
+        try:
+            R, color, radii, geom, binning, img, invdepth, cap = ext.rasterize_gaussians_ex(
+                rs.bg, means3D, colors_precomp, opacities, scales, rotations, float(rs.scale_modifier), cov3Ds_precomp,
+                rs.viewmatrix, rs.projmatrix, float(rs.tanfovx), float(rs.tanfovy), H, W, sh, int(rs.sh_degree),
+                rs.campos, bool(rs.prefiltered), bool(rs.antialiasing), bool(rs.debug), int(binning_hint))
+        except RuntimeError as e:
+            if "gsr_" in str(e):
+                raise N.GsrError(str(e)) from None
+            raise
+        _next_hint(key, binning_hint, R)
+        return R, color, radii, geom, binning, img, invdepth, cap
     fr = _Frame(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
     dev = fr.device
     with torch.cuda.device(dev):
@@ -119,15 +150,7 @@ def forward_raw(rs: GaussianRasterizationSettings, means3D, sh, colors_precomp, 
         if alloc.error is not None:
             raise alloc.error
         N.check(rc, "gsr_forward")
-        counters["forward_calls"] += 1
-        if 0 < binning_hint < R.value:
-            counters["hint_retries"] += 1
-        # the largest of the last 8 frames at this resolution: the views of a step differ in R, and a hint that is too
-        # small costs a second binning + compositing pass while one that is too large costs only memory
-        recent = _recent.setdefault(key, [])
-        recent.append(_bucket(int(R.value * 1.125) + 4096))
-        del recent[:-8]
-        _hint[key] = max(recent)
+        _next_hint(key, binning_hint, R.value)
     return (int(R.value), color, radii, alloc.buffers[N.GSR_BUF_GEOM], alloc.buffers[N.GSR_BUF_BINNING],
             alloc.buffers[N.GSR_BUF_IMG], invdepth, int(cap.value))
 
@@ -149,6 +172,27 @@ def backward_raw(rs: GaussianRasterizationSettings, means3D, radii, sh, colors_p
       stats           dict with any of max_radii2D / xyz_grad_accum / xyz_grad_count, (P,) float32:
                       the view's densification statistics (gaussian_model.py:174-181), fused.
     """
+    ext = N.ext()
+    if ext is not None:
+        if accumulate_into is not None:
+            acc, mask = [accumulate_into.get(n) for n in _GRAD_NAMES], 0
+        else:
+            names = _GRAD_NAMES if want is None else tuple(want)
+            acc, mask = [], sum(1 << i for i, n in enumerate(_GRAD_NAMES) if n in names)
+        st = [stats.get("max_radii2D"), stats.get("xyz_grad_accum"), stats.get("xyz_grad_count")] if stats else []
+        if dL_dcolor is None and dL_dinvdepth is None:
+            dL_dcolor = torch.zeros((3, int(rs.image_height), int(rs.image_width)), dtype=torch.float32,
+                                    device=means3D.device)
+        try:
+            return tuple(ext.rasterize_gaussians_backward_ex(
+                rs.bg, means3D, radii, colors_precomp, opacities, scales, rotations, float(rs.scale_modifier),
+                cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, float(rs.tanfovx), float(rs.tanfovy), dL_dcolor,
+                dL_dinvdepth, sh, int(rs.sh_degree), rs.campos, geomBuffer, int(num_rendered), binningBuffer, imgBuffer,
+                bool(rs.antialiasing), bool(rs.debug), mask, acc, st))
+        except RuntimeError as e:
+            if "gsr_" in str(e):
+                raise N.GsrError(str(e)) from None
+            raise
     fr = _Frame(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
     dev, P, M = fr.device, fr.P, fr.M
     shapes = dict(dL_dmeans2D=(P, 3), dL_dcolors=(P, 3), dL_dopacity=(P, 1), dL_dmeans3D=(P, 3), dL_dcov3D=(P, 6),
@@ -192,6 +236,9 @@ def mark_visible(positions: torch.Tensor, viewmatrix: torch.Tensor, projmatrix: 
     """_C.mark_visible (tests/rasterizer_python/test_mark_visible.py:13-14)."""
     if not positions.is_cuda:
         raise RuntimeError("mark_visible runs on CUDA devices only (no CPU fallback)")
+    ext = N.ext()
+    if ext is not None:
+        return ext.mark_visible(positions, viewmatrix, projmatrix)
     dev = positions.device
     p = N.f32c(positions)
     P = int(positions.shape[0])
@@ -374,3 +421,42 @@ def sort_pairs(keys: torch.Tensor, vals: torch.Tensor, end_bit: int = 64):
         N.check(N.lib().gsr_sort_pairs(N.ptr(keys), N.ptr(vals), N.ptr(ko), N.ptr(vo), N.ptr(kt), N.ptr(vt), n,
                                        int(end_bit), N.ptr(ws), N.stream_ptr(dev)), "gsr_sort_pairs")
     return ko, vo
+
+
+def hit_word_stats(rs: GaussianRasterizationSettings, binningBuffer, n_contrib, ranges, binning_capacity: int) -> dict:
+    """What the backward compositing kernel actually evaluates, counted from the forward's hit words (debug accessor,
+    bench.py's roofline): per (warp, list entry) VISIT the kernel runs the packed two-pixel path when the entry reached
+    both 8x4 sub-tiles of the warp's 8x8 block and the one-pixel path otherwise, so
+
+        pairs_evaluated = 32 lanes * (2 * visits_both + visits_single)        (pixel, splat) evaluations,
+
+    against A = sum(n_contrib), the convention of SURVEY.md 8(d) that also counts pairs the culling skipped.
+    n_contrib (H,W) int32 and ranges (T,2) int32 as export_state returns them."""
+    dev = n_contrib.device
+    H, W = int(rs.image_height), int(rs.image_width)
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    T = gx * gy
+    cap = int(binning_capacity)
+    hits_off = 128 + (cap * 4 + 127) // 128 * 128                  # gsr_bin_hits_off (csrc/gsr_common.cuh)
+    n_words = (cap // 32 + T + 2) * 8
+    hits = binningBuffer[hits_off:hits_off + 4 * n_words].view(torch.int32).view(-1, 8)
+    pad = torch.zeros((gy * 16, gx * 16), dtype=torch.int64, device=dev)
+    pad[:H, :W] = n_contrib.to(torch.int64)
+    # last contributor per 8x8 block = per warp; warp w of a tile owns block (w & 1, w >> 1)
+    blk = pad.view(gy, 2, 8, gx, 2, 8).amax(dim=(2, 5))           # (gy, by, gx, bx)
+    warp_last = blk.permute(0, 2, 1, 3).reshape(T, 4)             # [tile][warp = by * 2 + bx]
+    nchunks = (warp_last + 31) // 32                               # chunks of 32 entries the backward walks
+    slot0 = (ranges[:, 0].to(torch.int64) >> 5) + torch.arange(T, device=dev)
+    both = single = 0
+    for w in range(4):
+        colA = (w >> 1) * 4 + (w & 1)
+        n = nchunks[:, w]
+        tile_of = torch.repeat_interleave(torch.arange(T, device=dev), n)
+        first = torch.cumsum(n, 0) - n
+        k = torch.arange(tile_of.numel(), device=dev) - first[tile_of]
+        rows = hits[slot0[tile_of] + k]
+        a, b = rows[:, colA], rows[:, colA + 2]
+        pc = lambda x: sum(((x >> s) & 0x01010101) for s in range(8)).view(torch.uint8).to(torch.int64).sum()
+        both += int(pc(a & b))
+        single += int(pc(a ^ b))
+    return dict(visits_both=both, visits_single=single, pairs_evaluated=32 * (2 * both + single))

@@ -31,6 +31,15 @@ def load(name):
     return g, d, (w_img * mask[None]).astype(np.float32), (w_dep * mask[None]).astype(np.float32)
 
 
+def load_dir_weights(name):
+    """Loss weights of the dense directions: `dir_mask` also leaves out the pixels on the alpha floor's contour."""
+    g = np.load(os.path.join(HERE, "golden", name + "_grads.npz"))
+    d = np.load(os.path.join(HERE, "golden", name + ".npz"))
+    w_img, w_dep = loss_weights(int(d["image_height"]), int(d["image_width"]))
+    m = g["dir_mask"]
+    return (w_img * m[None]).astype(np.float32), (w_dep * m[None]).astype(np.float32)
+
+
 def tangential(grads: dict, rotations: np.ndarray) -> dict:
     """The reference normalises q inside computeConv3D (render_tools.py:61): its derivative with respect to a unit
     quaternion is the tangential part (I - q q^T) g of the derivative g the CUDA semantics give."""
@@ -42,8 +51,9 @@ def tangential(grads: dict, rotations: np.ndarray) -> dict:
     return out
 
 
-def compare(name: str, grads: dict, verbose=True):
-    """grads: name -> array, the analytic gradients for dL_dcolor = w_img, dL_dinvdepth = w_dep of load(name).
+def compare(name: str, grads: dict, grads_dir: dict = None, verbose=True):
+    """grads: name -> array, the analytic gradients for dL_dcolor = w_img, dL_dinvdepth = w_dep of load(name);
+    grads_dir: the same for the weights of load_dir_weights(name) (the dense directions' loss).
     Returns a list of (what, worst ratio err / tol) and asserts every sample within tolerance."""
     g, d, _, _ = load(name)
     grads = tangential(grads, d["rotations"])
@@ -63,6 +73,9 @@ def compare(name: str, grads: dict, verbose=True):
                   f"max abs err {err.max():.3e}")
         assert worst <= 1.0, (name, tname, worst)
     # dense directions: sum_t h_t <g_t, d_t>
+    if grads_dir is None:
+        return report
+    grads = tangential(grads_dir, d["rotations"])
     deg = int(d["sh_degree"])
     fdd = g["dirs_fd"]
     for j, k in enumerate(g["dir_k"]):

@@ -22,4 +22,5 @@ def test_cuda_backward_matches_reference_finite_differences(name):
     st = U.export(out)
     assert ((st["final_T"] >= 1e-3) == g["mask"]).mean() > 0.9999
     got = U.run_cuda_backward(out, w_img, w_dep)
-    GG.compare(name, got)
+    wd_img, wd_dep = GG.load_dir_weights(name)
+    GG.compare(name, got, U.run_cuda_backward(out, wd_img, wd_dep))

