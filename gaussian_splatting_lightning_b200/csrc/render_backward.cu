@@ -76,13 +76,18 @@ __global__ void __launch_bounds__(128, 7) render_backward_kernel(
   {                                                                                                       \
     __syncwarp();                                                                                         \
     if (lane < nslot * 10) {                                                                              \
-      const float4 r0 = lds128<0>(aRow), r1 = lds128<16>(aRow), r2 = lds128<32>(aRow), r3 = lds128<48>(aRow),  \
-                   r4 = lds128<64>(aRow), r5 = lds128<80>(aRow), r6 = lds128<96>(aRow), r7 = lds128<112>(aRow); \
-      const float t0 = (r0.x + r0.y) + (r0.z + r0.w), t1 = (r1.x + r1.y) + (r1.z + r1.w);                 \
-      const float t2 = (r2.x + r2.y) + (r2.z + r2.w), t3 = (r3.x + r3.y) + (r3.z + r3.w);                 \
-      const float t4 = (r4.x + r4.y) + (r4.z + r4.w), t5 = (r5.x + r5.y) + (r5.z + r5.w);                 \
-      const float t6 = (r6.x + r6.y) + (r6.z + r6.w), t7 = (r7.x + r7.y) + (r7.z + r7.w);                 \
-      const float sum = ((t0 + t1) + (t2 + t3)) + ((t4 + t5) + (t6 + t7));                                \
+      f32x2 a0, a1, a2, a3, a4, a5, a6, a7, a8, a9, a10, a11, a12, a13, a14, a15;                        \
+      lds2x64<0>(aRow, a0, a1); lds2x64<16>(aRow, a2, a3); lds2x64<32>(aRow, a4, a5); lds2x64<48>(aRow, a6, a7);   \
+      lds2x64<64>(aRow, a8, a9); lds2x64<80>(aRow, a10, a11); lds2x64<96>(aRow, a12, a13);                \
+      lds2x64<112>(aRow, a14, a15);                                                                       \
+      /* 32 floats as 16 packed pairs: 15 FADD2 + 1 FADD instead of 31 FADD */                            \
+      a0 = add2(a0, a1); a2 = add2(a2, a3); a4 = add2(a4, a5); a6 = add2(a6, a7);                         \
+      a8 = add2(a8, a9); a10 = add2(a10, a11); a12 = add2(a12, a13); a14 = add2(a14, a15);                \
+      a0 = add2(a0, a2); a4 = add2(a4, a6); a8 = add2(a8, a10); a12 = add2(a12, a14);                     \
+      a0 = add2(add2(a0, a4), add2(a8, a12));                                                             \
+      float slo, shi;                                                                                     \
+      upk2(a0, slo, shi);                                                                                 \
+      const float sum = slo + shi;                                                                        \
       atomicAdd(acc_col + (size_t)lds32u<0>(aIdMine) * 12, sum);                                          \
     }                                                                                                     \
     __syncwarp();                                                                                         \

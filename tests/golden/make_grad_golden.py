@@ -186,11 +186,22 @@ def main():
 
         def central_d(make, h):
             return (loss_d(make(+h)) - loss_d(make(-h))) / (2 * h)
+        # Gaussians outside 1.3 x the field of view do not move: there the reference clamps x/z, y/z before building the
+        # EWA Jacobian (render_tools.py:26-31) and its exact derivative sees x = lim * z, while the CUDA semantics the
+        # oracle and the kernels follow gate dL/dx to zero and treat the clamped x as a constant in dJ/dz -- a known
+        # difference of the two backward conventions for splats that sit outside the image (g2: 296 of 1500 Gaussians;
+        # with them moving, the directional derivatives differed by 1e-4 .. 4e-4 relative, without by < 5e-6)
+        import importlib
+        ct = importlib.import_module("gs_lightning.rasterize.camera_tools")
+        pv = ct.apply_extrinsic_matrix(torch.tensor(sc.params["means3D"]), sc.cam["viewmatrix"]).numpy()
+        free = (np.abs(pv[:, 0] / pv[:, 2]) <= 1.3 * sc.cam["tanfovx"]) & (np.abs(pv[:, 1] / pv[:, 2]) <= 1.3 * sc.cam["tanfovy"])
         cand_fd = []
         for k in range(3 * NUM_DIRS):
             dvec = {t: direction(k, t, sc.params[t].shape) for t in TENSORS}
             if sc.deg < 3:   # no movement in unused SH coefficients
                 dvec["shs"][:, (sc.deg + 1) ** 2:, :] = 0.0
+            for t in TENSORS:
+                dvec[t][~free] = 0.0
 
             def make(step):
                 return {t: sc.params[t] + step * hs[t] * dvec[t] for t in TENSORS}
@@ -201,10 +212,11 @@ def main():
             if abs(f1 - f2) <= 2e-6 * max(abs(f1), floor) and len(dir_k) < NUM_DIRS:
                 dir_k.append(k); dirs_fd.append(f1); dirs_fd2.append(f2)
         print(f"  {name}: {len(dir_k)} of {len(cand_fd)} candidate directions pass the h/2h check; "
-              f"{int((mask & ~dir_mask).sum())} pixels near the alpha floor left out of their loss", flush=True)
+              f"{int((mask & ~dir_mask).sum())} pixels near the alpha floor left out of their loss, "
+              f"{int((~free).sum())} Gaussians outside 1.3 x FOV held still", flush=True)
         out = os.path.join(HERE, name + "_grads.npz")
         np.savez_compressed(
-            out, mask=mask, dir_mask=dir_mask, tensor=np.array(rec["tensor"], np.int32), index=np.array(rec["index"], np.int64),
+            out, mask=mask, dir_mask=dir_mask, dir_gaussians=free, tensor=np.array(rec["tensor"], np.int32), index=np.array(rec["index"], np.int64),
             fd=np.array(rec["fd"], np.float64), fd2=np.array(rec["fd2"], np.float64), step=np.array(rec["step"], np.float64),
             dir_k=np.array(dir_k, np.int32), dirs_fd=np.array(dirs_fd, np.float64), dirs_fd2=np.array(dirs_fd2, np.float64),
             dir_steps=np.array([hs[t] for t in TENSORS], np.float64), dir_step=np.float64(DIR_STEP),

@@ -85,6 +85,7 @@ def compare(name: str, grads: dict, grads_dir: dict = None, verbose=True):
             dv = direction(int(k), tname, d[tname].shape)
             if tname == "shs" and deg < 3:
                 dv[:, (deg + 1) ** 2:, :] = 0.0
+            dv[~g["dir_gaussians"]] = 0.0     # Gaussians outside 1.3 x FOV are held still (make_grad_golden.py)
             tot += g["dir_steps"][ti] * float((a * dv).sum())
             mag += g["dir_steps"][ti] * float(np.abs(a * dv).sum())
         # the dot product cancels heavily (mag >> |tot|): float32 rounding of the analytic side is judged against mag

@@ -24,7 +24,7 @@ def test_c2_matches_oracle(oracle_lib):
     assert np.array_equal(st["vals_sorted"].view(np.uint32), ref["point_list"])
     assert np.array_equal(st["ranges"].view(np.uint32), ref["ranges"])
     frac, mx = U.close_fraction(out["color"].cpu().numpy(), ref["color"], 1e-4, 1e-4)
-    assert frac <= 2e-4 and mx <= 2e-2, (frac, mx)
+    assert frac <= 1e-4 and mx <= 1e-2, (frac, mx)
     rng = np.random.default_rng(3)
     dC = rng.standard_normal((3, H, W)).astype(np.float32)
     dD = rng.standard_normal((1, H, W)).astype(np.float32)
@@ -140,7 +140,7 @@ def test_full_size_matches_oracle(oracle_lib, name, backward):
                             (st["final_T"], ref["final_T"], "final_T")):
         frac, mx = U.close_fraction(got, want, 1e-4, 1e-4)
         print(f"{name} {what}: outlier fraction {frac:.2e}, max abs err {mx:.2e}")
-        assert frac <= 2e-4 and mx <= 2e-2, (what, frac, mx)
+        assert frac <= 1e-4 and mx <= 1e-2, (what, frac, mx)
     mism = float((st["n_contrib"].view(np.uint32) != ref["n_contrib"]).mean())
     print(f"{name} n_contrib mismatch fraction {mism:.2e}")
     assert mism <= 2e-4

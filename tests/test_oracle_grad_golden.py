@@ -27,7 +27,9 @@ def test_grad_goldens_are_reference_derived_and_selective():
     """The fixtures hold what their generator promises: h / 2h agreement of every kept sample, non-trivial values."""
     for name in GG.GRAD_GOLDENS:
         g = np.load(os.path.join(GOLDEN_DIR, name + "_grads.npz"))
-        assert len(g["fd"]) >= 150 and len(g["dirs_fd"]) >= 8
+        assert len(g["fd"]) >= 150 and len(g["dirs_fd"]) >= 8 and len(g["dir_k"]) == len(g["dirs_fd"])
+        assert g["dir_mask"].shape == g["mask"].shape and not (g["dir_mask"] & ~g["mask"]).any()
+        assert np.abs(g["dirs_fd"] - g["dirs_fd2"]).max() <= 2e-6 * np.abs(g["dirs_fd"]).max()
         for ti in range(5):
             fd, fd2 = g["fd"][g["tensor"] == ti], g["fd2"][g["tensor"] == ti]
             assert (np.abs(fd - fd2) <= 2e-6 * np.maximum(np.abs(fd), np.median(np.abs(fd))) + 1e-300).all()
