@@ -307,6 +307,10 @@ int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, con
   if (rc) return rc;
   rc = make_view(settings, g.M, &v);
   if (rc) return rc;
+  if (flags & ~(GSR_GRADS_ACCUMULATE | GSR_BWD_RENDER_ONLY)) return fail(GSR_EINVAL, "backward: unknown flag");
+  const bool render_only = (flags & GSR_BWD_RENDER_ONLY) != 0;
+  static const GsrGrads no_grads = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  if (render_only && !grads) grads = &no_grads;
   if (!grads) return fail(GSR_EINVAL, "backward: grads is NULL");
   const int P = g.P;
   if (P == 0) return GSR_OK;
@@ -314,7 +318,6 @@ int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, con
     return fail(GSR_EINVAL, "backward: NULL buffer");
   if (grads->dL_drotations && (reinterpret_cast<uintptr_t>(grads->dL_drotations) & 15))
     return fail(GSR_EINVAL, "dL_drotations must be 16-byte aligned");
-  if (flags & ~GSR_GRADS_ACCUMULATE) return fail(GSR_EINVAL, "backward: unknown flag");
   const bool debug = settings->debug != 0;
   GeomState geom = GeomState::carve((char*)geom_, P);
   ImgState img = ImgState::carve((char*)img_, v.W, v.H);
@@ -333,8 +336,64 @@ int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, con
     GSR_STAGE(ST_RENDER_BWD, gsr::launch_render_backward(v, img.ranges, img.tile_order, binning_, geom.recs, img.final_T, img.n_contrib, dL_dcolor,
                                           dL_dinvdepth, grad_acc, stream),
               "render backward kernel", debug, stream);
+  if (render_only) return GSR_OK;   // the raw sums stay in `scratch` for gsr_preprocess_backward_views
   GSR_STAGE(ST_PREPROCESS_BWD, gsr::launch_preprocess_backward(v, g, radii, geom, grad_acc, out, stream),
             "preprocess backward kernel", debug, stream);
+  return GSR_OK;
+}
+
+int gsr_preprocess_backward_views(const GsrViewState* views, int32_t num_views, const GsrGaussians* gaussians,
+                                  const GsrGrads* grads, int32_t flags, const GsrDensifyStats* stats, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (!views || num_views < 0 || !grads) return fail(GSR_EINVAL, "preprocess_backward_views: bad arguments");
+  if (flags & ~GSR_GRADS_ACCUMULATE) return fail(GSR_EINVAL, "preprocess_backward_views: unknown flag");
+  if (grads->dL_dmeans2D) return fail(GSR_EINVAL, "preprocess_backward_views: dL_dmeans2D is a per-view output (pass NULL)");
+  if (num_views == 0) return GSR_OK;
+  for (int k = 0; k < num_views; ++k)
+    if (!views[k].settings) return fail(GSR_EINVAL, "preprocess_backward_views: settings is NULL");
+  GsrGaussiansDev g;
+  int rc = make_gaussians(gaussians, views[0].settings->sh_degree, &g);
+  if (rc) return rc;
+  const int P = g.P;
+  if (P == 0) return GSR_OK;
+  if (grads->dL_drotations && (reinterpret_cast<uintptr_t>(grads->dL_drotations) & 15))
+    return fail(GSR_EINVAL, "dL_drotations must be 16-byte aligned");
+  std::vector<GsrView> vv(num_views);
+  std::vector<const int32_t*> radii(num_views);
+  std::vector<GeomState> geoms(num_views);
+  std::vector<const float*> accs(num_views);
+  for (int k = 0; k < num_views; ++k) {
+    const GsrViewState& s = views[k];
+    rc = make_view(s.settings, g.M, &vv[k]);
+    if (rc) return rc;
+    if (!s.radii || !s.geom || !s.scratch) return fail(GSR_EINVAL, "preprocess_backward_views: NULL buffer in a view");
+    if (s.settings->sh_degree != views[0].settings->sh_degree || s.settings->scale_modifier != views[0].settings->scale_modifier ||
+        (s.settings->antialiasing != 0) != (views[0].settings->antialiasing != 0))
+      return fail(GSR_EINVAL, "preprocess_backward_views: the views must share sh_degree, scale_modifier and antialiasing");
+    radii[k] = s.radii;
+    geoms[k] = GeomState::carve((char*)s.geom, P);
+    accs[k] = (const float*)s.scratch;
+  }
+  gsr::PreBwdOut out;
+  out.dL_dmeans2D = nullptr; out.dL_dcolors = grads->dL_dcolors; out.dL_dopacity = grads->dL_dopacity;
+  out.dL_dmeans3D = grads->dL_dmeans3D; out.dL_dcov3D = grads->dL_dcov3D; out.dL_dsh = grads->dL_dsh;
+  out.dL_dscales = grads->dL_dscales; out.dL_drot = grads->dL_drotations;
+  out.accumulate = (flags & GSR_GRADS_ACCUMULATE) ? 1 : 0;
+  out.max_radii2D = stats ? stats->max_radii2D : nullptr;
+  out.xyz_grad_accum = stats ? stats->xyz_grad_accum : nullptr;
+  out.xyz_grad_count = stats ? stats->xyz_grad_count : nullptr;
+  const bool debug = views[0].settings->debug != 0;
+  if (gsr::preprocess_backward_views_supported(g, out)) {
+    GSR_STAGE(ST_PREPROCESS_BWD, gsr::launch_preprocess_backward_views(num_views, vv.data(), radii.data(), geoms.data(),
+                                                                       accs.data(), g, out, stream),
+              "preprocess backward kernel (all views)", debug, stream);
+  } else {  // layouts the fused kernel does not take (SH rows that are not 16-byte multiples, unaligned tensors)
+    for (int k = 0; k < num_views; ++k) {
+      GSR_STAGE(ST_PREPROCESS_BWD, gsr::launch_preprocess_backward(vv[k], g, radii[k], geoms[k], accs[k], out, stream),
+                "preprocess backward kernel", debug, stream);
+      out.accumulate = 1;
+    }
+  }
   return GSR_OK;
 }
 

@@ -287,6 +287,12 @@ struct PreBwdOut {
 cudaError_t launch_preprocess_backward(const GsrView& v, const GsrGaussiansDev& g, const int32_t* radii,
                                        const GeomState& geom, const float* grad_acc, const PreBwdOut& out,
                                        cudaStream_t s);
+// all views of a step in one pass over the Gaussians (preprocess_backward.cu); supported() says whether the fused
+// kernel can take these tensors (else the caller runs the per-view kernel V times, accumulating)
+bool preprocess_backward_views_supported(const GsrGaussiansDev& g, const PreBwdOut& out);
+cudaError_t launch_preprocess_backward_views(int V, const GsrView* views, const int32_t* const* radii,
+                                             const GeomState* geoms, const float* const* grad_accs,
+                                             const GsrGaussiansDev& g, const PreBwdOut& out, cudaStream_t s);
 cudaError_t launch_export_geom(int P, const int32_t* radii, const GeomState& geom, float* depths, float* means2D,
                                float* cov3D, float* conic_opacity, float* rgb, uint8_t* clamped,
                                uint32_t* tiles_touched, uint32_t* point_offsets, cudaStream_t s);

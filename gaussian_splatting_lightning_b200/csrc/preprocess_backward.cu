@@ -400,4 +400,335 @@ cudaError_t launch_preprocess_backward(const GsrView& v, const GsrGaussiansDev& 
   return cudaGetLastError();
 }
 
+
+// ---- all views of a step in ONE pass over the Gaussians -------------------------------------------------------------
+// A training step renders V views and sums their gradients.  Run view by view, the kernel above reads the Gaussian's
+// inputs (236 B at SH degree 3) and read-modify-writes its 236 B of the step's gradient buffer V times: 8 x 0.143 ms of a
+// 11.4 ms C3 step.  Here every Gaussian is visited ONCE: its inputs and SH block come in once, the V views contribute
+// from their own 48-byte rows of raw pixel sums (+ radius and clamp bits: 53 B per view), the sums over the views are
+// kept in registers (dL/dmean3D, dL/dcov3D, dL/dopacity, the statistics) and in the warp's second shared-memory block
+// (dL/dsh), and the gradient row is written -- or added -- once.  The chain cov3D -> (scale, quaternion) is linear in
+// dL/dcov3D with view-independent factors, so it runs once on the sum.  cov3D itself is recomputed from scale and
+// rotation (the forward's exact expression; a Gaussian culled in one view has no stored copy there).
+// The densification statistics stay PER VIEW quantities (|| dL/dmean2D ||_2 is taken before the views are summed:
+// gaussian_model.py:174-181).  dL/dmean2D itself is a per-view output and is not produced here.
+constexpr int GSR_MAX_FUSED_VIEWS = 16;
+struct ViewSlot {
+  GsrView v;
+  const int32_t* radii;
+  const uint8_t* clamped;
+  const float* grad_acc;
+};
+struct PreBwdViewsArgs {
+  int V;
+  ViewSlot view[GSR_MAX_FUSED_VIEWS];
+  GsrGaussiansDev g;
+  float* dL_dcolors; float* dL_dopacity; float* dL_dmeans3D; float* dL_dcov3D; float* dL_dsh; float* dL_dscales;
+  float* dL_drot;
+  float* max_radii2D; float* xyz_grad_accum; float* xyz_grad_count;
+};
+
+template <int DEG>
+__device__ __forceinline__ void sh_backward_add(const float* __restrict__ sh, float* __restrict__ dsh, bool first,
+                                                float x, float y, float z, const float* g3, float* ddir) {
+  constexpr int N = (DEG + 1) * (DEG + 1);
+  constexpr int NV = (3 * N + 3) / 4;
+  float basis[N], bx[N], by[N], bz[N];
+  sh_basis<DEG>(x, y, z, basis);
+  sh_basis_grad<DEG>(x, y, z, bx, by, bz);
+  ddir[0] = ddir[1] = ddir[2] = 0.f;
+  float out[NV * 4];
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+      out[3 * k + ch] = basis[k] * g3[ch];
+      if (k > 0) {
+        const float s = sh[3 * k + ch] * g3[ch];
+        ddir[0] += bx[k] * s; ddir[1] += by[k] * s; ddir[2] += bz[k] * s;
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 3 * N; k < NV * 4; ++k) out[k] = 0.f;
+  float4* d4 = reinterpret_cast<float4*>(dsh);
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    float4 o = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+    if (!first) { const float4 p = d4[k]; o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w; }
+    d4[k] = o;
+  }
+}
+
+template <bool ACC>
+__global__ void __launch_bounds__(256, 2) preprocess_backward_views_kernel(const __grid_constant__ PreBwdViewsArgs a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ __align__(8) unsigned long long bars[8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int P = a.g.P, M = a.g.M;
+  const int w0 = blockIdx.x * 256 + warp * 32;
+  if (w0 >= P) return;
+  const int i = w0 + lane;
+  const int nrows = min(32, P - w0);
+  // which views see this Gaussian: one bit per view, loaded up front
+  uint32_t seen = 0;
+  int max_radius = 0;
+  if (i < P) {
+    for (int k = 0; k < a.V; ++k) {
+      const int r = a.view[k].radii[i];
+      if (r > 0) { seen |= 1u << k; max_radius = max(max_radius, r); }
+    }
+  }
+  const bool any_visible = __any_sync(0xffffffffu, seen != 0u);
+  if (ACC && !any_visible) return;  // nothing to add anywhere
+
+  const bool want_sh = a.g.shs != nullptr;
+  const uint32_t row_bytes = (uint32_t)M * 12u, blk_bytes = (uint32_t)nrows * row_bytes;
+  float* blk = reinterpret_cast<float*>(smem_raw + (size_t)warp * 32 * row_bytes);                      // SH in
+  float* dblk = reinterpret_cast<float*>(smem_raw + (size_t)(8 + warp) * 32 * row_bytes);               // dL/dsh out
+  const bool bulk_in = want_sh && any_visible;
+  if (bulk_in) {
+    if (lane == 0) {
+      mbar_init(&bars[warp], 1);
+      mbar_arrive_expect_tx(&bars[warp], blk_bytes);
+      bulk_copy_g2s(blk, a.g.shs + (size_t)w0 * M * 3, blk_bytes, &bars[warp]);
+    }
+    __syncwarp();
+  }
+  float dmean[3] = {0.f, 0.f, 0.f}, dS[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, dcol[3] = {0.f, 0.f, 0.f};
+  float dop = 0.f, norm_sum = 0.f, count = 0.f;
+  float* dsh_row = dblk + (size_t)lane * M * 3;
+  const float* sh_row = blk + (size_t)lane * M * 3;
+  bool sh_first = true;
+  float4 q_in = make_float4(1.f, 0.f, 0.f, 0.f);
+  float sc0 = 0.f, sc1 = 0.f, sc2 = 0.f;
+
+  if (seen) {
+    const float px = a.g.means3D[3 * (size_t)i], py = a.g.means3D[3 * (size_t)i + 1], pz = a.g.means3D[3 * (size_t)i + 2];
+    float s6[6];
+    const float mod = a.view[0].v.scale_modifier;
+    if (a.g.cov3D_precomp) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) s6[k] = a.g.cov3D_precomp[6 * (size_t)i + k];
+    } else {
+      q_in = reinterpret_cast<const float4*>(a.g.rotations)[i];
+      sc0 = a.g.scales[3 * (size_t)i]; sc1 = a.g.scales[3 * (size_t)i + 1]; sc2 = a.g.scales[3 * (size_t)i + 2];
+      cov3d_from_scale_rot(sc0, sc1, sc2, mod, q_in, s6);   // the forward's expression (preprocess.cu), bit for bit
+    }
+    const float S[3][3] = {{s6[0], s6[1], s6[2]}, {s6[1], s6[3], s6[4]}, {s6[2], s6[4], s6[5]}};
+    const float opac_in = a.g.opacities[i];
+    bool sh_waited = false;
+    for (int k = 0; k < a.V; ++k) {
+      if (!((seen >> k) & 1u)) continue;
+      const ViewSlot& vs = a.view[k];
+      const float4 g0 = reinterpret_cast<const float4*>(vs.grad_acc)[3 * (size_t)i];      // S0 S1 S2 S3
+      const float4 g1 = reinterpret_cast<const float4*>(vs.grad_acc)[3 * (size_t)i + 1];  // S4 S5 dr dg
+      const float4 g2 = reinterpret_cast<const float4*>(vs.grad_acc)[3 * (size_t)i + 2];  // db dinvz - -
+      const unsigned cl = want_sh ? vs.clamped[i] : 0u;
+      const float* __restrict__ view = vs.v.view;
+      const float* __restrict__ proj = vs.v.proj;
+      const float fx = vs.v.fx, fy = vs.v.fy;
+      JacobianCtx jc;
+      build_jacobian(view, px, py, pz, fx, fy, vs.v.tanfovx, vs.v.tanfovy, jc);
+      const Cov2D c0 = project_cov(s6, jc);
+      const float ca = c0.a + 0.3f, cc = c0.c + 0.3f, cb = c0.b;
+      const float det = fmaf(ca, cc, -(cb * cb));
+      const float det_inv = 1.f / det;
+      const float cA = cc * det_inv, cB = -cb * det_inv, cC = ca * det_inv;
+      const float dmx = -(cA * g0.x + cB * g0.y) * (0.5f * (float)vs.v.W);
+      const float dmy = -(cC * g0.y + cB * g0.x) * (0.5f * (float)vs.v.H);
+      const float dA = -0.5f * g0.z, dB = -g0.w, dC = -0.5f * g1.x;
+      const float d2inv = 1.f / (det * det + 0.0000001f);
+      float da = d2inv * (-cc * cc * dA + cb * cc * dB - cb * cb * dC);
+      float dc = d2inv * (-cb * cb * dA + ca * cb * dB - ca * ca * dC);
+      float db = d2inv * (2.f * cb * cc * dA - (ca * cc + cb * cb) * dB + 2.f * ca * cb * dC);
+      float dop_v = g1.y;
+      if (vs.v.antialiasing) {
+        const float det0 = c0.a * c0.c - c0.b * c0.b;
+        const float ratio = det0 / det;
+        const float h = sqrtf(fmaxf(0.000025f, ratio));
+        const float dL_dop_eff = dop_v;
+        dop_v = dL_dop_eff * h;
+        if (ratio > 0.000025f) {
+          const float dL_dratio = dL_dop_eff * opac_in / (2.f * h);
+          const float inv = 1.f / det, r2 = ratio * inv;
+          da += dL_dratio * (c0.c * inv - r2 * cc);
+          dc += dL_dratio * (c0.a * inv - r2 * ca);
+          db += dL_dratio * (-2.f * cb * inv + r2 * 2.f * cb);
+        }
+      }
+      dop += dop_v;
+      const float* m0 = jc.m0;
+      const float* m1 = jc.m1;
+      dS[0] += m0[0] * m0[0] * da + m0[0] * m1[0] * db + m1[0] * m1[0] * dc;
+      dS[3] += m0[1] * m0[1] * da + m0[1] * m1[1] * db + m1[1] * m1[1] * dc;
+      dS[5] += m0[2] * m0[2] * da + m0[2] * m1[2] * db + m1[2] * m1[2] * dc;
+      dS[1] += 2.f * m0[0] * m0[1] * da + (m0[0] * m1[1] + m0[1] * m1[0]) * db + 2.f * m1[0] * m1[1] * dc;
+      dS[2] += 2.f * m0[0] * m0[2] * da + (m0[0] * m1[2] + m0[2] * m1[0]) * db + 2.f * m1[0] * m1[2] * dc;
+      dS[4] += 2.f * m0[1] * m0[2] * da + (m0[1] * m1[2] + m0[2] * m1[1]) * db + 2.f * m1[1] * m1[2] * dc;
+      float dJ00 = 0.f, dJ02 = 0.f, dJ11 = 0.f, dJ12 = 0.f;
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const float Sm0 = S[r][0] * m0[0] + S[r][1] * m0[1] + S[r][2] * m0[2];
+        const float Sm1 = S[r][0] * m1[0] + S[r][1] * m1[1] + S[r][2] * m1[2];
+        const float dm0 = 2.f * da * Sm0 + db * Sm1;
+        const float dm1 = 2.f * dc * Sm1 + db * Sm0;
+        dJ00 += dm0 * view[4 * r + 0]; dJ02 += dm0 * view[4 * r + 2];
+        dJ11 += dm1 * view[4 * r + 1]; dJ12 += dm1 * view[4 * r + 2];
+      }
+      const float tz = jc.tz, tzi = 1.f / tz, tz2 = tzi * tzi, tz3 = tz2 * tzi;
+      const float dtx = (jc.gate_x ? 1.f : 0.f) * -fx * tz2 * dJ02;
+      const float dty = (jc.gate_y ? 1.f : 0.f) * -fy * tz2 * dJ12;
+      float dtz = -fx * tz2 * dJ00 - fy * tz2 * dJ11 + 2.f * fx * jc.tx * tz3 * dJ02 + 2.f * fy * jc.ty * tz3 * dJ12;
+      dtz -= g2.y * tz2;  // inverse depth
+      float dm[3];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) dm[j] = dtx * view[4 * j + 0] + dty * view[4 * j + 1] + dtz * view[4 * j + 2];
+      {
+        const float hx = xform_col(proj, 0, px, py, pz), hy = xform_col(proj, 1, px, py, pz);
+        const float hw = xform_col(proj, 3, px, py, pz);
+        const float mw = 1.f / (hw + 0.0000001f);
+        const float mul1 = hx * mw * mw, mul2 = hy * mw * mw;
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+          dm[j] += (proj[4 * j + 0] * mw - proj[4 * j + 3] * mul1) * dmx +
+                   (proj[4 * j + 1] * mw - proj[4 * j + 3] * mul2) * dmy;
+      }
+      norm_sum += sqrtf(dmx * dmx + dmy * dmy);   // the view's own norm, before the views are summed
+      count += 1.f;
+      dcol[0] += g1.z; dcol[1] += g1.w; dcol[2] += g2.x;
+      if (want_sh) {
+        if (!sh_waited) { mbar_wait(&bars[warp], 0); sh_waited = true; }
+        const float* __restrict__ cam = vs.v.campos;
+        const float dirx = px - cam[0], diry = py - cam[1], dirz = pz - cam[2];
+        const float len = sqrtf(dirx * dirx + diry * diry + dirz * dirz);
+        const float x = dirx / len, y = diry / len, z = dirz / len;
+        const float g3[3] = {(cl & 1u) ? 0.f : g1.z, (cl & 2u) ? 0.f : g1.w, (cl & 4u) ? 0.f : g2.x};
+        float ddir[3];
+        switch (vs.v.deg) {
+          case 0: sh_backward_add<0>(sh_row, dsh_row, sh_first, x, y, z, g3, ddir); break;
+          case 1: sh_backward_add<1>(sh_row, dsh_row, sh_first, x, y, z, g3, ddir); break;
+          case 2: sh_backward_add<2>(sh_row, dsh_row, sh_first, x, y, z, g3, ddir); break;
+          default: sh_backward_add<3>(sh_row, dsh_row, sh_first, x, y, z, g3, ddir); break;
+        }
+        sh_first = false;
+        const float ng = x * ddir[0] + y * ddir[1] + z * ddir[2];
+        dm[0] += (ddir[0] - x * ng) / len;
+        dm[1] += (ddir[1] - y * ng) / len;
+        dm[2] += (ddir[2] - z * ng) / len;
+      }
+      dmean[0] += dm[0]; dmean[1] += dm[1]; dmean[2] += dm[2];
+    }
+  }
+  // ---- the Gaussian's row of every output, once ------------------------------------------------------------------
+  if (i < P && (seen || !ACC)) {
+    if (a.dL_dopacity) put<ACC>(a.dL_dopacity + i, dop);
+    if (a.dL_dmeans3D)
+      for (int j = 0; j < 3; ++j) put<ACC>(a.dL_dmeans3D + 3 * (size_t)i + j, dmean[j]);
+    if (a.dL_dcolors)
+      for (int j = 0; j < 3; ++j) put<ACC>(a.dL_dcolors + 3 * (size_t)i + j, dcol[j]);
+    if (a.dL_dcov3D)
+      for (int k = 0; k < 6; ++k) put<ACC>(a.dL_dcov3D + 6 * (size_t)i + k, dS[k]);
+    if (seen) {
+      if (a.max_radii2D) atomicMax(reinterpret_cast<int*>(a.max_radii2D + i), __float_as_int((float)max_radius));
+      if (a.xyz_grad_accum) atomicAdd(a.xyz_grad_accum + i, norm_sum);
+      if (a.xyz_grad_count) atomicAdd(a.xyz_grad_count + i, count);
+    }
+    float4 dq = make_float4(0.f, 0.f, 0.f, 0.f);
+    float dsc[3] = {0.f, 0.f, 0.f};
+    if (seen && !a.g.cov3D_precomp && (a.dL_dscales || a.dL_drot)) {
+      const float4 q = q_in;
+      float R[3][3];
+      quat_to_R(q, R);
+      const float mod = a.view[0].v.scale_modifier;
+      const float s[3] = {mod * sc0, mod * sc1, mod * sc2};
+      const float Gm[3][3] = {{dS[0], 0.5f * dS[1], 0.5f * dS[2]},
+                              {0.5f * dS[1], dS[3], 0.5f * dS[4]},
+                              {0.5f * dS[2], 0.5f * dS[4], dS[5]}};
+      float dR[3][3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        float dsk = 0.f;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          const float dLrk = 2.f * (Gm[r][0] * R[0][k] + Gm[r][1] * R[1][k] + Gm[r][2] * R[2][k]) * s[k];
+          dsk += dLrk * R[r][k];
+          dR[r][k] = dLrk * s[k];
+        }
+        dsc[k] = mod * dsk;
+      }
+      const float r = q.x, x = q.y, y = q.z, z = q.w;
+      dq.x = 2.f * (-z * dR[0][1] + y * dR[0][2] + z * dR[1][0] - x * dR[1][2] - y * dR[2][0] + x * dR[2][1]);
+      dq.y = 2.f * (y * dR[0][1] + z * dR[0][2] + y * dR[1][0] - 2.f * x * dR[1][1] - r * dR[1][2] + z * dR[2][0] +
+                    r * dR[2][1] - 2.f * x * dR[2][2]);
+      dq.z = 2.f * (-2.f * y * dR[0][0] + x * dR[0][1] + r * dR[0][2] + x * dR[1][0] + z * dR[1][2] - r * dR[2][0] +
+                    z * dR[2][1] - 2.f * y * dR[2][2]);
+      dq.w = 2.f * (-2.f * z * dR[0][0] - r * dR[0][1] + x * dR[0][2] + r * dR[1][0] - 2.f * z * dR[1][1] +
+                    y * dR[1][2] + x * dR[2][0] + y * dR[2][1]);
+    }
+    if (a.dL_dscales)
+      for (int k = 0; k < 3; ++k) put<ACC>(a.dL_dscales + 3 * (size_t)i + k, dsc[k]);
+    if (a.dL_drot) put4<ACC>(reinterpret_cast<float4*>(a.dL_drot) + i, dq);
+  }
+  // ---- the warp's dL/dsh block: one bulk store / bulk reduction ----------------------------------------------------
+  if (want_sh && a.dL_dsh) {
+    if (sh_first && i < P)   // no view touched this row: it must read as zeros
+      for (int k = 0; k < 3 * M / 4; ++k) reinterpret_cast<float4*>(dsh_row)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (bulk_in) mbar_wait(&bars[warp], 0);  // every lane: the warp must not retire under its in-flight SH copy
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+    if (lane == 0) {
+      float* dst = a.dL_dsh + (size_t)w0 * M * 3;
+      if (ACC) bulk_reduce_add_s2g(dst, dblk, blk_bytes);
+      else bulk_copy_s2g(dst, dblk, blk_bytes);
+      bulk_commit_and_wait_read();
+    }
+  } else if (bulk_in) {
+    mbar_wait(&bars[warp], 0);
+  }
+}
+
+// All views must share sh_degree, scale_modifier and the Gaussian tensors.  Requires the bulk-copy layout (M % 4 == 0,
+// 16-byte aligned shs / dL_dsh); the caller falls back to the per-view kernel otherwise.
+bool preprocess_backward_views_supported(const GsrGaussiansDev& g, const PreBwdOut& o) {
+  if (o.dL_dmeans2D) return false;
+  if (!g.shs) return true;
+  return (g.M % 4) == 0 && (size_t)512 * g.M * 12 <= 200 * 1024 && (reinterpret_cast<uintptr_t>(g.shs) & 15) == 0 &&
+         (!o.dL_dsh || (reinterpret_cast<uintptr_t>(o.dL_dsh) & 15) == 0);
+}
+
+cudaError_t launch_preprocess_backward_views(int V, const GsrView* views, const int32_t* const* radii,
+                                             const GeomState* geoms, const float* const* grad_accs,
+                                             const GsrGaussiansDev& g, const PreBwdOut& o, cudaStream_t s) {
+  if (g.P <= 0 || V <= 0) return cudaSuccess;
+  PreBwdOut out = o;
+  for (int v0 = 0; v0 < V; v0 += GSR_MAX_FUSED_VIEWS) {
+    PreBwdViewsArgs a;
+    a.V = min(GSR_MAX_FUSED_VIEWS, V - v0);
+    for (int k = 0; k < a.V; ++k) {
+      a.view[k].v = views[v0 + k];
+      a.view[k].radii = radii[v0 + k];
+      a.view[k].clamped = geoms[v0 + k].clamped;
+      a.view[k].grad_acc = grad_accs[v0 + k];
+    }
+    a.g = g;
+    a.dL_dcolors = out.dL_dcolors; a.dL_dopacity = out.dL_dopacity; a.dL_dmeans3D = out.dL_dmeans3D;
+    a.dL_dcov3D = out.dL_dcov3D; a.dL_dsh = g.shs ? out.dL_dsh : nullptr; a.dL_dscales = out.dL_dscales;
+    a.dL_drot = out.dL_drot;
+    a.max_radii2D = out.max_radii2D; a.xyz_grad_accum = out.xyz_grad_accum; a.xyz_grad_count = out.xyz_grad_count;
+    const size_t smem = g.shs ? (size_t)512 * g.M * 12 : 0;   // SH block in + dL/dsh block out, 8 warps each
+    auto kern = out.accumulate ? preprocess_backward_views_kernel<true> : preprocess_backward_views_kernel<false>;
+    if (smem > 48 * 1024 - 256) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      if (e != cudaSuccess) return e;
+    }
+    kern<<<(g.P + 255) / 256, 256, smem, s>>>(a);
+    count_launch();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    out.accumulate = 1;   // further groups of views add to the first
+  }
+  return cudaSuccess;
+}
+
 }  // namespace gsr

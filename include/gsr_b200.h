@@ -102,6 +102,9 @@ typedef struct GsrGrads {
 #define GSR_GRADS_ACCUMULATE 1 /* outputs are += (several views into one gradient buffer, the layout the
                                   view-parallel all-reduce sends); rows of culled Gaussians are not touched */
 
+#define GSR_BWD_RENDER_ONLY 2   /* stop after the compositing backward: `scratch` then holds the view's raw pixel sums
+                                  (P,12) for gsr_preprocess_backward_views; grads may be NULL, nothing else is written */
+
 /* Densification statistics of one view, fused into the backward so that the per-view norm is
  * taken BEFORE gradients of several views are summed.  Mirrors
  * GaussianModel.update_max_radii2D / update_xyz_gradient (gs_lightning/modules/gaussian_model.py:174-181)
@@ -166,6 +169,23 @@ int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, con
                  const float* dL_dcolor, const float* dL_dinvdepth, const void* geom,
                  const void* binning, const void* img, int64_t num_rendered, void* scratch,
                  const GsrGrads* grads, int32_t flags, const GsrDensifyStats* stats, void* stream);
+
+/* The preprocess backward of ALL views of a training step in one pass over the Gaussians (the reference trains one view
+ * per step, gs_lightning_module.py:139-140; the view-parallel step of SURVEY.md 8(e) sums V views per rank).  Each view
+ * was rendered by gsr_forward and taken through gsr_backward(..., GSR_BWD_RENDER_ONLY): its settings, radii, geometry
+ * buffer and scratch are handed over here.  The Gaussian's inputs are read once, its gradient row written (or, with
+ * GSR_GRADS_ACCUMULATE, added) once; the densification statistics stay per-view quantities (the norm of dL_dmeans2D is
+ * taken per view before the sum).  grads->dL_dmeans2D must be NULL (a per-view output).  All views must share
+ * sh_degree, scale_modifier and antialiasing.  Results equal the sum of per-view gsr_backward calls up to float
+ * summation order. */
+typedef struct GsrViewState {
+  const GsrSettings* settings;
+  const int32_t* radii;   /* device (P)                                              */
+  const void* geom;       /* the view's geometry buffer (gsr_forward)                */
+  const void* scratch;    /* the view's (P,12) raw sums (gsr_backward RENDER_ONLY)    */
+} GsrViewState;
+int gsr_preprocess_backward_views(const GsrViewState* views, int32_t num_views, const GsrGaussians* gaussians,
+                                  const GsrGrads* grads, int32_t flags, const GsrDensifyStats* stats, void* stream);
 
 /* present[i] = ([p_i,1] @ viewmatrix).z > 0.2   (camera_tools.py:5-8). */
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, uint8_t* present,
