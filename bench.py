@@ -50,6 +50,8 @@ def parse_args():
                     help="which of the step's N*views-per-rank views a rank owns (see view_index)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--per-view-backward", action="store_true",
+                    help="run every view's preprocess backward on its own (default: one fused pass per step over all views)")
     ap.add_argument("--no-extras", action="store_true",
                     help="skip the secondary blocks (single view per step, C1, C4 strong scaling, C5 render only)")
     return ap.parse_args()
@@ -224,7 +226,7 @@ NCU_COUNTS = os.path.join(ROOT, "profiles", "ncu_counts.json")   # per-launch co
 class Rig:
     """One workload on one rank: replicated scene, this rank's cameras, step buffers, view streams."""
 
-    def __init__(self, workload, vpr, streams, device, rank, world, partition, seed_grad=1234):
+    def __init__(self, workload, vpr, streams, device, rank, world, partition, seed_grad=1234, fused=True):
         from gaussian_splatting_lightning_b200.view_parallel import StepBuffers, ViewStreams
         self.workload, self.vpr, self.world, self.rank, self.device = workload, vpr, world, rank, device
         self.P, self.deg, self.W, self.H = synthetic.config(workload)
@@ -243,14 +245,22 @@ class Rig:
         self.acc_into, self.stat_into = self.bufs.grads(), self.bufs.densify_stats()
         self.n_streams = streams
         self.steps_done = 0
+        self.fused, self.states = fused, []
         self.vstreams = ViewStreams(device, streams)   # independent views of a step round-robin over CUDA streams
 
     def one_view(self, c, fwd_only=False):
-        from gaussian_splatting_lightning_b200.rasterizer import backward_raw, forward_raw
+        from gaussian_splatting_lightning_b200.rasterizer import backward_raw, backward_render_only, forward_raw
         rs, sc = c["settings"], self.scene
         R, color, radii, geom, binning, img, invd, cap = forward_raw(
             rs, sc["means3D"], sc["shs"], None, sc["opacities"], sc["scales"], sc["rotations"], None)
         if fwd_only:
+            return color
+        if self.fused:
+            # the compositing backward of the view; its preprocess backward runs with the other views' in ONE pass
+            # over the Gaussians at the end of the step (rasterizer.preprocess_backward_views)
+            scratch = backward_render_only(rs, sc["means3D"], radii, sc["shs"], None, sc["opacities"], sc["scales"],
+                                           sc["rotations"], None, self.dL_dcolor, self.dL_dinv, geom, binning, img, R)
+            self.states.append((rs, radii, geom, scratch))
             return color
         # gradients += into the flat all-reduce buffer and the view's densification statistics
         # (gaussian_model.py:174-181), both fused into the preprocess backward kernel
@@ -264,7 +274,17 @@ class Rig:
             # per-step buffers: gradient sum and statistics DELTAS of this step's views; the radii candidates stay
             # (max commutes with the steps: their exchange is deferred to densification time, StepBuffers.all_reduce)
             self.bufs.zero_(keep_max_radii=self.world > 1)
+        self.states = []
         self.vstreams.run(len(self.cams), lambda j: self.one_view(self.cams[j], fwd_only))
+        if self.fused and not fwd_only:
+            from gaussian_splatting_lightning_b200.rasterizer import preprocess_backward_views
+            sc, cur = self.scene, torch.cuda.current_stream(self.device)
+            for _rs, radii, geom, scratch in self.states:      # allocated under the view streams' pools, read here
+                for t in (radii, geom, scratch):
+                    t.record_stream(cur)
+            preprocess_backward_views(self.states, sc["means3D"], sc["shs"], None, sc["opacities"], sc["scales"],
+                                      sc["rotations"], None, accumulate_into=self.acc_into, stats=self.stat_into)
+            self.states = []
         if self.world > 1 and not fwd_only:
             self.bufs.all_reduce(max_radii=False)   # sum(flat + stats): ONE collective per step
             self.steps_done += 1
@@ -367,6 +387,8 @@ class E2E:
                            ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(self.n_slots)]
         self.loss_fns = {"l1": l1_loss, "full": lambda c_, g_: photometric_loss(c_[None], g_[None], 0.2)[0]}
         self.loss_kind = "l1"
+        from gaussian_splatting_lightning_b200.rasterizer import StepSink
+        self.sink = StepSink(rig.acc_into, rig.stat_into)
         self.h2d_bytes_per_step = vpr * (3 * H * W * 4 + 38 * 4)
         self.d2h_bytes_per_step = vpr * 4
 
@@ -390,11 +412,21 @@ class E2E:
         cam_d, gt = sl["cam"], sl["gt"]
         rs = rig.cams[j]["settings"]._replace(viewmatrix=cam_d[0:16].view(4, 4), projmatrix=cam_d[16:32].view(4, 4),
                                               campos=cam_d[32:35], bg=cam_d[35:38])
-        sp = torch.zeros_like(p["means3D"], requires_grad=True)
-        with accumulate_gradients_into(rig.acc_into, rig.stat_into):
-            color, radii, invd = GaussianRasterizer(rs)(
-                means3D=p["means3D"], means2D=sp, shs=p["shs"], colors_precomp=None, opacities=p["opacities"],
-                scales=p["scales"], rotations=p["rotations"], cov3D_precomp=None)
+        if rig.fused:
+            # StepSink: the view's backward runs the compositing backward and parks the view; the preprocess backward
+            # of all views is ONE pass at the end of the step.  No dummy screen-space leaf: it exists in the reference
+            # (gs_lightning_module.py:316-317) to carry dL_dmeans2D to the densification statistics, which the fused
+            # pass produces itself.
+            with self.sink:
+                color, radii, invd = GaussianRasterizer(rs)(
+                    means3D=p["means3D"], means2D=None, shs=p["shs"], colors_precomp=None, opacities=p["opacities"],
+                    scales=p["scales"], rotations=p["rotations"], cov3D_precomp=None)
+        else:
+            sp = torch.zeros_like(p["means3D"], requires_grad=True)
+            with accumulate_gradients_into(rig.acc_into, rig.stat_into):
+                color, radii, invd = GaussianRasterizer(rs)(
+                    means3D=p["means3D"], means2D=sp, shs=p["shs"], colors_precomp=None, opacities=p["opacities"],
+                    scales=p["scales"], rotations=p["rotations"], cov3D_precomp=None)
         loss = self.loss_fns[self.loss_kind](color, gt)
         loss.backward()
         self.loss_host[j].copy_(loss.detach(), non_blocking=True)
@@ -407,6 +439,8 @@ class E2E:
         for j in range(min(self.n_slots - 1, rig.vpr)):
             self.upload(j)
         rig.vstreams.run(rig.vpr, self.view)
+        if rig.fused:
+            self.sink.flush()
         if rig.world > 1:
             rig.bufs.all_reduce(max_radii=False)
         main.synchronize()                               # the step's result (losses) is on the host
@@ -509,7 +543,7 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
     vpr = args.views_per_rank
-    rig = Rig(args.workload, vpr, args.streams, device, rank, world, args.partition)
+    rig = Rig(args.workload, vpr, args.streams, device, rank, world, args.partition, fused=not args.per_view_backward)
     P, deg, W, H, M = rig.P, rig.deg, rig.W, rig.H, rig.M
     counters = workload_counters(rig)
     K, Wm = args.steps, max(args.warmup, 3)
@@ -641,9 +675,16 @@ def headline(args, rig, counters, prof, clocks, value, fwd_value, ms_total, ms_f
     v0 = counters["view0"]
     visit_scale = ((counters["visits_both"] + counters["visits_single"]) / max(1.0, v0["visits_both"] + v0["visits_single"]))
     stages, stage_sum = [], 0.0
+    if rig.fused:
+        # one fused pass per STEP over all views: inputs in once (44 + 12 M), the gradient row + statistics out once
+        # (44 + 12 M + 12), per view the radius of every Gaussian (4) and 49 B per visible one (raw sums 48, clamp bits 1);
+        # reported per frame (1 / views_per_rank of the pass)
+        model["preprocess_backward"] = dict(bytes=(P * (2 * (44 + 12 * M) + 12)) / vpr + 4 * P + 49 * counters["Pvis"])
     for name, (tot_ms, calls) in prof.items():
         if calls == 0:
             continue
+        if rig.fused and name == "preprocess_backward":
+            calls *= vpr          # per-frame share of the per-step pass
         avg_ms = tot_ms / calls
         stage_sum += tot_ms
         m = model[name]
@@ -711,6 +752,7 @@ def headline(args, rig, counters, prof, clocks, value, fwd_value, ms_total, ms_f
                    "views_per_rank": vpr, "frames_per_step": vpr * world, "streams_per_rank": args.streams,
                    "parallelism": f"view-parallel x{world}", "partition": args.partition,
                    "ffi": ffi_name(),
+                   "preprocess_backward": "one fused pass per step over all views" if rig.fused else "per view",
                    "l2": (lambda mb: f"inputs ({mb:.0f} MB of Gaussian parameters + {48 * P / 1e6:.0f} MB records) "
                           + ("exceed the 126 MB L2; no flush" if mb > 126 else
                              "fit the 126 MB L2: a parity-test size, not a bench line"))((44 + 12 * M) * P / 1e6),

@@ -253,6 +253,114 @@ std::tuple<Tensor, Tensor, Tensor, Tensor, Tensor, Tensor, Tensor, Tensor> raste
   return {*g[0], *g[1], *g[2], *g[3], *g[4], *g[5], *g[6], *g[7]};
 }
 
+// The compositing backward alone (gsr_backward with GSR_BWD_RENDER_ONLY): returns the view's (P,12) raw pixel sums for
+// preprocess_backward_views.
+Tensor render_backward_only(
+    const Tensor& bg, const Tensor& means3D, const Tensor& radii, const OptTensor& colors, const Tensor& opacities,
+    const OptTensor& scales, const OptTensor& rotations, double scale_modifier, const OptTensor& cov3D,
+    const Tensor& viewmatrix, const Tensor& projmatrix, double tanfovx, double tanfovy, const OptTensor& dL_dout_color,
+    const OptTensor& dL_dout_invdepth, const OptTensor& sh, int64_t degree, const Tensor& campos, const Tensor& geomBuffer,
+    int64_t R, const Tensor& binningBuffer, const Tensor& imageBuffer, bool antialiasing, bool debug) {
+  int64_t H = 0, W = 0;
+  if (present(dL_dout_color)) { H = dL_dout_color->size(-2); W = dL_dout_color->size(-1); }
+  else if (present(dL_dout_invdepth)) { H = dL_dout_invdepth->size(-2); W = dL_dout_invdepth->size(-1); }
+  TORCH_CHECK(H > 0 && W > 0, "backward: one of dL_dout_color / dL_dout_invdepth must be given");
+  Frame fr(means3D, sh, colors, opacities, scales, rotations, cov3D, bg, viewmatrix, projmatrix, campos, tanfovx,
+           tanfovy, H, W, scale_modifier, degree, false, antialiasing, debug);
+  const c10::cuda::CUDAGuard guard(fr.dev);
+  auto fopt = torch::TensorOptions().dtype(torch::kFloat32).device(fr.dev);
+  const int64_t P = fr.g.P;
+  Tensor scratch = torch::empty({(int64_t)gsr_backward_scratch_bytes((int32_t)P)}, fopt.dtype(torch::kUInt8));
+  if (P == 0) return scratch;
+  Tensor dC = f32c(dL_dout_color, fr.dev);
+  if (!dC.defined()) dC = torch::zeros({3, H, W}, fopt);
+  Tensor dD = f32c(dL_dout_invdepth, fr.dev);
+  Tensor radii_c = radii.contiguous();
+  cudaStream_t stream = at::cuda::getCurrentCUDAStream(fr.dev.index()).stream();
+  check(gsr_backward(&fr.st, &fr.g, radii_c.data_ptr<int32_t>(), dC.data_ptr<float>(), fp(dD), geomBuffer.data_ptr(),
+                     binningBuffer.defined() && binningBuffer.numel() ? binningBuffer.data_ptr() : nullptr,
+                     imageBuffer.data_ptr(), R, scratch.data_ptr(), nullptr, GSR_BWD_RENDER_ONLY, nullptr, (void*)stream),
+        "gsr_backward");
+  return scratch;
+}
+
+// One view of a step for preprocess_backward_views:
+// (bg, viewmatrix, projmatrix, tanfovx, tanfovy, image_height, image_width, campos, radii, geomBuffer, scratch)
+using ViewTuple = std::tuple<Tensor, Tensor, Tensor, double, double, int64_t, int64_t, Tensor, Tensor, Tensor, Tensor>;
+
+// gsr_preprocess_backward_views: the preprocess backward of all views of a step in one pass over the Gaussians.
+// Returns the 8-tuple layout of the backward (dL_dmeans2D is a per-view output and always None here).
+std::vector<OptTensor> preprocess_backward_views(
+    const std::vector<ViewTuple>& views, const Tensor& means3D, const OptTensor& colors, const Tensor& opacities,
+    const OptTensor& scales, const OptTensor& rotations, double scale_modifier, const OptTensor& cov3D, const OptTensor& sh,
+    int64_t degree, bool antialiasing, bool debug, int64_t want_mask, const std::vector<OptTensor>& accumulate_into,
+    const std::vector<OptTensor>& stats) {
+  TORCH_CHECK(!views.empty(), "preprocess_backward_views: no views");
+  const c10::Device dev = means3D.device();
+  std::vector<Frame> frames;   // keeps every view's device-side settings alive over the call
+  frames.reserve(views.size());
+  std::vector<Tensor> keep;
+  std::vector<GsrViewState> vs(views.size());
+  for (size_t k = 0; k < views.size(); ++k) {
+    const auto& [bg, view, proj, tfx, tfy, H, W, campos, radii, geom, scratch] = views[k];
+    frames.emplace_back(means3D, sh, colors, opacities, scales, rotations, cov3D, bg, view, proj, campos, tfx, tfy, H, W,
+                        scale_modifier, degree, false, antialiasing, debug);
+    keep.push_back(radii.contiguous());
+  }
+  for (size_t k = 0; k < views.size(); ++k) {
+    vs[k].settings = &frames[k].st;
+    vs[k].radii = keep[k].data_ptr<int32_t>();
+    vs[k].geom = std::get<9>(views[k]).data_ptr();
+    vs[k].scratch = std::get<10>(views[k]).data_ptr();
+  }
+  const Frame& fr = frames[0];
+  const c10::cuda::CUDAGuard guard(dev);
+  const int64_t P = fr.g.P, M = fr.g.M;
+  auto fopt = torch::TensorOptions().dtype(torch::kFloat32).device(dev);
+  const std::array<std::vector<int64_t>, NUM_GRADS> shapes = {{{P, 3}, {P, 3}, {P, 1}, {P, 3}, {P, 6}, {P, M, 3}, {P, 3}, {P, 4}}};
+  std::vector<OptTensor> out(NUM_GRADS);
+  const bool acc = !accumulate_into.empty();
+  if (acc) {
+    TORCH_CHECK((int)accumulate_into.size() == NUM_GRADS, "accumulate_into must hold 8 entries");
+    for (int i = 1; i < NUM_GRADS; ++i) {
+      if (!accumulate_into[i].has_value() || !accumulate_into[i]->defined()) continue;
+      const Tensor& t = *accumulate_into[i];
+      int64_t n = 1;
+      for (auto d : shapes[i]) n *= d;
+      TORCH_CHECK(t.is_cuda() && t.scalar_type() == torch::kFloat32 && t.is_contiguous() && t.numel() == n,
+                  "accumulate_into[", i, "] must be a contiguous float32 CUDA tensor of ", n, " elements");
+      out[i] = t;
+    }
+  } else {
+    for (int i = 1; i < NUM_GRADS; ++i)
+      if (want_mask & (1ll << i)) out[i] = torch::empty(shapes[i], fopt);
+  }
+  if (P == 0) return out;
+  GsrGrads gr;
+  float** slots[NUM_GRADS] = {&gr.dL_dmeans2D, &gr.dL_dcolors, &gr.dL_dopacity, &gr.dL_dmeans3D, &gr.dL_dcov3D, &gr.dL_dsh,
+                              &gr.dL_dscales, &gr.dL_drotations};
+  for (int i = 0; i < NUM_GRADS; ++i) *slots[i] = out[i].has_value() ? fpm(*out[i]) : nullptr;
+  GsrDensifyStats ds{nullptr, nullptr, nullptr};
+  bool have_stats = false;
+  if (!stats.empty()) {
+    TORCH_CHECK(stats.size() == 3, "stats must hold 3 entries");
+    float** sp[3] = {&ds.max_radii2D, &ds.xyz_grad_accum, &ds.xyz_grad_count};
+    for (int i = 0; i < 3; ++i) {
+      if (!stats[i].has_value() || !stats[i]->defined()) continue;
+      const Tensor& t = *stats[i];
+      TORCH_CHECK(t.is_cuda() && t.scalar_type() == torch::kFloat32 && t.is_contiguous() && t.numel() == P,
+                  "stats[", i, "] must be a contiguous float32 CUDA tensor of ", P, " elements");
+      *sp[i] = t.data_ptr<float>();
+      have_stats = true;
+    }
+  }
+  cudaStream_t stream = at::cuda::getCurrentCUDAStream(dev.index()).stream();
+  check(gsr_preprocess_backward_views(vs.data(), (int32_t)vs.size(), &fr.g, &gr, acc ? GSR_GRADS_ACCUMULATE : 0,
+                                      have_stats ? &ds : nullptr, (void*)stream),
+        "gsr_preprocess_backward_views");
+  return out;
+}
+
 Tensor mark_visible(const Tensor& means3D, const Tensor& viewmatrix, const OptTensor& /*projmatrix*/) {
   TORCH_CHECK(means3D.is_cuda(), "mark_visible runs on CUDA devices only (no CPU fallback)");
   const c10::Device dev = means3D.device();
@@ -278,5 +386,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         pybind11::arg("projmatrix") = pybind11::none());
   m.def("rasterize_gaussians_ex", &rasterize_gaussians_ex);
   m.def("rasterize_gaussians_backward_ex", &rasterize_gaussians_backward_ex);
+  m.def("render_backward_only", &render_backward_only);
+  m.def("preprocess_backward_views", &preprocess_backward_views);
   m.def("version", [] { return std::string(gsr_version()); });
 }

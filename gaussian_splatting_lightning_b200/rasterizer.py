@@ -232,6 +232,97 @@ def backward_raw(rs: GaussianRasterizationSettings, means3D, radii, sh, colors_p
     return tuple(g.values())
 
 
+def backward_render_only(rs: GaussianRasterizationSettings, means3D, radii, sh, colors_precomp, opacities, scales,
+                         rotations, cov3Ds_precomp, dL_dcolor, dL_dinvdepth, geomBuffer, binningBuffer, imgBuffer,
+                         num_rendered: int) -> torch.Tensor:
+    """The compositing backward of one view alone (gsr_backward with GSR_BWD_RENDER_ONLY).  Returns the view's scratch
+    buffer -- (P,12) raw pixel sums per Gaussian -- to hand to preprocess_backward_views together with the view's
+    settings, radii and geometry buffer."""
+    ext = N.ext()
+    if dL_dcolor is None and dL_dinvdepth is None:
+        dL_dcolor = torch.zeros((3, int(rs.image_height), int(rs.image_width)), dtype=torch.float32, device=means3D.device)
+    if ext is not None:
+        try:
+            return ext.render_backward_only(
+                rs.bg, means3D, radii, colors_precomp, opacities, scales, rotations, float(rs.scale_modifier),
+                cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, float(rs.tanfovx), float(rs.tanfovy), dL_dcolor,
+                dL_dinvdepth, sh, int(rs.sh_degree), rs.campos, geomBuffer, int(num_rendered), binningBuffer, imgBuffer,
+                bool(rs.antialiasing), bool(rs.debug))
+        except RuntimeError as e:
+            if "gsr_" in str(e):
+                raise N.GsrError(str(e)) from None
+            raise
+    fr = _Frame(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
+    dev, P = fr.device, fr.P
+    with torch.cuda.device(dev):
+        scratch = torch.empty(N.lib().gsr_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
+        if P == 0:
+            return scratch
+        dC = N.f32c(dL_dcolor, dev)
+        if dC is None:
+            dC = torch.zeros((3, fr.H, fr.W), dtype=torch.float32, device=dev)
+        dD = N.f32c(dL_dinvdepth, dev)
+        N.check(N.lib().gsr_backward(C.byref(fr.settings), C.byref(fr.gaussians), N.ptr(radii), N.ptr(dC), N.ptr(dD),
+                                     N.ptr(geomBuffer), N.ptr(binningBuffer), N.ptr(imgBuffer), int(num_rendered),
+                                     N.ptr(scratch), None, N.GSR_BWD_RENDER_ONLY, None, N.stream_ptr(dev)), "gsr_backward")
+    return scratch
+
+
+def preprocess_backward_views(views, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                              want=None, accumulate_into=None, stats=None):
+    """gsr_preprocess_backward_views: the preprocess backward of ALL views of a training step in one pass over the
+    Gaussians.  views: sequence of (raster_settings, radii, geomBuffer, scratch), scratch from backward_render_only.
+    Returns the 8-tuple of backward_raw with dL_dmeans2D = None (a per-view output); `want`, `accumulate_into` and
+    `stats` as in backward_raw.  The result equals the sum of per-view backward_raw calls up to float summation order;
+    the densification statistics are the per-view ones (norm taken per view, then summed)."""
+    views = list(views)
+    if not views:
+        raise ValueError("preprocess_backward_views: no views")
+    rs0 = views[0][0]
+    ext = N.ext()
+    if accumulate_into is not None:
+        acc = [None if n == "dL_dmeans2D" else accumulate_into.get(n) for n in _GRAD_NAMES]
+        mask = 0
+    else:
+        names = tuple(n for n in (_GRAD_NAMES if want is None else want) if n != "dL_dmeans2D")
+        acc, mask = [], sum(1 << i for i, n in enumerate(_GRAD_NAMES) if n in names)
+    st = [stats.get("max_radii2D"), stats.get("xyz_grad_accum"), stats.get("xyz_grad_count")] if stats else []
+    if ext is not None:
+        vt = [(rs.bg, rs.viewmatrix, rs.projmatrix, float(rs.tanfovx), float(rs.tanfovy), int(rs.image_height),
+               int(rs.image_width), rs.campos, radii, geom, scratch) for rs, radii, geom, scratch in views]
+        try:
+            return tuple(ext.preprocess_backward_views(
+                vt, means3D, colors_precomp, opacities, scales, rotations, float(rs0.scale_modifier), cov3Ds_precomp, sh,
+                int(rs0.sh_degree), bool(rs0.antialiasing), bool(rs0.debug), mask, acc, st))
+        except RuntimeError as e:
+            if "gsr_" in str(e):
+                raise N.GsrError(str(e)) from None
+            raise
+    frames = [_Frame(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp) for rs, *_ in views]
+    fr = frames[0]
+    dev, P, M = fr.device, fr.P, fr.M
+    shapes = dict(dL_dmeans2D=(P, 3), dL_dcolors=(P, 3), dL_dopacity=(P, 1), dL_dmeans3D=(P, 3), dL_dcov3D=(P, 6),
+                  dL_dsh=(P, M, 3), dL_dscales=(P, 3), dL_drotations=(P, 4))
+    with torch.cuda.device(dev):
+        if accumulate_into is not None:
+            g = dict(zip(_GRAD_NAMES, acc))
+        else:
+            g = {n: (torch.empty(shapes[n], dtype=torch.float32, device=dev) if mask >> i & 1 else None)
+                 for i, n in enumerate(_GRAD_NAMES)}
+        if P == 0:
+            return tuple(g.values())
+        arr = (N.GsrViewState * len(views))(*[
+            N.GsrViewState(C.pointer(f.settings), N.ptr(radii), N.ptr(geom), N.ptr(scratch))
+            for f, (_rs, radii, geom, scratch) in zip(frames, views)])
+        grads = N.GsrGrads(*[N.ptr(t) for t in g.values()])
+        ds = N.GsrDensifyStats(*[N.ptr(t) for t in st]) if st else None
+        N.check(N.lib().gsr_preprocess_backward_views(arr, len(views), C.byref(fr.gaussians), C.byref(grads),
+                                                      N.GSR_GRADS_ACCUMULATE if accumulate_into is not None else 0,
+                                                      C.byref(ds) if ds is not None else None, N.stream_ptr(dev)),
+                "gsr_preprocess_backward_views")
+    return tuple(g.values())
+
+
 def mark_visible(positions: torch.Tensor, viewmatrix: torch.Tensor, projmatrix: torch.Tensor = None) -> torch.Tensor:
     """_C.mark_visible (tests/rasterizer_python/test_mark_visible.py:13-14)."""
     if not positions.is_cuda:
@@ -254,6 +345,51 @@ def mark_visible(positions: torch.Tensor, viewmatrix: torch.Tensor, projmatrix: 
 class _Sink(threading.local):
     grads = None
     stats = None
+    step = None      # a StepSink: views of a step whose preprocess backward is deferred to ONE fused pass
+
+
+class StepSink:
+    """Collects the views of one training step for the fused preprocess backward (preprocess_backward_views).
+
+        sink = StepSink(buffers.grads(), buffers.densify_stats())
+        for view in views:
+            with sink:                                    # = accumulate_gradients_into(...) with deferral
+                color, radii, depth = rasterizer(...)     # parameters are LEAF tensors, means2D=None
+            loss(color).backward()                        # runs the compositing backward only, parks the view here
+        sink.flush()                                      # ONE pass over the Gaussians for all parked views
+
+    A view is parked only if every gradient autograd wants from it is covered by the sink (leaf inputs, no dL_dmeans2D
+    request: the dummy screen-space leaf of gs_lightning_module.py:316-317 exists for the densification statistics, which
+    the fused pass produces itself); any other view takes the per-view path at once, adding into the same tensors."""
+
+    def __init__(self, grads, stats=None):
+        self.grads, self.stats = dict(grads), (dict(stats) if stats else None)
+        self.pending = []        # (rs, radii, geom, scratch)
+        self.inputs = None       # (means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp)
+        self._prev = None
+
+    def __enter__(self):
+        self._prev = (_sink.grads, _sink.stats, _sink.step)
+        _sink.grads, _sink.stats, _sink.step = self.grads, self.stats, self
+        return self
+
+    def __exit__(self, *exc):
+        _sink.grads, _sink.stats, _sink.step = self._prev
+        return False
+
+    def flush(self):
+        """Run the fused preprocess backward over the parked views (on the current stream) and forget them."""
+        if not self.pending:
+            return
+        views, self.pending = self.pending, []
+        means3D, sh, colors, opac, scales, rot, cov = self.inputs
+        cur = torch.cuda.current_stream(means3D.device)
+        for _rs, radii, geom, scratch in views:      # possibly allocated under other streams' pools
+            for t in (radii, geom, scratch):
+                t.record_stream(cur)
+        preprocess_backward_views(views, means3D, sh, colors, opac, scales, rot, cov,
+                                  accumulate_into={n: t for n, t in self.grads.items() if n != "dL_dmeans2D"},
+                                  stats=self.stats)
 
 
 _sink = _Sink()
@@ -291,6 +427,7 @@ class _RasterizeGaussians(torch.autograd.Function):
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                 raster_settings):
         ctx.sink = (_sink.grads, _sink.stats) if _sink.grads is not None else None
+        ctx.step_sink = _sink.step
         # The sink may take over the gradient of an input only when that input is a LEAF: for an activation
         # (the reference passes exp(_scaling), sigmoid(_opacity), normalize(_rotation), cat(dc, rest):
         # gs_lightning_module.py:337-348) autograd has to receive the gradient to carry it on to the parameters.
@@ -326,6 +463,21 @@ class _RasterizeGaussians(torch.autograd.Function):
             # (into a zeroed tensor, since the accumulate flag covers the whole call).
             sink_grads, sink_stats = ctx.sink
             P, M = means3D.shape[0], (sh.shape[1] if has_sh else 0)
+            step = ctx.step_sink
+            if step is not None and all(n in sink_grads and n != "dL_dmeans2D" and ctx.leaf[_SINK_INPUT[n]] for n in want):
+                # park the view: compositing backward now, its preprocess backward in the step's ONE fused pass
+                nz = lambda t, ok: t if ok else None
+                inputs = (means3D, nz(sh, has_sh), nz(colors_precomp, has_col), opacities, nz(scales, has_scale),
+                          nz(rotations, has_rot), nz(cov3Ds_precomp, has_cov))
+                if step.inputs is None or not step.pending:
+                    step.inputs = inputs
+                same = lambda a, b: (a is None and b is None) or (a is not None and b is not None and
+                                                               a.data_ptr() == b.data_ptr() and a.shape == b.shape)
+                if all(same(a, b) for a, b in zip(step.inputs, inputs)):
+                    scratch = backward_render_only(ctx.raster_settings, *inputs[:1], radii, *inputs[1:], grad_out_color,
+                                                   grad_out_depth, geomBuffer, binningBuffer, imgBuffer, ctx.num_rendered)
+                    step.pending.append((ctx.raster_settings, radii, geomBuffer, scratch))
+                    return (None,) * 9
             shapes = dict(dL_dmeans2D=(P, 3), dL_dcolors=(P, 3), dL_dopacity=(P, 1), dL_dmeans3D=(P, 3),
                           dL_dcov3D=(P, 6), dL_dsh=(P, M, 3), dL_dscales=(P, 3), dL_drotations=(P, 4))
             acc, fresh = {}, {}

@@ -153,22 +153,33 @@ class ViewStreams:
             join = torch.cuda.Event()
             join.record(st)
             main.wait_event(join)
+        # what fn returned was allocated under the side streams' pools and is consumed on `main` from here on: tell
+        # the caching allocator, or a block freed while main-stream work still reads it could be reissued to a side stream
+        for k, o in enumerate(out):
+            if k % n:
+                for t in (o if isinstance(o, (list, tuple)) else (o,)):
+                    if isinstance(t, torch.Tensor) and t.is_cuda:
+                        t.record_stream(main)
         return out
 
 
 def render_step(settings_per_view: Sequence, scene: Dict[str, torch.Tensor], dL_dcolor, dL_dinvdepth,
                 buffers: StepBuffers, group=None, exchange: bool = True,
-                streams: Optional[ViewStreams] = None) -> List[torch.Tensor]:
+                streams: Optional[ViewStreams] = None, fused: bool = True) -> List[torch.Tensor]:
     """Forward + backward of this rank's views into `buffers`, then the exchange.
 
     settings_per_view: GaussianRasterizationSettings of the views this rank owns;
     dL_dcolor / dL_dinvdepth: callables view_index, color, invdepth -> gradient tensors (or fixed tensors).
     streams: spread the views over CUDA streams (ViewStreams); None = the current stream only.
+    fused (default): every view runs forward + the compositing backward; the preprocess backward of ALL views then
+    runs as one pass over the Gaussians (rasterizer.preprocess_backward_views: inputs read once, the step's gradient row
+    written once).  fused=False: view by view, each view's preprocess backward adding into the buffers.
     Returns the rendered colour images.
     """
-    from .rasterizer import backward_raw, forward_raw
+    from .rasterizer import backward_raw, backward_render_only, forward_raw, preprocess_backward_views
     buffers.zero_()
     grads, stats = buffers.grads(), buffers.densify_stats()
+    states = [None] * len(settings_per_view)
 
     def one_view(k):
         rs = settings_per_view[k]
@@ -176,14 +187,27 @@ def render_step(settings_per_view: Sequence, scene: Dict[str, torch.Tensor], dL_
             rs, scene["means3D"], scene["shs"], None, scene["opacities"], scene["scales"], scene["rotations"], None)
         gC = dL_dcolor(k, color, invd) if callable(dL_dcolor) else dL_dcolor
         gD = dL_dinvdepth(k, color, invd) if callable(dL_dinvdepth) else dL_dinvdepth
-        backward_raw(rs, scene["means3D"], radii, scene["shs"], None, scene["opacities"], scene["scales"],
-                     scene["rotations"], None, gC, gD, geom, binning, img, R, accumulate_into=grads, stats=stats)
+        if fused:
+            scratch = backward_render_only(rs, scene["means3D"], radii, scene["shs"], None, scene["opacities"],
+                                           scene["scales"], scene["rotations"], None, gC, gD, geom, binning, img, R)
+            states[k] = (rs, radii, geom, scratch)
+        else:
+            backward_raw(rs, scene["means3D"], radii, scene["shs"], None, scene["opacities"], scene["scales"],
+                         scene["rotations"], None, gC, gD, geom, binning, img, R, accumulate_into=grads, stats=stats)
         return color
 
     if streams is None:
         images = [one_view(k) for k in range(len(settings_per_view))]
     else:
         images = streams.run(len(settings_per_view), one_view)
+    if fused and states:
+        if streams is not None:   # the views' buffers were allocated on the side streams and are read on this one
+            cur = torch.cuda.current_stream(scene["means3D"].device)
+            for _rs, radii, geom, scratch in states:
+                for t in (radii, geom, scratch):
+                    t.record_stream(cur)
+        preprocess_backward_views(states, scene["means3D"], scene["shs"], None, scene["opacities"], scene["scales"],
+                                  scene["rotations"], None, accumulate_into=grads, stats=stats)
     if exchange:
         buffers.all_reduce(group)
     return images

@@ -322,3 +322,94 @@ def test_upstream_signature_of_the_extension():
         assert np.abs(t.cpu().numpy().reshape(ref[k].shape) - ref[k]).max() / s <= 1e-5, k
     vis = C_.mark_visible(d["means3D"], rs.viewmatrix, rs.projmatrix)
     assert vis.dtype == torch.bool and vis.shape == (6000,)
+
+
+@pytest.mark.parametrize("P,deg,V", [(9001, 3, 3), (5000, 0, 3), (3000, 2, 20)])
+def test_fused_multi_view_preprocess_backward_equals_the_per_view_sum(P, deg, V):
+    """gsr_preprocess_backward_views (all views of a step in one pass over the Gaussians) against the per-view backward:
+    gradients equal up to summation order, the densification statistics (per-view norms, counts, max radii) too.
+    deg 0 takes the library's per-view fallback (SH rows of 12 bytes), V = 20 two groups of views."""
+    from gaussian_splatting_lightning_b200.rasterizer import (backward_raw, backward_render_only, forward_raw,
+                                                              preprocess_backward_views)
+    from gaussian_splatting_lightning_b200.view_parallel import StepBuffers, ViewStreams, render_step
+    W, H = 176, 112
+    scene = {k: v.to(U.DEV) for k, v in U.synthetic.make_scene(P, deg, W, H, seed=P).items()}
+    cams = [U.settings_from_camera(U.synthetic_case(8, deg, W, H, view_k=k % 8, num_views=8)[0]) for k in range(V)]
+    g = torch.Generator().manual_seed(9)
+    dC = [torch.randn(3, H, W, generator=g).to(U.DEV) for _ in range(V)]
+    dD = [torch.randn(1, H, W, generator=g).to(U.DEV) for _ in range(V)]
+    M = (deg + 1) ** 2
+    a, b = StepBuffers(P, M, U.DEV), StepBuffers(P, M, U.DEV)
+    render_step(cams, scene, lambda k, c, d: dC[k], lambda k, c, d: dD[k], a, exchange=False, fused=False)
+    render_step(cams, scene, lambda k, c, d: dC[k], lambda k, c, d: dD[k], b, exchange=False, fused=True,
+                streams=ViewStreams(U.DEV, 3))
+    torch.cuda.synchronize()
+    assert float(a.grads()["dL_dmeans3D"].abs().max()) > 0
+    for n in a.grads():
+        w, got = a.grads()[n], b.grads()[n]
+        s = max(1.0, float(w.abs().max()))
+        assert float((got - w).abs().max()) / s <= 2e-5, n
+    assert torch.equal(a.max_radii, b.max_radii) and torch.equal(a.stats[1], b.stats[1])
+    assert float((a.stats[0] - b.stats[0]).abs().max()) <= 2e-5 * max(1.0, float(a.stats[0].max()))
+    # the storing (non-accumulating) form with a selection of outputs
+    states, want = [], None
+    for k in range(min(V, 3)):
+        R, color, radii, geom, binning, img, invd, cap = forward_raw(cams[k], scene["means3D"], scene["shs"], None,
+                                                                    scene["opacities"], scene["scales"], scene["rotations"], None)
+        args = (cams[k], scene["means3D"], radii, scene["shs"], None, scene["opacities"], scene["scales"], scene["rotations"],
+                None, dC[k], dD[k], geom, binning, img, R)
+        states.append((cams[k], radii, geom, backward_render_only(*args)))
+        one = backward_raw(*args)
+        want = one if want is None else tuple(x + y for x, y in zip(want, one))
+    got = preprocess_backward_views(states, scene["means3D"], scene["shs"], None, scene["opacities"], scene["scales"],
+                                    scene["rotations"], None, want=("dL_dmeans3D", "dL_dsh", "dL_drotations", "dL_dcov3D"))
+    assert [t is not None for t in got] == [False, False, False, True, True, True, False, True]
+    for i in (3, 4, 5, 7):
+        s = max(1.0, float(want[i].abs().max()))
+        assert float((got[i] - want[i]).abs().max()) / s <= 2e-5, i
+
+
+def test_step_sink_defers_the_autograd_backward_to_one_fused_pass():
+    """rasterizer.StepSink: inside it the autograd backward of a view runs the compositing backward only and parks the
+    view; flush() runs the preprocess backward of all parked views in one pass.  Same gradient sum and statistics as the
+    immediate accumulation (accumulate_gradients_into); a view that asks for dL_dmeans2D is not parked."""
+    from gaussian_splatting_lightning_b200.rasterizer import GaussianRasterizer, StepSink, accumulate_gradients_into
+    from gaussian_splatting_lightning_b200.view_parallel import StepBuffers
+    P, W, H, deg = 7000, 160, 96, 3
+    scene = {k: v.to(U.DEV) for k, v in U.synthetic.make_scene(P, deg, W, H, seed=31).items()}
+    cams = [U.settings_from_camera(U.synthetic_case(8, deg, W, H, view_k=k, num_views=8)[0]) for k in (0, 2, 5)]
+    g = torch.Generator().manual_seed(4)
+    dC = [torch.randn(3, H, W, generator=g).to(U.DEV) for _ in cams]
+
+    def params():
+        return {k: scene[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+
+    def render(p, rs, sp=None):
+        return GaussianRasterizer(rs)(means3D=p["means3D"], means2D=sp, shs=p["shs"], opacities=p["opacities"],
+                                      scales=p["scales"], rotations=p["rotations"])[0]
+
+    a, pa = StepBuffers(P, 16, U.DEV), params()
+    for rs, w in zip(cams, dC):
+        with accumulate_gradients_into(a.grads(), a.densify_stats()):
+            img = render(pa, rs)
+        (img * w).sum().backward()
+    b, pb = StepBuffers(P, 16, U.DEV), params()
+    sink = StepSink(b.grads(), b.densify_stats())
+    for rs, w in zip(cams, dC):
+        with sink:
+            img = render(pb, rs)
+        (img * w).sum().backward()
+    assert len(sink.pending) == 3 and float(b.grads()["dL_dmeans3D"].abs().max()) == 0.0     # nothing written yet
+    sink.flush()
+    assert not sink.pending
+    for n in a.grads():
+        s = max(1.0, float(a.grads()[n].abs().max()))
+        assert float((a.grads()[n] - b.grads()[n]).abs().max()) / s <= 2e-5, n
+    assert torch.equal(a.max_radii, b.max_radii) and torch.equal(a.stats[1], b.stats[1])
+    assert float((a.stats[0] - b.stats[0]).abs().max()) <= 2e-5 * max(1.0, float(a.stats[0].max()))
+    # a view whose dummy screen-space leaf wants its gradient takes the immediate path
+    sp = torch.zeros_like(pb["means3D"], requires_grad=True)
+    with sink:
+        img = render(pb, cams[0], sp)
+    (img * dC[0]).sum().backward()
+    assert not sink.pending and sp.grad is not None and float(sp.grad.abs().max()) > 0
