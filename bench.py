@@ -273,7 +273,8 @@ class Rig:
         if not fwd_only:
             # per-step buffers: gradient sum and statistics DELTAS of this step's views; the radii candidates stay
             # (max commutes with the steps: their exchange is deferred to densification time, StepBuffers.all_reduce)
-            self.bufs.zero_(keep_max_radii=self.world > 1)
+            # (the fused pass overwrites every gradient row: only the statistics need clearing)
+            self.bufs.zero_(keep_max_radii=self.world > 1, stats_only=self.fused)
         self.states = []
         self.vstreams.run(len(self.cams), lambda j: self.one_view(self.cams[j], fwd_only))
         if self.fused and not fwd_only:
@@ -283,7 +284,8 @@ class Rig:
                 for t in (radii, geom, scratch):
                     t.record_stream(cur)
             preprocess_backward_views(self.states, sc["means3D"], sc["shs"], None, sc["opacities"], sc["scales"],
-                                      sc["rotations"], None, accumulate_into=self.acc_into, stats=self.stat_into)
+                                      sc["rotations"], None, accumulate_into=self.acc_into, stats=self.stat_into,
+                                      overwrite=True)
             self.states = []
         if self.world > 1 and not fwd_only:
             self.bufs.all_reduce(max_radii=False)   # sum(flat + stats): ONE collective per step
@@ -435,12 +437,13 @@ class E2E:
     def step(self):
         rig = self.rig
         main = torch.cuda.current_stream()
-        rig.bufs.zero_(keep_max_radii=rig.world > 1)
+        rig.bufs.zero_(keep_max_radii=rig.world > 1, stats_only=rig.fused)
         for j in range(min(self.n_slots - 1, rig.vpr)):
             self.upload(j)
         rig.vstreams.run(rig.vpr, self.view)
         if rig.fused:
-            self.sink.flush()
+            assert len(self.sink.pending) == rig.vpr      # every view parked: the pass may overwrite the buffer
+            self.sink.flush(overwrite=True)
         if rig.world > 1:
             rig.bufs.all_reduce(max_radii=False)
         main.synchronize()                               # the step's result (losses) is on the host

@@ -30,7 +30,7 @@ SOURCES = {
     "radix_sort.cu": [],
     "render_forward.cu": [],
     "render_backward.cu": [],
-    "preprocess_backward.cu": ["-fmad=false"],
+    "preprocess_backward.cu": ["--use_fast_math"],   # gradients only (1e-4 contract): contraction, approximate div / sqrt
     "loss.cu": [],
     "optimizer.cu": ["-fmad=false"],
 }

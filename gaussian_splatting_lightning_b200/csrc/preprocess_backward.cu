@@ -61,6 +61,25 @@ __device__ __forceinline__ void put4(float4* p, float4 v) {
     *p = v;
   }
 }
+// n consecutive floats (n even, p 8-byte aligned): stores, or vector reductions at the L2 (REDG.E.ADD.F32x2 / F32x4)
+template <bool ACC, int N>
+__device__ __forceinline__ void put_run(float* p, const float* v) {
+  static_assert(N % 2 == 0, "runs of an even number of floats");
+  if (!ACC) {
+#pragma unroll
+    for (int k = 0; k < N; k += 2) *reinterpret_cast<float2*>(p + k) = make_float2(v[k], v[k + 1]);
+  } else if ((N % 4) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+#pragma unroll
+    for (int k = 0; k < N; k += 4)
+      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p + k), "f"(v[k]), "f"(v[k + 1]), "f"(v[k + 2]),
+                   "f"(v[k + 3]) : "memory");
+  } else {
+#pragma unroll
+    for (int k = 0; k < N; k += 2)
+      asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(p + k), "f"(v[k]), "f"(v[k + 1]) : "memory");
+  }
+}
+
 template <int DEG, bool ACC>
 __device__ __forceinline__ void sh_backward(const float* __restrict__ sh, float* __restrict__ dsh, int M, bool vec4,
                                             float x, float y, float z, const float* g3, float* ddir) {
@@ -404,14 +423,21 @@ cudaError_t launch_preprocess_backward(const GsrView& v, const GsrGaussiansDev& 
 // ---- all views of a step in ONE pass over the Gaussians -------------------------------------------------------------
 // A training step renders V views and sums their gradients.  Run view by view, the kernel above reads the Gaussian's
 // inputs (236 B at SH degree 3) and read-modify-writes its 236 B of the step's gradient buffer V times: 8 x 0.143 ms of a
-// 11.4 ms C3 step.  Here every Gaussian is visited ONCE: its inputs and SH block come in once, the V views contribute
-// from their own 48-byte rows of raw pixel sums (+ radius and clamp bits: 53 B per view), the sums over the views are
-// kept in registers (dL/dmean3D, dL/dcov3D, dL/dopacity, the statistics) and in the warp's second shared-memory block
-// (dL/dsh), and the gradient row is written -- or added -- once.  The chain cov3D -> (scale, quaternion) is linear in
-// dL/dcov3D with view-independent factors, so it runs once on the sum.  cov3D itself is recomputed from scale and
-// rotation (the forward's exact expression; a Gaussian culled in one view has no stored copy there).
+// 11.4 ms C3 step.  Here every Gaussian is visited ONCE by a group of L lanes, one lane per view (views k, k + L, ... for
+// V > L): a lane does its view's part of the chain from that view's own 48-byte row of raw pixel sums -- the same
+// memory-level parallelism as the per-view kernel -- and the L lanes then combine:
+//   * dL/dmean3D, dL/dcov3D, dL/dopacity, dL/dcolor and the statistics by L - 1 shuffle levels;
+//   * dL/dsh = sum_v basis_v (x) dL/dcolor_v is a (16 x V)(V x 3) product: the lanes park basis_v and the clamp-masked
+//     colour gradient (19 floats) in shared memory and every lane accumulates its own 16 / L coefficients of the row.
+// The Gaussian's inputs are loaded once per group (the L lanes read the same addresses: one transaction), its SH row comes
+// through L1, the gradient row is written -- or added -- once, cooperatively by the group.  The chain
+// cov3D -> (scale, quaternion) is linear in dL/dcov3D with view-independent factors, so it runs once on the sum.  cov3D is
+// recomputed from scale and rotation (the forward's exact expression; a Gaussian culled in one view has no stored copy).
 // The densification statistics stay PER VIEW quantities (|| dL/dmean2D ||_2 is taken before the views are summed:
 // gaussian_model.py:174-181).  dL/dmean2D itself is a per-view output and is not produced here.
+// (A first version -- one thread per Gaussian looping over the views, sums in registers, dL/dsh in a second shared-memory
+// block -- measured 1.04 ms per 8 views against 8 x 0.143: 120 registers, 16 warps per SM and eight dependent round trips
+// per thread.)
 constexpr int GSR_MAX_FUSED_VIEWS = 16;
 struct ViewSlot {
   GsrView v;
@@ -428,98 +454,77 @@ struct PreBwdViewsArgs {
   float* max_radii2D; float* xyz_grad_accum; float* xyz_grad_count;
 };
 
+// basis[0..15] (zero beyond the active degree) and d(colour)/d(direction) contracted with g3, from the Gaussian's SH row
 template <int DEG>
-__device__ __forceinline__ void sh_backward_add(const float* __restrict__ sh, float* __restrict__ dsh, bool first,
-                                                float x, float y, float z, const float* g3, float* ddir) {
+__device__ __forceinline__ void sh_dir_grad(const float* __restrict__ sh, float x, float y, float z, const float* g3,
+                                            float* basis16, float* ddir) {
   constexpr int N = (DEG + 1) * (DEG + 1);
-  constexpr int NV = (3 * N + 3) / 4;
   float basis[N], bx[N], by[N], bz[N];
   sh_basis<DEG>(x, y, z, basis);
   sh_basis_grad<DEG>(x, y, z, bx, by, bz);
-  ddir[0] = ddir[1] = ddir[2] = 0.f;
-  float out[NV * 4];
 #pragma unroll
-  for (int k = 0; k < N; ++k) {
+  for (int k = 0; k < 16; ++k) basis16[k] = k < N ? basis[k] : 0.f;
+  ddir[0] = ddir[1] = ddir[2] = 0.f;
+#pragma unroll
+  for (int k = 1; k < N; ++k) {
 #pragma unroll
     for (int ch = 0; ch < 3; ++ch) {
-      out[3 * k + ch] = basis[k] * g3[ch];
-      if (k > 0) {
-        const float s = sh[3 * k + ch] * g3[ch];
-        ddir[0] += bx[k] * s; ddir[1] += by[k] * s; ddir[2] += bz[k] * s;
-      }
+      const float s = sh[3 * k + ch] * g3[ch];
+      ddir[0] += bx[k] * s; ddir[1] += by[k] * s; ddir[2] += bz[k] * s;
     }
-  }
-#pragma unroll
-  for (int k = 3 * N; k < NV * 4; ++k) out[k] = 0.f;
-  float4* d4 = reinterpret_cast<float4*>(dsh);
-#pragma unroll
-  for (int k = 0; k < NV; ++k) {
-    float4 o = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
-    if (!first) { const float4 p = d4[k]; o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w; }
-    d4[k] = o;
   }
 }
 
-template <bool ACC>
-__global__ void __launch_bounds__(256, 2) preprocess_backward_views_kernel(const __grid_constant__ PreBwdViewsArgs a) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ __align__(8) unsigned long long bars[8];
+template <bool ACC, int L>
+__global__ void __launch_bounds__(256, 3) preprocess_backward_views_kernel(const __grid_constant__ PreBwdViewsArgs a) {
+  constexpr int GPW = 32 / L;       // Gaussians per warp
+  constexpr int CPL = 16 / L;       // SH coefficients of the row a lane owns
+  __shared__ float s_ex[8][32][20]; // per warp and lane: basis[16], masked dL/dcolour[3] of the lane's view
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int sub = lane % L, grp = lane / L;
   const int P = a.g.P, M = a.g.M;
-  const int w0 = blockIdx.x * 256 + warp * 32;
-  if (w0 >= P) return;
-  const int i = w0 + lane;
-  const int nrows = min(32, P - w0);
-  // which views see this Gaussian: one bit per view, loaded up front
-  uint32_t seen = 0;
-  int max_radius = 0;
-  if (i < P) {
-    for (int k = 0; k < a.V; ++k) {
-      const int r = a.view[k].radii[i];
-      if (r > 0) { seen |= 1u << k; max_radius = max(max_radius, r); }
-    }
-  }
-  const bool any_visible = __any_sync(0xffffffffu, seen != 0u);
-  if (ACC && !any_visible) return;  // nothing to add anywhere
-
+  const long long gi = ((long long)blockIdx.x * 8 + warp) * GPW + grp;
+  const bool valid = gi < P;
+  const int i = valid ? (int)gi : 0;
   const bool want_sh = a.g.shs != nullptr;
-  const uint32_t row_bytes = (uint32_t)M * 12u, blk_bytes = (uint32_t)nrows * row_bytes;
-  float* blk = reinterpret_cast<float*>(smem_raw + (size_t)warp * 32 * row_bytes);                      // SH in
-  float* dblk = reinterpret_cast<float*>(smem_raw + (size_t)(8 + warp) * 32 * row_bytes);               // dL/dsh out
-  const bool bulk_in = want_sh && any_visible;
-  if (bulk_in) {
-    if (lane == 0) {
-      mbar_init(&bars[warp], 1);
-      mbar_arrive_expect_tx(&bars[warp], blk_bytes);
-      bulk_copy_g2s(blk, a.g.shs + (size_t)w0 * M * 3, blk_bytes, &bars[warp]);
-    }
-    __syncwarp();
-  }
-  float dmean[3] = {0.f, 0.f, 0.f}, dS[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, dcol[3] = {0.f, 0.f, 0.f};
-  float dop = 0.f, norm_sum = 0.f, count = 0.f;
-  float* dsh_row = dblk + (size_t)lane * M * 3;
-  const float* sh_row = blk + (size_t)lane * M * 3;
-  bool sh_first = true;
-  float4 q_in = make_float4(1.f, 0.f, 0.f, 0.f);
-  float sc0 = 0.f, sc1 = 0.f, sc2 = 0.f;
+  const uint32_t gmask = (L == 32) ? 0xffffffffu : (((1u << L) - 1u) << (grp * L));   // the group's lanes
 
-  if (seen) {
-    const float px = a.g.means3D[3 * (size_t)i], py = a.g.means3D[3 * (size_t)i + 1], pz = a.g.means3D[3 * (size_t)i + 2];
-    float s6[6];
-    const float mod = a.view[0].v.scale_modifier;
+  float px = 0.f, py = 0.f, pz = 0.f, opac_in = 0.f, sc0 = 0.f, sc1 = 0.f, sc2 = 0.f;
+  float4 q_in = make_float4(1.f, 0.f, 0.f, 0.f);
+  float s6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (valid) {
+    px = a.g.means3D[3 * (size_t)i]; py = a.g.means3D[3 * (size_t)i + 1]; pz = a.g.means3D[3 * (size_t)i + 2];
+    opac_in = a.g.opacities[i];
     if (a.g.cov3D_precomp) {
 #pragma unroll
       for (int k = 0; k < 6; ++k) s6[k] = a.g.cov3D_precomp[6 * (size_t)i + k];
     } else {
       q_in = reinterpret_cast<const float4*>(a.g.rotations)[i];
       sc0 = a.g.scales[3 * (size_t)i]; sc1 = a.g.scales[3 * (size_t)i + 1]; sc2 = a.g.scales[3 * (size_t)i + 2];
-      cov3d_from_scale_rot(sc0, sc1, sc2, mod, q_in, s6);   // the forward's expression (preprocess.cu), bit for bit
+      cov3d_from_scale_rot(sc0, sc1, sc2, a.view[0].v.scale_modifier, q_in, s6);   // the forward's expression, bit for bit
     }
-    const float S[3][3] = {{s6[0], s6[1], s6[2]}, {s6[1], s6[3], s6[4]}, {s6[2], s6[4], s6[5]}};
-    const float opac_in = a.g.opacities[i];
-    bool sh_waited = false;
-    for (int k = 0; k < a.V; ++k) {
-      if (!((seen >> k) & 1u)) continue;
+  }
+  const float S[3][3] = {{s6[0], s6[1], s6[2]}, {s6[1], s6[3], s6[4]}, {s6[2], s6[4], s6[5]}};
+  const float* __restrict__ sh_row = want_sh ? a.g.shs + (size_t)i * M * 3 : nullptr;
+
+  float dmean[3] = {0.f, 0.f, 0.f}, dS[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, dcol[3] = {0.f, 0.f, 0.f};
+  float dop = 0.f, norm_sum = 0.f, count = 0.f;
+  int max_radius = 0;
+  float dsh_mine[3 * CPL];
+#pragma unroll
+  for (int k = 0; k < 3 * CPL; ++k) dsh_mine[k] = 0.f;
+
+  for (int k0 = 0; k0 < a.V; k0 += L) {
+    const int k = k0 + sub;
+    const int radius = (valid && k < a.V) ? a.view[k].radii[i] : 0;
+    // the lane's basis_v and masked colour gradient go to shared memory for the dL/dsh product below; zeros when the
+    // view does not see the Gaussian
+    float4* mine = reinterpret_cast<float4*>(&s_ex[warp][lane][0]);
+    if (!(radius > 0)) {
+      const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      mine[0] = z4; mine[1] = z4; mine[2] = z4; mine[3] = z4; mine[4] = z4;
+    }
+    if (radius > 0) {
       const ViewSlot& vs = a.view[k];
       const float4 g0 = reinterpret_cast<const float4*>(vs.grad_acc)[3 * (size_t)i];      // S0 S1 S2 S3
       const float4 g1 = reinterpret_cast<const float4*>(vs.grad_acc)[3 * (size_t)i + 1];  // S4 S5 dr dg
@@ -528,6 +533,7 @@ __global__ void __launch_bounds__(256, 2) preprocess_backward_views_kernel(const
       const float* __restrict__ view = vs.v.view;
       const float* __restrict__ proj = vs.v.proj;
       const float fx = vs.v.fx, fy = vs.v.fy;
+      max_radius = max(max_radius, radius);
       JacobianCtx jc;
       build_jacobian(view, px, py, pz, fx, fy, vs.v.tanfovx, vs.v.tanfovy, jc);
       const Cov2D c0 = project_cov(s6, jc);
@@ -598,103 +604,145 @@ __global__ void __launch_bounds__(256, 2) preprocess_backward_views_kernel(const
       count += 1.f;
       dcol[0] += g1.z; dcol[1] += g1.w; dcol[2] += g2.x;
       if (want_sh) {
-        if (!sh_waited) { mbar_wait(&bars[warp], 0); sh_waited = true; }
         const float* __restrict__ cam = vs.v.campos;
         const float dirx = px - cam[0], diry = py - cam[1], dirz = pz - cam[2];
         const float len = sqrtf(dirx * dirx + diry * diry + dirz * dirz);
         const float x = dirx / len, y = diry / len, z = dirz / len;
         const float g3[3] = {(cl & 1u) ? 0.f : g1.z, (cl & 2u) ? 0.f : g1.w, (cl & 4u) ? 0.f : g2.x};
-        float ddir[3];
+        float ddir[3], basis16[16];
         switch (vs.v.deg) {
-          case 0: sh_backward_add<0>(sh_row, dsh_row, sh_first, x, y, z, g3, ddir); break;
-          case 1: sh_backward_add<1>(sh_row, dsh_row, sh_first, x, y, z, g3, ddir); break;
-          case 2: sh_backward_add<2>(sh_row, dsh_row, sh_first, x, y, z, g3, ddir); break;
-          default: sh_backward_add<3>(sh_row, dsh_row, sh_first, x, y, z, g3, ddir); break;
+          case 0: sh_dir_grad<0>(sh_row, x, y, z, g3, basis16, ddir); break;
+          case 1: sh_dir_grad<1>(sh_row, x, y, z, g3, basis16, ddir); break;
+          case 2: sh_dir_grad<2>(sh_row, x, y, z, g3, basis16, ddir); break;
+          default: sh_dir_grad<3>(sh_row, x, y, z, g3, basis16, ddir); break;
         }
-        sh_first = false;
+        mine[0] = make_float4(basis16[0], basis16[1], basis16[2], basis16[3]);
+        mine[1] = make_float4(basis16[4], basis16[5], basis16[6], basis16[7]);
+        mine[2] = make_float4(basis16[8], basis16[9], basis16[10], basis16[11]);
+        mine[3] = make_float4(basis16[12], basis16[13], basis16[14], basis16[15]);
+        mine[4] = make_float4(g3[0], g3[1], g3[2], 0.f);
         const float ng = x * ddir[0] + y * ddir[1] + z * ddir[2];
         dm[0] += (ddir[0] - x * ng) / len;
         dm[1] += (ddir[1] - y * ng) / len;
         dm[2] += (ddir[2] - z * ng) / len;
+      } else {
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        mine[0] = z4; mine[1] = z4; mine[2] = z4; mine[3] = z4; mine[4] = z4;
       }
       dmean[0] += dm[0]; dmean[1] += dm[1]; dmean[2] += dm[2];
     }
-  }
-  // ---- the Gaussian's row of every output, once ------------------------------------------------------------------
-  if (i < P && (seen || !ACC)) {
-    if (a.dL_dopacity) put<ACC>(a.dL_dopacity + i, dop);
-    if (a.dL_dmeans3D)
-      for (int j = 0; j < 3; ++j) put<ACC>(a.dL_dmeans3D + 3 * (size_t)i + j, dmean[j]);
-    if (a.dL_dcolors)
-      for (int j = 0; j < 3; ++j) put<ACC>(a.dL_dcolors + 3 * (size_t)i + j, dcol[j]);
-    if (a.dL_dcov3D)
-      for (int k = 0; k < 6; ++k) put<ACC>(a.dL_dcov3D + 6 * (size_t)i + k, dS[k]);
-    if (seen) {
-      if (a.max_radii2D) atomicMax(reinterpret_cast<int*>(a.max_radii2D + i), __float_as_int((float)max_radius));
-      if (a.xyz_grad_accum) atomicAdd(a.xyz_grad_accum + i, norm_sum);
-      if (a.xyz_grad_count) atomicAdd(a.xyz_grad_count + i, count);
-    }
-    float4 dq = make_float4(0.f, 0.f, 0.f, 0.f);
-    float dsc[3] = {0.f, 0.f, 0.f};
-    if (seen && !a.g.cov3D_precomp && (a.dL_dscales || a.dL_drot)) {
-      const float4 q = q_in;
-      float R[3][3];
-      quat_to_R(q, R);
-      const float mod = a.view[0].v.scale_modifier;
-      const float s[3] = {mod * sc0, mod * sc1, mod * sc2};
-      const float Gm[3][3] = {{dS[0], 0.5f * dS[1], 0.5f * dS[2]},
-                              {0.5f * dS[1], dS[3], 0.5f * dS[4]},
-                              {0.5f * dS[2], 0.5f * dS[4], dS[5]}};
-      float dR[3][3];
+    if (want_sh && a.dL_dsh) {
+      // dL/dsh row += sum over the group's views of basis_v (x) g3_v; a lane owns coefficients CPL * sub ...
+      __syncwarp();
 #pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        float dsk = 0.f;
+      for (int v = 0; v < L; ++v) {
+        const float* src = &s_ex[warp][grp * L + v][0];
+        const float4 gv = reinterpret_cast<const float4*>(src)[4];
 #pragma unroll
-        for (int r = 0; r < 3; ++r) {
-          const float dLrk = 2.f * (Gm[r][0] * R[0][k] + Gm[r][1] * R[1][k] + Gm[r][2] * R[2][k]) * s[k];
-          dsk += dLrk * R[r][k];
-          dR[r][k] = dLrk * s[k];
+        for (int c = 0; c < CPL; ++c) {
+          const float bv = src[CPL * sub + c];
+          dsh_mine[3 * c + 0] = fmaf(bv, gv.x, dsh_mine[3 * c + 0]);
+          dsh_mine[3 * c + 1] = fmaf(bv, gv.y, dsh_mine[3 * c + 1]);
+          dsh_mine[3 * c + 2] = fmaf(bv, gv.z, dsh_mine[3 * c + 2]);
         }
-        dsc[k] = mod * dsk;
       }
-      const float r = q.x, x = q.y, y = q.z, z = q.w;
-      dq.x = 2.f * (-z * dR[0][1] + y * dR[0][2] + z * dR[1][0] - x * dR[1][2] - y * dR[2][0] + x * dR[2][1]);
-      dq.y = 2.f * (y * dR[0][1] + z * dR[0][2] + y * dR[1][0] - 2.f * x * dR[1][1] - r * dR[1][2] + z * dR[2][0] +
-                    r * dR[2][1] - 2.f * x * dR[2][2]);
-      dq.z = 2.f * (-2.f * y * dR[0][0] + x * dR[0][1] + r * dR[0][2] + x * dR[1][0] + z * dR[1][2] - r * dR[2][0] +
-                    z * dR[2][1] - 2.f * y * dR[2][2]);
-      dq.w = 2.f * (-2.f * z * dR[0][0] - r * dR[0][1] + x * dR[0][2] + r * dR[1][0] - 2.f * z * dR[1][1] +
-                    y * dR[1][2] + x * dR[2][0] + y * dR[2][1]);
+      __syncwarp();
     }
-    if (a.dL_dscales)
-      for (int k = 0; k < 3; ++k) put<ACC>(a.dL_dscales + 3 * (size_t)i + k, dsc[k]);
-    if (a.dL_drot) put4<ACC>(reinterpret_cast<float4*>(a.dL_drot) + i, dq);
   }
-  // ---- the warp's dL/dsh block: one bulk store / bulk reduction ----------------------------------------------------
-  if (want_sh && a.dL_dsh) {
-    if (sh_first && i < P)   // no view touched this row: it must read as zeros
-      for (int k = 0; k < 3 * M / 4; ++k) reinterpret_cast<float4*>(dsh_row)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (bulk_in) mbar_wait(&bars[warp], 0);  // every lane: the warp must not retire under its in-flight SH copy
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    __syncwarp();
-    if (lane == 0) {
-      float* dst = a.dL_dsh + (size_t)w0 * M * 3;
-      if (ACC) bulk_reduce_add_s2g(dst, dblk, blk_bytes);
-      else bulk_copy_s2g(dst, dblk, blk_bytes);
-      bulk_commit_and_wait_read();
+  // ---- combine the group's lanes -----------------------------------------------------------------------------------
+#pragma unroll
+  for (int off = 1; off < L; off <<= 1) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      dmean[j] += __shfl_xor_sync(0xffffffffu, dmean[j], off);
+      dcol[j] += __shfl_xor_sync(0xffffffffu, dcol[j], off);
     }
-  } else if (bulk_in) {
-    mbar_wait(&bars[warp], 0);
+#pragma unroll
+    for (int j = 0; j < 6; ++j) dS[j] += __shfl_xor_sync(0xffffffffu, dS[j], off);
+    dop += __shfl_xor_sync(0xffffffffu, dop, off);
+    norm_sum += __shfl_xor_sync(0xffffffffu, norm_sum, off);
+    count += __shfl_xor_sync(0xffffffffu, count, off);
+    max_radius = max(max_radius, __shfl_xor_sync(0xffffffffu, max_radius, off));
+  }
+  (void)gmask;
+  const bool seen = count > 0.f;
+  if (!valid || (ACC && !seen)) return;   // accumulating: rows of Gaussians no view saw keep their value
+  // ---- the Gaussian's row of every output, once: scalars by the group's first lane, dL/dsh by all of them ---------
+  if (want_sh && a.dL_dsh) {
+    float* row = a.dL_dsh + (size_t)i * M * 3;
+    if (M >= 16 && (reinterpret_cast<uintptr_t>(row) & 7) == 0) {
+      put_run<ACC, 3 * CPL>(row + 3 * CPL * sub, dsh_mine);   // the lane's 3 * CPL consecutive floats of the row
+    } else {
+#pragma unroll
+      for (int c = 0; c < CPL; ++c) {
+        const int coef = CPL * sub + c;
+        if (coef < M) {
+#pragma unroll
+          for (int ch = 0; ch < 3; ++ch) put<ACC>(row + 3 * coef + ch, dsh_mine[3 * c + ch]);
+        }
+      }
+    }
+    if (!ACC)   // stored coefficients beyond 16 (never used by a degree <= 3 evaluation) read as zeros
+      for (int coef = 16 + sub; coef < M; coef += L)
+        for (int ch = 0; ch < 3; ++ch) row[3 * coef + ch] = 0.f;
+  }
+  if (sub != 0) return;
+  if (a.dL_dopacity) put<ACC>(a.dL_dopacity + i, dop);
+  if (a.dL_dmeans3D)
+    for (int j = 0; j < 3; ++j) put<ACC>(a.dL_dmeans3D + 3 * (size_t)i + j, dmean[j]);
+  if (a.dL_dcolors)
+    for (int j = 0; j < 3; ++j) put<ACC>(a.dL_dcolors + 3 * (size_t)i + j, dcol[j]);
+  if (a.dL_dcov3D)
+    for (int k = 0; k < 6; ++k) put<ACC>(a.dL_dcov3D + 6 * (size_t)i + k, dS[k]);
+  if (seen) {
+    if (a.max_radii2D) atomicMax(reinterpret_cast<int*>(a.max_radii2D + i), __float_as_int((float)max_radius));
+    if (a.xyz_grad_accum) atomicAdd(a.xyz_grad_accum + i, norm_sum);
+    if (a.xyz_grad_count) atomicAdd(a.xyz_grad_count + i, count);
+  }
+  float4 dq = make_float4(0.f, 0.f, 0.f, 0.f);
+  float dsc[3] = {0.f, 0.f, 0.f};
+  if (seen && !a.g.cov3D_precomp && (a.dL_dscales || a.dL_drot)) {
+    const float4 q = q_in;
+    float R[3][3];
+    quat_to_R(q, R);
+    const float mod = a.view[0].v.scale_modifier;
+    const float s[3] = {mod * sc0, mod * sc1, mod * sc2};
+    const float Gm[3][3] = {{dS[0], 0.5f * dS[1], 0.5f * dS[2]},
+                            {0.5f * dS[1], dS[3], 0.5f * dS[4]},
+                            {0.5f * dS[2], 0.5f * dS[4], dS[5]}};
+    float dR[3][3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      float dsk = 0.f;
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const float dLrk = 2.f * (Gm[r][0] * R[0][k] + Gm[r][1] * R[1][k] + Gm[r][2] * R[2][k]) * s[k];
+        dsk += dLrk * R[r][k];
+        dR[r][k] = dLrk * s[k];
+      }
+      dsc[k] = mod * dsk;
+    }
+    const float r = q.x, x = q.y, y = q.z, z = q.w;
+    dq.x = 2.f * (-z * dR[0][1] + y * dR[0][2] + z * dR[1][0] - x * dR[1][2] - y * dR[2][0] + x * dR[2][1]);
+    dq.y = 2.f * (y * dR[0][1] + z * dR[0][2] + y * dR[1][0] - 2.f * x * dR[1][1] - r * dR[1][2] + z * dR[2][0] +
+                  r * dR[2][1] - 2.f * x * dR[2][2]);
+    dq.z = 2.f * (-2.f * y * dR[0][0] + x * dR[0][1] + r * dR[0][2] + x * dR[1][0] + z * dR[1][2] - r * dR[2][0] +
+                  z * dR[2][1] - 2.f * y * dR[2][2]);
+    dq.w = 2.f * (-2.f * z * dR[0][0] - r * dR[0][1] + x * dR[0][2] + r * dR[1][0] - 2.f * z * dR[1][1] +
+                  y * dR[1][2] + x * dR[2][0] + y * dR[2][1]);
+  }
+  if (a.dL_dscales)
+    for (int k = 0; k < 3; ++k) put<ACC>(a.dL_dscales + 3 * (size_t)i + k, dsc[k]);
+  if (a.dL_drot) {
+    const float dqv[4] = {dq.x, dq.y, dq.z, dq.w};
+    put_run<ACC, 4>(a.dL_drot + 4 * (size_t)i, dqv);
   }
 }
 
-// All views must share sh_degree, scale_modifier and the Gaussian tensors.  Requires the bulk-copy layout (M % 4 == 0,
-// 16-byte aligned shs / dL_dsh); the caller falls back to the per-view kernel otherwise.
+// All views must share sh_degree, scale_modifier and the Gaussian tensors.  The caller falls back to the per-view
+// kernel for what this one does not take.
 bool preprocess_backward_views_supported(const GsrGaussiansDev& g, const PreBwdOut& o) {
-  if (o.dL_dmeans2D) return false;
-  if (!g.shs) return true;
-  return (g.M % 4) == 0 && (size_t)512 * g.M * 12 <= 200 * 1024 && (reinterpret_cast<uintptr_t>(g.shs) & 15) == 0 &&
-         (!o.dL_dsh || (reinterpret_cast<uintptr_t>(o.dL_dsh) & 15) == 0);
+  return !o.dL_dmeans2D;
 }
 
 cudaError_t launch_preprocess_backward_views(int V, const GsrView* views, const int32_t* const* radii,
@@ -716,13 +764,19 @@ cudaError_t launch_preprocess_backward_views(int V, const GsrView* views, const 
     a.dL_dcov3D = out.dL_dcov3D; a.dL_dsh = g.shs ? out.dL_dsh : nullptr; a.dL_dscales = out.dL_dscales;
     a.dL_drot = out.dL_drot;
     a.max_radii2D = out.max_radii2D; a.xyz_grad_accum = out.xyz_grad_accum; a.xyz_grad_count = out.xyz_grad_count;
-    const size_t smem = g.shs ? (size_t)512 * g.M * 12 : 0;   // SH block in + dL/dsh block out, 8 warps each
-    auto kern = out.accumulate ? preprocess_backward_views_kernel<true> : preprocess_backward_views_kernel<false>;
-    if (smem > 48 * 1024 - 256) {
-      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-      if (e != cudaSuccess) return e;
+    // L lanes per Gaussian, one per view: 8 for a step of many views, 4 / 2 for few
+    const int L = a.V > 4 ? 8 : (a.V > 2 ? 4 : 2);
+    const int per_cta = 256 / L;
+    const unsigned grid = (unsigned)((g.P + per_cta - 1) / per_cta);
+    if (out.accumulate) {
+      if (L == 8) preprocess_backward_views_kernel<true, 8><<<grid, 256, 0, s>>>(a);
+      else if (L == 4) preprocess_backward_views_kernel<true, 4><<<grid, 256, 0, s>>>(a);
+      else preprocess_backward_views_kernel<true, 2><<<grid, 256, 0, s>>>(a);
+    } else {
+      if (L == 8) preprocess_backward_views_kernel<false, 8><<<grid, 256, 0, s>>>(a);
+      else if (L == 4) preprocess_backward_views_kernel<false, 4><<<grid, 256, 0, s>>>(a);
+      else preprocess_backward_views_kernel<false, 2><<<grid, 256, 0, s>>>(a);
     }
-    kern<<<(g.P + 255) / 256, 256, smem, s>>>(a);
     count_launch();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;

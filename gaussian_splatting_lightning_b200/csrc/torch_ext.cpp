@@ -294,7 +294,9 @@ std::vector<OptTensor> preprocess_backward_views(
     const std::vector<ViewTuple>& views, const Tensor& means3D, const OptTensor& colors, const Tensor& opacities,
     const OptTensor& scales, const OptTensor& rotations, double scale_modifier, const OptTensor& cov3D, const OptTensor& sh,
     int64_t degree, bool antialiasing, bool debug, int64_t want_mask, const std::vector<OptTensor>& accumulate_into,
-    const std::vector<OptTensor>& stats) {
+    const std::vector<OptTensor>& stats, bool overwrite) {
+  // overwrite: the tensors of accumulate_into are WRITTEN (every row, zeros where no view saw the Gaussian) instead of
+  // added to -- the step's buffer needs no clearing and the kernel no reductions at the L2
   TORCH_CHECK(!views.empty(), "preprocess_backward_views: no views");
   const c10::Device dev = means3D.device();
   std::vector<Frame> frames;   // keeps every view's device-side settings alive over the call
@@ -355,7 +357,7 @@ std::vector<OptTensor> preprocess_backward_views(
     }
   }
   cudaStream_t stream = at::cuda::getCurrentCUDAStream(dev.index()).stream();
-  check(gsr_preprocess_backward_views(vs.data(), (int32_t)vs.size(), &fr.g, &gr, acc ? GSR_GRADS_ACCUMULATE : 0,
+  check(gsr_preprocess_backward_views(vs.data(), (int32_t)vs.size(), &fr.g, &gr, (acc && !overwrite) ? GSR_GRADS_ACCUMULATE : 0,
                                       have_stats ? &ds : nullptr, (void*)stream),
         "gsr_preprocess_backward_views");
   return out;

@@ -269,11 +269,13 @@ def backward_render_only(rs: GaussianRasterizationSettings, means3D, radii, sh, 
 
 
 def preprocess_backward_views(views, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                              want=None, accumulate_into=None, stats=None):
+                              want=None, accumulate_into=None, stats=None, overwrite=False):
     """gsr_preprocess_backward_views: the preprocess backward of ALL views of a training step in one pass over the
     Gaussians.  views: sequence of (raster_settings, radii, geomBuffer, scratch), scratch from backward_render_only.
     Returns the 8-tuple of backward_raw with dL_dmeans2D = None (a per-view output); `want`, `accumulate_into` and
-    `stats` as in backward_raw.  The result equals the sum of per-view backward_raw calls up to float summation order;
+    `stats` as in backward_raw; overwrite=True WRITES the tensors of accumulate_into (every row; zeros where no view
+    saw the Gaussian) instead of adding to them, so a step whose views all go through one call needs no cleared buffer
+    and no reductions at the L2.  The result equals the sum of per-view backward_raw calls up to float summation order;
     the densification statistics are the per-view ones (norm taken per view, then summed)."""
     views = list(views)
     if not views:
@@ -293,7 +295,7 @@ def preprocess_backward_views(views, means3D, sh, colors_precomp, opacities, sca
         try:
             return tuple(ext.preprocess_backward_views(
                 vt, means3D, colors_precomp, opacities, scales, rotations, float(rs0.scale_modifier), cov3Ds_precomp, sh,
-                int(rs0.sh_degree), bool(rs0.antialiasing), bool(rs0.debug), mask, acc, st))
+                int(rs0.sh_degree), bool(rs0.antialiasing), bool(rs0.debug), mask, acc, st, bool(overwrite)))
         except RuntimeError as e:
             if "gsr_" in str(e):
                 raise N.GsrError(str(e)) from None
@@ -317,7 +319,7 @@ def preprocess_backward_views(views, means3D, sh, colors_precomp, opacities, sca
         grads = N.GsrGrads(*[N.ptr(t) for t in g.values()])
         ds = N.GsrDensifyStats(*[N.ptr(t) for t in st]) if st else None
         N.check(N.lib().gsr_preprocess_backward_views(arr, len(views), C.byref(fr.gaussians), C.byref(grads),
-                                                      N.GSR_GRADS_ACCUMULATE if accumulate_into is not None else 0,
+                                                      N.GSR_GRADS_ACCUMULATE if (accumulate_into is not None and not overwrite) else 0,
                                                       C.byref(ds) if ds is not None else None, N.stream_ptr(dev)),
                 "gsr_preprocess_backward_views")
     return tuple(g.values())
@@ -377,8 +379,10 @@ class StepSink:
         _sink.grads, _sink.stats, _sink.step = self._prev
         return False
 
-    def flush(self):
-        """Run the fused preprocess backward over the parked views (on the current stream) and forget them."""
+    def flush(self, overwrite: bool = False):
+        """Run the fused preprocess backward over the parked views (on the current stream) and forget them.
+        overwrite=True writes the gradient tensors instead of adding to them (every view of the step was parked and the
+        tensors were not cleared: preprocess_backward_views)."""
         if not self.pending:
             return
         views, self.pending = self.pending, []
@@ -389,7 +393,7 @@ class StepSink:
                 t.record_stream(cur)
         preprocess_backward_views(views, means3D, sh, colors, opac, scales, rot, cov,
                                   accumulate_into={n: t for n, t in self.grads.items() if n != "dL_dmeans2D"},
-                                  stats=self.stats)
+                                  stats=self.stats, overwrite=overwrite)
 
 
 _sink = _Sink()

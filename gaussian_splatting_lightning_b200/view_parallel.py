@@ -81,9 +81,16 @@ class StepBuffers:
         """pass as backward_raw(..., stats=...)."""
         return dict(max_radii2D=self.max_radii, xyz_grad_accum=self.stats[0], xyz_grad_count=self.stats[1])
 
-    def zero_(self, keep_max_radii: bool = False) -> None:
-        """Clear the step.  keep_max_radii: leave the radii candidates alone (deferred max exchange, see all_reduce)."""
-        (self._summed if keep_max_radii else self._store).zero_()
+    def zero_(self, keep_max_radii: bool = False, stats_only: bool = False) -> None:
+        """Clear the step.  keep_max_radii: leave the radii candidates alone (deferred max exchange, see all_reduce).
+        stats_only: leave the gradient sections alone too -- the fused preprocess backward of the whole step overwrites
+        every row of them (preprocess_backward_views(..., overwrite=True))."""
+        if stats_only:
+            self._stats2.zero_()
+            if not keep_max_radii:
+                self.max_radii.zero_()
+        else:
+            (self._summed if keep_max_radii else self._store).zero_()
 
     # -- the one exchange step --------------------------------------------------------------------
     def all_reduce(self, group=None, async_op: bool = False, max_radii: bool = True):
@@ -177,7 +184,7 @@ def render_step(settings_per_view: Sequence, scene: Dict[str, torch.Tensor], dL_
     Returns the rendered colour images.
     """
     from .rasterizer import backward_raw, backward_render_only, forward_raw, preprocess_backward_views
-    buffers.zero_()
+    buffers.zero_(stats_only=fused and len(settings_per_view) > 0)
     grads, stats = buffers.grads(), buffers.densify_stats()
     states = [None] * len(settings_per_view)
 
@@ -207,7 +214,7 @@ def render_step(settings_per_view: Sequence, scene: Dict[str, torch.Tensor], dL_
                 for t in (radii, geom, scratch):
                     t.record_stream(cur)
         preprocess_backward_views(states, scene["means3D"], scene["shs"], None, scene["opacities"], scene["scales"],
-                                  scene["rotations"], None, accumulate_into=grads, stats=stats)
+                                  scene["rotations"], None, accumulate_into=grads, stats=stats, overwrite=True)
     if exchange:
         buffers.all_reduce(group)
     return images
