@@ -219,6 +219,7 @@ def stage_model(P, M, Pvis, R, L, A, HW, T, passes):
 # which roofline bounds a stage: the compositing kernels are bound by FP32 instruction issue, the
 # per-Gaussian kernels by HBM bytes, the binning stages by latency / L2 transactions (reported against HBM bytes)
 STAGE_BOUND = {"render_forward": "fp32_issue", "render_backward": "fp32_issue"}
+EXCHANGE_CHUNKS = 4      # Gaussian ranges the fused step backward + all-reduce are pipelined over (N > 1)
 DENSIFY_INTERVAL = 100   # gs_lightning/lightning/gs_lightning_module.py:32,198: densification reads max_radii2D every 100 steps
 NCU_COUNTS = os.path.join(ROOT, "profiles", "ncu_counts.json")   # per-launch counters of the committed ncu capture
 
@@ -241,8 +242,10 @@ class Rig:
         self.dL_dinv = torch.randn(1, self.H, self.W, generator=g).to(device)
         # per-step exchange buffers: flat gradient buffer [means3D 3 | sh 3M | opacity 1 | scales 3 | rot 4]
         # (59 floats per Gaussian at M = 16) + densification-statistics deltas (view_parallel.py)
-        self.bufs = StepBuffers(self.P, self.M, device)
-        self.acc_into, self.stat_into = self.bufs.grads(), self.bufs.densify_stats()
+        # (chunk-major with N > 1 ranks: the exchange then follows the fused preprocess backward range by range)
+        self.bufs = StepBuffers(self.P, self.M, device, chunks=(EXCHANGE_CHUNKS if world > 1 and fused else 1))
+        one = self.bufs.num_chunks == 1
+        self.acc_into, self.stat_into = (self.bufs.grads(), self.bufs.densify_stats()) if one else (None, None)
         self.n_streams = streams
         self.steps_done = 0
         self.fused, self.states = fused, []
@@ -277,18 +280,17 @@ class Rig:
             self.bufs.zero_(keep_max_radii=self.world > 1, stats_only=self.fused)
         self.states = []
         self.vstreams.run(len(self.cams), lambda j: self.one_view(self.cams[j], fwd_only))
-        if self.fused and not fwd_only:
-            from gaussian_splatting_lightning_b200.rasterizer import preprocess_backward_views
-            sc, cur = self.scene, torch.cuda.current_stream(self.device)
-            for _rs, radii, geom, scratch in self.states:      # allocated under the view streams' pools, read here
-                for t in (radii, geom, scratch):
-                    t.record_stream(cur)
-            preprocess_backward_views(self.states, sc["means3D"], sc["shs"], None, sc["opacities"], sc["scales"],
-                                      sc["rotations"], None, accumulate_into=self.acc_into, stats=self.stat_into,
-                                      overwrite=True)
+        if fwd_only:
+            return
+        if self.fused:
+            # ONE pass over the Gaussians for all views of the step, Gaussian range by Gaussian range; each range's
+            # all-reduce (sum of gradients + statistics: one collective) runs under the pass over the next range
+            from gaussian_splatting_lightning_b200.view_parallel import fused_backward_and_exchange
+            fused_backward_and_exchange(self.states, self.scene, self.bufs, exchange=self.world > 1, max_radii=False)
             self.states = []
-        if self.world > 1 and not fwd_only:
+        elif self.world > 1:
             self.bufs.all_reduce(max_radii=False)   # sum(flat + stats): ONE collective per step
+        if self.world > 1:
             self.steps_done += 1
             if self.steps_done % DENSIFY_INTERVAL == 0:
                 self.bufs.all_reduce_max_radii()    # the deferred max, when densification would read max_radii2D
@@ -382,7 +384,8 @@ class E2E:
         self.cam_host = [torch.cat([c["host"]["viewmatrix"].reshape(-1), c["host"]["projmatrix"].reshape(-1),
                                     c["host"]["campos"].reshape(-1), torch.zeros(3)]).pin_memory() for c in rig.cams]
         self.loss_host = torch.zeros(vpr).pin_memory()
-        parameter_groups_on(rig.bufs, self.params)
+        if rig.bufs.num_chunks == 1:
+            parameter_groups_on(rig.bufs, self.params)     # .grad = the parameter's rows of the step buffer
         self.copy_stream = torch.cuda.Stream(dev)
         self.n_slots = rig.n_streams + 1
         self.slots = [dict(cam=torch.empty(38, device=dev), gt=torch.empty(3, H, W, device=dev),
@@ -390,7 +393,9 @@ class E2E:
         self.loss_fns = {"l1": l1_loss, "full": lambda c_, g_: photometric_loss(c_[None], g_[None], 0.2)[0]}
         self.loss_kind = "l1"
         from gaussian_splatting_lightning_b200.rasterizer import StepSink
-        self.sink = StepSink(rig.acc_into, rig.stat_into)
+        one = rig.bufs.num_chunks == 1
+        # chunk-major buffer (N > 1): the sink only parks the views; names of what it covers are all it needs
+        self.sink = StepSink(rig.bufs.grads(0), rig.bufs.densify_stats(0)) if not one else StepSink(rig.acc_into, rig.stat_into)
         self.h2d_bytes_per_step = vpr * (3 * H * W * 4 + 38 * 4)
         self.d2h_bytes_per_step = vpr * 4
 
@@ -442,9 +447,14 @@ class E2E:
             self.upload(j)
         rig.vstreams.run(rig.vpr, self.view)
         if rig.fused:
+            from gaussian_splatting_lightning_b200.view_parallel import fused_backward_and_exchange
             assert len(self.sink.pending) == rig.vpr      # every view parked: the pass may overwrite the buffer
-            self.sink.flush(overwrite=True)
-        if rig.world > 1:
+            p = self.params
+            fused_backward_and_exchange(self.sink.pending, dict(means3D=p["means3D"], shs=p["shs"], opacities=p["opacities"],
+                                                                scales=p["scales"], rotations=p["rotations"]),
+                                        rig.bufs, exchange=rig.world > 1, max_radii=False)
+            self.sink.pending = []
+        elif rig.world > 1:
             rig.bufs.all_reduce(max_radii=False)
         main.synchronize()                               # the step's result (losses) is on the host
         return float(self.loss_host.sum())
@@ -466,6 +476,11 @@ def neighbours(rig, e2e):
     from gaussian_splatting_lightning_b200.training import FusedAdam, densify_fold, fused_ssim, l1_loss
     device, P, H, W = rig.device, rig.P, rig.H, rig.W
     params, bufs = e2e.params, rig.bufs
+    if bufs.num_chunks > 1:      # the single-kernel measurements want whole-P gradient tensors
+        from gaussian_splatting_lightning_b200.training import parameter_groups_on
+        from gaussian_splatting_lightning_b200.view_parallel import StepBuffers
+        bufs = StepBuffers(P, rig.M, device)
+        parameter_groups_on(bufs, params)
     hbm_pk = peaks()[0]
     opt = FusedAdam([{"params": [params[k]], "lr": lr} for k, lr in
                      (("means3D", 1.6e-4), ("shs", 2.5e-3), ("opacities", 5e-2), ("scales", 5e-3), ("rotations", 1e-3))],

@@ -71,7 +71,7 @@ class GsrStateExport(C.Structure):
 # every symbol include/gsr_b200.h declares (tests check that the library exports them all)
 EXPORTED_SYMBOLS = [
     "gsr_version", "gsr_last_error", "gsr_geom_bytes", "gsr_img_bytes", "gsr_binning_bytes",
-    "gsr_backward_scratch_bytes", "gsr_forward", "gsr_backward", "gsr_preprocess_backward_views", "gsr_mark_visible", "gsr_export_state",
+    "gsr_backward_scratch_bytes", "gsr_forward", "gsr_backward", "gsr_preprocess_backward_views", "gsr_preprocess_backward_views_range", "gsr_mark_visible", "gsr_export_state",
     "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count", "gsr_profile_enable", "gsr_profile_reset",
     "gsr_profile_collect", "gsr_profile_stage_count", "gsr_profile_stage_name", "gsr_profile_stage_ms",
     "gsr_profile_stage_calls", "gsr_l1_loss_scratch_bytes", "gsr_l1_loss", "gsr_adam_step", "gsr_densify_fold", "gsr_fused_ssim_scratch_bytes",
@@ -118,6 +118,10 @@ def lib():
     L.gsr_preprocess_backward_views.restype = C.c_int
     L.gsr_preprocess_backward_views.argtypes = [C.POINTER(GsrViewState), C.c_int32, C.POINTER(GsrGaussians),
                                                 C.POINTER(GsrGrads), C.c_int32, C.POINTER(GsrDensifyStats), C.c_void_p]
+    L.gsr_preprocess_backward_views_range.restype = C.c_int
+    L.gsr_preprocess_backward_views_range.argtypes = [C.POINTER(GsrViewState), C.c_int32, C.POINTER(GsrGaussians),
+                                                      C.POINTER(GsrGrads), C.c_int32, C.POINTER(GsrDensifyStats),
+                                                      C.c_int32, C.c_int32, C.c_void_p]
     L.gsr_mark_visible.restype = C.c_int
     L.gsr_mark_visible.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.gsr_export_state.restype = C.c_int

@@ -344,6 +344,13 @@ int gsr_backward(const GsrSettings* settings, const GsrGaussians* gaussians, con
 
 int gsr_preprocess_backward_views(const GsrViewState* views, int32_t num_views, const GsrGaussians* gaussians,
                                   const GsrGrads* grads, int32_t flags, const GsrDensifyStats* stats, void* stream_) {
+  return gsr_preprocess_backward_views_range(views, num_views, gaussians, grads, flags, stats, 0,
+                                             gaussians ? gaussians->P : 0, stream_);
+}
+
+int gsr_preprocess_backward_views_range(const GsrViewState* views, int32_t num_views, const GsrGaussians* gaussians,
+                                        const GsrGrads* grads, int32_t flags, const GsrDensifyStats* stats,
+                                        int32_t first, int32_t count, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (!views || num_views < 0 || !grads) return fail(GSR_EINVAL, "preprocess_backward_views: bad arguments");
   if (flags & ~GSR_GRADS_ACCUMULATE) return fail(GSR_EINVAL, "preprocess_backward_views: unknown flag");
@@ -355,7 +362,8 @@ int gsr_preprocess_backward_views(const GsrViewState* views, int32_t num_views, 
   int rc = make_gaussians(gaussians, views[0].settings->sh_degree, &g);
   if (rc) return rc;
   const int P = g.P;
-  if (P == 0) return GSR_OK;
+  if (first < 0 || count < 0 || (long long)first + count > P) return fail(GSR_EINVAL, "preprocess_backward_views: range outside [0, P)");
+  if (P == 0 || count == 0) return GSR_OK;
   if (grads->dL_drotations && (reinterpret_cast<uintptr_t>(grads->dL_drotations) & 15))
     return fail(GSR_EINVAL, "dL_drotations must be 16-byte aligned");
   std::vector<GsrView> vv(num_views);
@@ -370,10 +378,20 @@ int gsr_preprocess_backward_views(const GsrViewState* views, int32_t num_views, 
     if (s.settings->sh_degree != views[0].settings->sh_degree || s.settings->scale_modifier != views[0].settings->scale_modifier ||
         (s.settings->antialiasing != 0) != (views[0].settings->antialiasing != 0))
       return fail(GSR_EINVAL, "preprocess_backward_views: the views must share sh_degree, scale_modifier and antialiasing");
-    radii[k] = s.radii;
+    radii[k] = s.radii + first;
     geoms[k] = GeomState::carve((char*)s.geom, P);
-    accs[k] = (const float*)s.scratch;
+    geoms[k].clamped += first;     // the geometry arrays the backward reads per Gaussian
+    geoms[k].cov3D += (size_t)first * 6;
+    accs[k] = (const float*)s.scratch + (size_t)first * 12;
   }
+  // the Gaussians of the range: every input pointer moves to the range's first row
+  g.P = count;
+  g.means3D += (size_t)first * 3; g.opacities += first;
+  if (g.shs) g.shs += (size_t)first * g.M * 3;
+  if (g.colors_precomp) g.colors_precomp += (size_t)first * 3;
+  if (g.scales) g.scales += (size_t)first * 3;
+  if (g.rotations) g.rotations += (size_t)first * 4;
+  if (g.cov3D_precomp) g.cov3D_precomp += (size_t)first * 6;
   gsr::PreBwdOut out;
   out.dL_dmeans2D = nullptr; out.dL_dcolors = grads->dL_dcolors; out.dL_dopacity = grads->dL_dopacity;
   out.dL_dmeans3D = grads->dL_dmeans3D; out.dL_dcov3D = grads->dL_dcov3D; out.dL_dsh = grads->dL_dsh;

@@ -294,7 +294,8 @@ std::vector<OptTensor> preprocess_backward_views(
     const std::vector<ViewTuple>& views, const Tensor& means3D, const OptTensor& colors, const Tensor& opacities,
     const OptTensor& scales, const OptTensor& rotations, double scale_modifier, const OptTensor& cov3D, const OptTensor& sh,
     int64_t degree, bool antialiasing, bool debug, int64_t want_mask, const std::vector<OptTensor>& accumulate_into,
-    const std::vector<OptTensor>& stats, bool overwrite) {
+    const std::vector<OptTensor>& stats, bool overwrite, int64_t first, int64_t count) {
+  // [first, first + count): the Gaussians this call covers (count < 0: all); outputs and statistics hold `count` rows
   // overwrite: the tensors of accumulate_into are WRITTEN (every row, zeros where no view saw the Gaussian) instead of
   // added to -- the step's buffer needs no clearing and the kernel no reductions at the L2
   TORCH_CHECK(!views.empty(), "preprocess_backward_views: no views");
@@ -317,7 +318,10 @@ std::vector<OptTensor> preprocess_backward_views(
   }
   const Frame& fr = frames[0];
   const c10::cuda::CUDAGuard guard(dev);
-  const int64_t P = fr.g.P, M = fr.g.M;
+  const int64_t Pall = fr.g.P, M = fr.g.M;
+  if (count < 0) { first = 0; count = Pall; }
+  TORCH_CHECK(first >= 0 && first + count <= Pall, "preprocess_backward_views: range outside [0, P)");
+  const int64_t P = count;
   auto fopt = torch::TensorOptions().dtype(torch::kFloat32).device(dev);
   const std::array<std::vector<int64_t>, NUM_GRADS> shapes = {{{P, 3}, {P, 3}, {P, 1}, {P, 3}, {P, 6}, {P, M, 3}, {P, 3}, {P, 4}}};
   std::vector<OptTensor> out(NUM_GRADS);
@@ -357,8 +361,9 @@ std::vector<OptTensor> preprocess_backward_views(
     }
   }
   cudaStream_t stream = at::cuda::getCurrentCUDAStream(dev.index()).stream();
-  check(gsr_preprocess_backward_views(vs.data(), (int32_t)vs.size(), &fr.g, &gr, (acc && !overwrite) ? GSR_GRADS_ACCUMULATE : 0,
-                                      have_stats ? &ds : nullptr, (void*)stream),
+  check(gsr_preprocess_backward_views_range(vs.data(), (int32_t)vs.size(), &fr.g, &gr,
+                                            (acc && !overwrite) ? GSR_GRADS_ACCUMULATE : 0, have_stats ? &ds : nullptr,
+                                            (int32_t)first, (int32_t)count, (void*)stream),
         "gsr_preprocess_backward_views");
   return out;
 }

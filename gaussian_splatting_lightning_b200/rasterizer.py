@@ -269,13 +269,14 @@ def backward_render_only(rs: GaussianRasterizationSettings, means3D, radii, sh, 
 
 
 def preprocess_backward_views(views, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                              want=None, accumulate_into=None, stats=None, overwrite=False):
+                              want=None, accumulate_into=None, stats=None, overwrite=False, first=0, count=None):
     """gsr_preprocess_backward_views: the preprocess backward of ALL views of a training step in one pass over the
     Gaussians.  views: sequence of (raster_settings, radii, geomBuffer, scratch), scratch from backward_render_only.
     Returns the 8-tuple of backward_raw with dL_dmeans2D = None (a per-view output); `want`, `accumulate_into` and
     `stats` as in backward_raw; overwrite=True WRITES the tensors of accumulate_into (every row; zeros where no view
     saw the Gaussian) instead of adding to them, so a step whose views all go through one call needs no cleared buffer
-    and no reductions at the L2.  The result equals the sum of per-view backward_raw calls up to float summation order;
+    and no reductions at the L2.  first / count restrict the pass to the Gaussians [first, first + count): outputs,
+    accumulate_into and stats then hold `count` rows (view_parallel.StepBuffers(chunks=...) exchanges range by range).  The result equals the sum of per-view backward_raw calls up to float summation order;
     the densification statistics are the per-view ones (norm taken per view, then summed)."""
     views = list(views)
     if not views:
@@ -295,14 +296,16 @@ def preprocess_backward_views(views, means3D, sh, colors_precomp, opacities, sca
         try:
             return tuple(ext.preprocess_backward_views(
                 vt, means3D, colors_precomp, opacities, scales, rotations, float(rs0.scale_modifier), cov3Ds_precomp, sh,
-                int(rs0.sh_degree), bool(rs0.antialiasing), bool(rs0.debug), mask, acc, st, bool(overwrite)))
+                int(rs0.sh_degree), bool(rs0.antialiasing), bool(rs0.debug), mask, acc, st, bool(overwrite), int(first),
+                -1 if count is None else int(count)))
         except RuntimeError as e:
             if "gsr_" in str(e):
                 raise N.GsrError(str(e)) from None
             raise
     frames = [_Frame(rs, means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp) for rs, *_ in views]
     fr = frames[0]
-    dev, P, M = fr.device, fr.P, fr.M
+    dev, Pall, M = fr.device, fr.P, fr.M
+    P = Pall - first if count is None else int(count)
     shapes = dict(dL_dmeans2D=(P, 3), dL_dcolors=(P, 3), dL_dopacity=(P, 1), dL_dmeans3D=(P, 3), dL_dcov3D=(P, 6),
                   dL_dsh=(P, M, 3), dL_dscales=(P, 3), dL_drotations=(P, 4))
     with torch.cuda.device(dev):
@@ -318,10 +321,10 @@ def preprocess_backward_views(views, means3D, sh, colors_precomp, opacities, sca
             for f, (_rs, radii, geom, scratch) in zip(frames, views)])
         grads = N.GsrGrads(*[N.ptr(t) for t in g.values()])
         ds = N.GsrDensifyStats(*[N.ptr(t) for t in st]) if st else None
-        N.check(N.lib().gsr_preprocess_backward_views(arr, len(views), C.byref(fr.gaussians), C.byref(grads),
-                                                      N.GSR_GRADS_ACCUMULATE if (accumulate_into is not None and not overwrite) else 0,
-                                                      C.byref(ds) if ds is not None else None, N.stream_ptr(dev)),
-                "gsr_preprocess_backward_views")
+        N.check(N.lib().gsr_preprocess_backward_views_range(
+            arr, len(views), C.byref(fr.gaussians), C.byref(grads),
+            N.GSR_GRADS_ACCUMULATE if (accumulate_into is not None and not overwrite) else 0,
+            C.byref(ds) if ds is not None else None, int(first), P, N.stream_ptr(dev)), "gsr_preprocess_backward_views")
     return tuple(g.values())
 
 

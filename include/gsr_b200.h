@@ -186,6 +186,13 @@ typedef struct GsrViewState {
 } GsrViewState;
 int gsr_preprocess_backward_views(const GsrViewState* views, int32_t num_views, const GsrGaussians* gaussians,
                                   const GsrGrads* grads, int32_t flags, const GsrDensifyStats* stats, void* stream);
+/* The same pass over the Gaussians [first, first + count) only.  `gaussians` and the views describe the whole set; the
+ * pointers of `grads` and `stats` address the RANGE's own rows (row 0 = Gaussian `first`), so that a step buffer laid out
+ * range by range can be exchanged range by range: the all-reduce of range c runs under the pass over range c + 1
+ * (view_parallel.StepBuffers(chunks=...)). */
+int gsr_preprocess_backward_views_range(const GsrViewState* views, int32_t num_views, const GsrGaussians* gaussians,
+                                        const GsrGrads* grads, int32_t flags, const GsrDensifyStats* stats,
+                                        int32_t first, int32_t count, void* stream);
 
 /* present[i] = ([p_i,1] @ viewmatrix).z > 0.2   (camera_tools.py:5-8). */
 int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, uint8_t* present,

@@ -413,3 +413,26 @@ def test_step_sink_defers_the_autograd_backward_to_one_fused_pass():
         img = render(pb, cams[0], sp)
     (img * dC[0]).sum().backward()
     assert not sink.pending and sp.grad is not None and float(sp.grad.abs().max()) > 0
+
+
+def test_chunked_fused_step_equals_the_unchunked_one():
+    """fused_backward_and_exchange over a chunk-major StepBuffers (the layout the pipelined exchange uses): the same
+    gradient rows and statistics as the whole-P pass, range by range (gsr_preprocess_backward_views_range)."""
+    from gaussian_splatting_lightning_b200.view_parallel import StepBuffers, render_step
+    P, deg, W, H, V = 9001, 3, 176, 112, 5
+    scene = {k: v.to(U.DEV) for k, v in U.synthetic.make_scene(P, deg, W, H, seed=12).items()}
+    cams = [U.settings_from_camera(U.synthetic_case(8, deg, W, H, view_k=k, num_views=8)[0]) for k in range(V)]
+    g = torch.Generator().manual_seed(2)
+    dC = [torch.randn(3, H, W, generator=g).to(U.DEV) for _ in range(V)]
+    a, b = StepBuffers(P, 16, U.DEV), StepBuffers(P, 16, U.DEV, chunks=4)
+    assert b.num_chunks == 4 and b.chunks[-1][0] + b.chunks[-1][1] == P
+    b._store.fill_(123.0)        # the pass overwrites every gradient row: stale contents must not survive
+    render_step(cams, scene, lambda k, c, d: dC[k], None, a, exchange=False)
+    render_step(cams, scene, lambda k, c, d: dC[k], None, b, exchange=False)
+    torch.cuda.synchronize()
+    for n in a.grads():
+        got = torch.cat([b.grads(c)[n] for c in range(b.num_chunks)])
+        s = max(1.0, float(a.grads()[n].abs().max()))
+        assert float((got - a.grads()[n]).abs().max()) / s <= 2e-5, n
+    assert torch.equal(torch.cat([b.densify_stats(c)["xyz_grad_count"] for c in range(4)]), a.stats[1])
+    assert torch.equal(b.max_radii, a.max_radii)

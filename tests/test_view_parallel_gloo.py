@@ -162,3 +162,64 @@ def test_bench_partitions_cover_the_same_views():
         slot = [bench.view_index(0, g, world * vpr) for g in range(world * vpr)]       # global view g -> orbit slot
         for r in range(world):
             assert inter[r] == [slot[g] for g in partition_views(world * vpr, world, r)]
+
+
+def _worker_chunked(rank: int, port: int, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=WORLD)
+    try:
+        P2 = 5000
+        buf = StepBuffers(P2, M, "cpu", chunks=3)
+        g = torch.Generator().manual_seed(77 + rank)
+        full = {n: torch.randn((P2, M, 3) if n == "dL_dsh" else (P2, w), generator=g) for n, w in buf.widths.items()}
+        radii = torch.randint(0, 50, (P2,), generator=g).float()
+        for c, (f, n) in enumerate(buf.chunks):
+            for name, t in buf.grads(c).items():
+                t.copy_(full[name][f:f + n])
+            st = buf.densify_stats(c)
+            st["xyz_grad_accum"].fill_(rank + 1.0)
+            st["xyz_grad_count"].fill_(1.0)
+            st["max_radii2D"].copy_(radii[f:f + n])
+        works = [buf.all_reduce_chunk(c, async_op=True) for c in range(buf.num_chunks)]
+        works.append(buf.all_reduce_max_radii(async_op=True))
+        for w in works:
+            w.wait()
+        got = {n: torch.cat([buf.grads(c)[n] for c in range(buf.num_chunks)]) for n in buf.widths}
+        out[rank] = dict(full=full, got=got, radii=radii, max_radii=buf.max_radii.clone(),
+                         accum=torch.cat([buf.densify_stats(c)["xyz_grad_accum"] for c in range(buf.num_chunks)]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_chunk_major_buffers_exchange_range_by_range():
+    """StepBuffers(chunks=C): every chunk is one contiguous, 128-byte aligned block [its gradient rows | its statistics];
+    all_reduce_chunk per chunk + the max of the radii give what the single all-reduce of the whole buffer gives."""
+    buf = StepBuffers(5000, 16, "cpu", chunks=3)
+    assert buf.chunks == [(0, 2048), (2048, 2048), (4096, 904)] and buf.num_chunks == 3
+    base = buf._store.data_ptr()
+    prev_end = 0
+    for c, (f, n) in enumerate(buf.chunks):
+        blk = buf._chunk_block[c]
+        assert (blk.data_ptr() - base) == 4 * prev_end and (blk.data_ptr() - base) % 128 == 0
+        prev_end += blk.numel()
+        for t in list(buf.grads(c).values()) + list(buf.densify_stats(c).values())[1:]:
+            assert t.is_contiguous() and (t.data_ptr() - base) % 128 == 0
+            assert blk.data_ptr() <= t.data_ptr() and t.data_ptr() + 4 * t.numel() <= blk.data_ptr() + 4 * blk.numel()
+        assert buf.grads(c)["dL_dsh"].shape == (n, 16, 3) and buf.densify_stats(c)["max_radii2D"].shape == (n,)
+    with pytest.raises(ValueError):
+        buf.grads()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker_chunked, args=(_free_port(), out), nprocs=WORLD, join=True)
+    for n in out[0]["full"]:
+        want = out[0]["full"][n] + out[1]["full"][n]
+        assert torch.allclose(out[0]["got"][n], want, atol=1e-6) and torch.equal(out[0]["got"][n], out[1]["got"][n])
+    assert torch.equal(out[0]["max_radii"], torch.maximum(out[0]["radii"], out[1]["radii"]))
+    assert torch.equal(out[0]["accum"], torch.full((5000,), 3.0))
+    # folding the chunked deltas into running statistics
+    mr, acc, cnt = torch.zeros(5000), torch.zeros(5000, 1), torch.zeros(5000, 1)
+    for c in range(buf.num_chunks):
+        st = buf.densify_stats(c)
+        st["xyz_grad_accum"].fill_(0.5); st["xyz_grad_count"].fill_(2.0); st["max_radii2D"].fill_(7.0)
+    buf.apply_densify_stats(mr, acc, cnt)
+    assert float(mr.min()) == 7.0 and float(acc.min()) == 0.5 and float(cnt.max()) == 2.0
