@@ -425,7 +425,7 @@ def test_chunked_fused_step_equals_the_unchunked_one():
     g = torch.Generator().manual_seed(2)
     dC = [torch.randn(3, H, W, generator=g).to(U.DEV) for _ in range(V)]
     a, b = StepBuffers(P, 16, U.DEV), StepBuffers(P, 16, U.DEV, chunks=4)
-    assert b.num_chunks == 4 and b.chunks[-1][0] + b.chunks[-1][1] == P
+    assert b.num_chunks == 3 and b.chunks[-1][0] + b.chunks[-1][1] == P     # boundaries on multiples of 1024 Gaussians
     b._store.fill_(123.0)        # the pass overwrites every gradient row: stale contents must not survive
     render_step(cams, scene, lambda k, c, d: dC[k], None, a, exchange=False)
     render_step(cams, scene, lambda k, c, d: dC[k], None, b, exchange=False)
@@ -434,5 +434,5 @@ def test_chunked_fused_step_equals_the_unchunked_one():
         got = torch.cat([b.grads(c)[n] for c in range(b.num_chunks)])
         s = max(1.0, float(a.grads()[n].abs().max()))
         assert float((got - a.grads()[n]).abs().max()) / s <= 2e-5, n
-    assert torch.equal(torch.cat([b.densify_stats(c)["xyz_grad_count"] for c in range(4)]), a.stats[1])
+    assert torch.equal(torch.cat([b.densify_stats(c)["xyz_grad_count"] for c in range(b.num_chunks)]), a.stats[1])
     assert torch.equal(b.max_radii, a.max_radii)
