@@ -29,7 +29,7 @@ SOURCES = {
     "tile_binning.cu": ["-fmad=false"],
     "radix_sort.cu": [],
     "render_forward.cu": [],
-    "render_backward.cu": [],
+    "render_backward.cu": os.environ.get("GSR_BWD_FLAGS", "").split(),
     "preprocess_backward.cu": ["--use_fast_math"],   # gradients only (1e-4 contract): contraction, approximate div / sqrt
     "loss.cu": [],
     "optimizer.cu": ["-fmad=false"],

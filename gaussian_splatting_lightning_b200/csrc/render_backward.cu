@@ -32,27 +32,67 @@
 //     ONE red.global.add.f32 instruction into the 48-byte-per-Gaussian accumulator rows -- 1/64 of the atomics of
 //     the per-pixel scheme.  Measured against a recursive-halving shuffle reduction (12 shuffles + 22 selects + 12
 //     adds per visit): 0.873 -> 0.850 ms; a hybrid (one shuffle level, then shared memory) was slower (0.900 ms).
+#ifdef GSR_BWD_BATCH
+#define GSR_BATCH GSR_BWD_BATCH
+#endif
+#ifndef GSR_BWD_CTAS
+#define GSR_BWD_CTAS 7
+#endif
 #include "gsr_common.cuh"
 #include "render_common.cuh"
 
+// GSR_BWD_PERWARP (default): every warp runs its own double-buffered pipeline over the tile's list, chunk of 32 entries by
+// chunk, staging ONLY the entries its hit words name -- no CTA barrier anywhere.  The r2_v9 source-level capture had 10 %
+// of all warp samples parked at the per-batch __syncthreads (the four warps of a tile see very different numbers of
+// hits).  0: the CTA-wide batches of GSR_BATCH entries.
+#ifndef GSR_BWD_PERWARP
+#define GSR_BWD_PERWARP 1
+#endif
+// GSR_BWD_WARP_CTA (with GSR_BWD_PERWARP): one warp per CTA, four CTAs per tile.  Only ~1.5 of a tile's 4 warps have work
+// on a given entry; as single-warp CTAs the idle ones retire at once and their slots go to warps that still work.
+#ifndef GSR_BWD_WARP_CTA
+#define GSR_BWD_WARP_CTA 1
+#endif
+#if GSR_BWD_PERWARP && GSR_BWD_WARP_CTA
+#define GSR_BWD_THREADS 32
+#else
+#define GSR_BWD_THREADS 128
+#endif
+#define GSR_BWD_WARPS (GSR_BWD_THREADS / 32)
+#if GSR_BWD_PERWARP
+#define GSR_BWD_PLANE 512        /* 32 entries x 16 bytes */
+#else
+#define GSR_BWD_PLANE GSR_PLANE
+#endif
+
 namespace gsr {
 
-__global__ void __launch_bounds__(128, 7) render_backward_kernel(
+__global__ void __launch_bounds__(GSR_BWD_THREADS, GSR_BWD_CTAS * (128 / GSR_BWD_THREADS)) render_backward_kernel(
     const GsrView v, const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
     const char* __restrict__ binning,
     const GsrRec* __restrict__ recs, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
     const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth, float* __restrict__ grad_acc) {
+#if GSR_BWD_PERWARP
+  __shared__ float4 sRec[GSR_BWD_WARPS][2][3][32];          // [warp][buffer][plane 0-2 of render_common.cuh][entry of the chunk]
+#else
   __shared__ float4 sRec[2][3][GSR_BATCH];      // two staged batches, planes 0-2 of render_common.cuh
   __shared__ uint32_t sHit[2][GSR_BATCH / 32][8];   // [buffer][chunk of the batch][sub-tile column]
   __shared__ uint32_t s_warp_max[4];
+#endif
   // reduction over the warp's lanes by transposition through shared memory: RED_STRIDE = 36 floats per row keeps the
   // rows 16-byte aligned and the 128-bit row reads of a quarter warp on 32 distinct banks
   constexpr int RED_STRIDE = 36;
-  __shared__ __align__(16) float sRed[4][30 * RED_STRIDE];
-  __shared__ uint32_t sRedId[4][4];
+  __shared__ __align__(16) float sRed[GSR_BWD_WARPS][30 * RED_STRIDE];
+  __shared__ uint32_t sRedId[GSR_BWD_WARPS][4];
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tile = tile_order ? (int)tile_order[blockIdx.x] : (int)blockIdx.x;
+#if GSR_BWD_THREADS == 32
+  const int lane = threadIdx.x, warp = blockIdx.x & 3, wslot = 0;      // the tile's warp = the CTA; its shared-memory slot 0
+  const int tile_slot = blockIdx.x >> 2;
+#else
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, wslot = warp;
+  const int tile_slot = blockIdx.x;
+#endif
+  const int tile = tile_order ? (int)tile_order[tile_slot] : tile_slot;
   const int tx = tile % v.gx, ty = tile / v.gx;
   const int sx0 = tx * GSR_TILE + (warp & 1) * 8, sy0 = ty * GSR_TILE + (warp >> 1) * 8;
   const int pxi = sx0 + (lane & 7), pyA = sy0 + (lane >> 3), pyB = pyA + 4;
@@ -61,10 +101,10 @@ __global__ void __launch_bounds__(128, 7) render_backward_kernel(
   const int colA = (warp >> 1) * 4 + (warp & 1), colB = colA + 2;
   const uint2 range = ranges[tile];
   // shared-memory addresses the hit loop uses, pinned in registers (keep_u32)
-  const uint32_t aRed = (uint32_t)__cvta_generic_to_shared(sRed[warp]);
+  const uint32_t aRed = (uint32_t)__cvta_generic_to_shared(sRed[wslot]);
   const uint32_t aPark0 = keep_u32(aRed + (uint32_t)lane * 4u);                       // column of this lane, slot 0
   const uint32_t aRow = keep_u32(aRed + (uint32_t)lane * (RED_STRIDE * 4u));           // row this lane adds at a flush
-  const uint32_t aId = keep_u32((uint32_t)__cvta_generic_to_shared(sRedId[warp]));
+  const uint32_t aId = keep_u32((uint32_t)__cvta_generic_to_shared(sRedId[wslot]));
   const int red_visit = lane / 10, red_sum = lane - red_visit * 10;   // the row lane `lane` adds at a flush
   float* const acc_col = grad_acc + red_sum;
   const uint32_t aIdMine = keep_u32(aId + (uint32_t)red_visit * 4u);
@@ -130,12 +170,16 @@ __global__ void __launch_bounds__(128, 7) render_backward_kernel(
   const float npyA = -(float)pyA, npyB = -(float)pyB;
 
   const uint32_t warp_last = __reduce_max_sync(0xffffffffu, max(lastA, lastB));
+#if GSR_BWD_PERWARP
+  if (warp_last == 0) return;      // the warps of a tile are independent: no barrier follows
+#else
   if (lane == 0) s_warp_max[warp] = warp_last;
   __syncthreads();
   uint32_t max_last = 0;
 #pragma unroll
   for (int w = 0; w < 4; ++w) max_last = max(max_last, s_warp_max[w]);
   if (max_last == 0) return;
+#endif
 
   float nTA = -TfA, nTB = -TfB;                                  // -T
   float nar0A = 0.f, nar1A = 0.f, nar2A = 0.f, nar3A = 0.f;      // -(colour / inverse depth accumulated behind the splat)
@@ -172,6 +216,52 @@ __global__ void __launch_bounds__(128, 7) render_backward_kernel(
     s6 = w * dp0##S; s7 = w * dp1##S; s8 = w * dp2##S; s9 = w * dp3##S;                                  \
   }
 
+#if GSR_BWD_PERWARP
+  // The warp's own pipeline, from the chunk holding its last contributor down to chunk 0.  Per chunk: the two hit
+  // words of the warp's sub-tiles and the lane's list entry are loaded two chunks ahead (plain loads), the records of the
+  // entries the words name are copied one chunk ahead (three 16-byte cp.async by the lane whose bit is set) into the
+  // warp's other buffer, and the current chunk is replayed from shared memory.  __syncwarp is the only synchronisation.
+  const uint32_t* __restrict__ plist = point_list + range.x;
+  const uint32_t nlist = range.y - range.x;
+  const uint32_t aW = keep_u32(aRec + (uint32_t)wslot * (2u * 3u * GSR_BWD_PLANE));
+  const uint32_t aMineW = aW + (uint32_t)lane * 16u;
+  auto issue_chunk = [&](int buf, uint32_t m, uint32_t gidx) {
+    if ((m >> lane) & 1u) {
+      const GsrRec* r = recs + gidx;
+      const uint32_t dst = aMineW + (uint32_t)buf * (3u * GSR_BWD_PLANE);
+      cp_async16(dst, &r->a);
+      cp_async16(dst + GSR_BWD_PLANE, &r->b);
+      cp_async16(dst + 2 * GSR_BWD_PLANE, &r->c);
+    }
+    cp_async_commit();
+  };
+  int c = (int)((warp_last - 1u) >> 5);
+  uint32_t maskA = hit_rows[(size_t)c * 8 + colA], maskB = hit_rows[(size_t)c * 8 + colB];
+  {
+    const uint32_t e = (uint32_t)c * 32u + (uint32_t)lane;
+    issue_chunk(0, maskA | maskB, e < nlist ? plist[e] : 0u);
+  }
+  uint32_t nA = 0, nB = 0, nidx = 0;      // chunk c - 1
+  if (c > 0) {
+    nA = hit_rows[(size_t)(c - 1) * 8 + colA]; nB = hit_rows[(size_t)(c - 1) * 8 + colB];
+    nidx = plist[(uint32_t)(c - 1) * 32u + (uint32_t)lane];
+  }
+  for (int k = 0; c >= 0; --c, ++k) {
+    const int base = c * 32;
+    cp_async_wait_all();     // this lane's copies of chunk c have landed ...
+    __syncwarp();            // ... every lane's have, and the warp is done with the other buffer
+    uint32_t tA = 0, tB = 0, tidx = 0;     // chunk c - 2
+    if (c > 0) {
+      issue_chunk((k + 1) & 1, nA | nB, nidx);
+      if (c > 1) {
+        tA = hit_rows[(size_t)(c - 2) * 8 + colA]; tB = hit_rows[(size_t)(c - 2) * 8 + colB];
+        tidx = plist[(uint32_t)(c - 2) * 32u + (uint32_t)lane];
+      }
+    }
+    const uint32_t aBuf = keep_u32(aW + (uint32_t)(k & 1) * (3u * GSR_BWD_PLANE));
+    {
+      const int c0 = 0;
+#else
   // Batches of GSR_BATCH entries from the back of the list, double buffered (render_common.cuh): a thread copies ONE
   // entry per batch (three 16-byte cp.async from the entry's record; its Gaussian index was loaded a batch earlier) and
   // the first 32 threads one hit word each, so the copies of the next batch are in flight while the warps replay this
@@ -182,7 +272,7 @@ __global__ void __launch_bounds__(128, 7) render_backward_kernel(
   const uint32_t aHit = (uint32_t)__cvta_generic_to_shared(sHit);
   const uint32_t aHitA = keep_u32(aHit + (uint32_t)colA * 4u);   // column A of chunk 0, buffer 0 (column B = +8 bytes)
   auto issue = [&](int b, int k, uint32_t gidx) {     // batch b (entries b * GSR_BATCH ...) into buffer k & 1
-    if (b * GSR_BATCH + tid < (int)max_last) {
+    if (tid < GSR_BATCH && b * GSR_BATCH + tid < (int)max_last) {
       const GsrRec* r = recs + gidx;
       const uint32_t dst = aMine + (uint32_t)(k & 1) * (3u * GSR_PLANE);
       cp_async16(dst, &r->a);
@@ -198,8 +288,8 @@ __global__ void __launch_bounds__(128, 7) render_backward_kernel(
   uint32_t gnext = 0;
   {
     const int e0 = (nb - 1) * GSR_BATCH + tid;
-    issue(nb - 1, 0, e0 < (int)max_last ? plist[e0] : 0u);
-    if (nb > 1) gnext = plist[(nb - 2) * GSR_BATCH + tid];
+    issue(nb - 1, 0, (tid < GSR_BATCH && e0 < (int)max_last) ? plist[e0] : 0u);
+    if (nb > 1 && tid < GSR_BATCH) gnext = plist[(nb - 2) * GSR_BATCH + tid];
   }
   for (int b = nb - 1, k = 0; b >= 0; --b, ++k) {
     const int base = b * GSR_BATCH;
@@ -208,7 +298,7 @@ __global__ void __launch_bounds__(128, 7) render_backward_kernel(
     __syncthreads();         // ... everybody's have, and buffer (k + 1) & 1 (read by the previous batch) is free
     if (b > 0) {
       issue(b - 1, k + 1, gnext);
-      if (b > 1) gnext = plist[(b - 2) * GSR_BATCH + tid];
+      if (b > 1 && tid < GSR_BATCH) gnext = plist[(b - 2) * GSR_BATCH + tid];
     }
     if ((int)warp_last <= base) continue;  // nothing in this batch reaches the warp's pixels
     const uint32_t aBuf = keep_u32(aRec + (uint32_t)(k & 1) * (3u * GSR_PLANE));
@@ -216,6 +306,7 @@ __global__ void __launch_bounds__(128, 7) render_backward_kernel(
 
     for (int c0 = ((min(cnt, (int)warp_last - base) - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
       const uint32_t maskA = lds32u<0>(aHitBuf + (uint32_t)c0), maskB = lds32u<8>(aHitBuf + (uint32_t)c0);  // (c0 / 32) * 32 B
+#endif
       uint32_t mask = maskA | maskB;
       const uint32_t both = maskA & maskB;
       while (mask) {
@@ -226,8 +317,8 @@ __global__ void __launch_bounds__(128, 7) render_backward_kernel(
         const uint32_t idx = (uint32_t)(base + j);
         const uint32_t addr = aBuf + (uint32_t)j * 16u;
         const float4 ra = lds128<0>(addr);                    // {mean.x, mean.y, hA, hB}
-        const float4 rb = lds128<GSR_PLANE>(addr);            // {hC, -opacity, r, g}
-        const float4 rc = lds128<2 * GSR_PLANE>(addr);        // {b, 1/z, tau2, bits(gaussian id)}
+        const float4 rb = lds128<GSR_BWD_PLANE>(addr);            // {hC, -opacity, r, g}
+        const float4 rc = lds128<2 * GSR_BWD_PLANE>(addr);        // {b, 1/z, tau2, bits(gaussian id)}
         const float mx = ra.x, my = ra.y, hA = ra.z, hB = ra.w, hC = rb.x, no = rb.y, cr = rb.z, cg = rb.w, cb = rc.x,
                     iz = rc.y;
         const float dx = mx - pxf;
@@ -311,6 +402,9 @@ __global__ void __launch_bounds__(128, 7) render_backward_kernel(
         }
       }
     }
+#if GSR_BWD_PERWARP
+    maskA = nA; maskB = nB; nA = tA; nB = tB; nidx = tidx;
+#endif
   }
   if (nslot) GSR_BWD_FLUSH()
   cp_async_wait_all();
@@ -324,7 +418,7 @@ cudaError_t launch_render_backward(const GsrView& v, const uint2* ranges, const 
                                    const float* dL_dinvdepth, float* grad_acc, cudaStream_t s) {
   const int tiles = v.gx * v.gy;
   if (tiles <= 0) return cudaSuccess;
-  render_backward_kernel<<<tiles, 128, 0, s>>>(v, ranges, tile_order, (const char*)binning, recs, final_T, n_contrib, dL_dpix,
+  render_backward_kernel<<<tiles * (128 / GSR_BWD_THREADS), GSR_BWD_THREADS, 0, s>>>(v, ranges, tile_order, (const char*)binning, recs, final_T, n_contrib, dL_dpix,
                                                dL_dinvdepth, grad_acc);
   count_launch();
   return cudaGetLastError();

@@ -144,7 +144,9 @@ __device__ __forceinline__ f32x2 lds1x64(uint32_t addr) {
 // alpha T = (-alpha)(-T): exact, and no packed negation exists).  The packed instructions take a scalar register as a
 // broadcast operand (SASS `R.F32`), so per-splat values need no duplication: pk2(v, v) costs nothing.
 // Two buffers: the copies of batch b + 1 are in flight while the warps composite batch b (ONE barrier per batch).
+#ifndef GSR_BATCH
 #define GSR_BATCH 128
+#endif
 #define GSR_PLANE (GSR_BATCH * 16)
 
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gmem) {
