@@ -33,9 +33,26 @@
 #include "gsr_common.cuh"
 #include "render_common.cuh"
 
+// GSR_FWD_PERWARP = 1 (measured, NOT the default): one warp per CTA, four CTAs per tile, the warp staging the tile's list
+// itself chunk of 32 entries by chunk -- the change that took render_backward from 0.744 to 0.698 ms.  Here every entry
+// has to be staged by each of the tile's four warps (the culling test needs all of them, the backward stages only what
+// its hit words name): 4 x the L2 -> shared traffic, 0.374 -> 0.410 ms on C3.  Default 0: CTA-wide batches of GSR_BATCH.
+#ifndef GSR_FWD_PERWARP
+#define GSR_FWD_PERWARP 0
+#endif
+#if GSR_FWD_PERWARP
+#define GSR_FWD_THREADS 32
+#define GSR_FWD_PLANE 512          /* 32 entries x 16 bytes */
+#define GSR_FWD_MINCTAS 32
+#else
+#define GSR_FWD_THREADS 128
+#define GSR_FWD_PLANE GSR_PLANE
+#define GSR_FWD_MINCTAS 9
+#endif
+
 namespace gsr {
 
-__global__ void __launch_bounds__(128, 9) render_forward_kernel(const GsrView v, const uint2* __restrict__ ranges,
+__global__ void __launch_bounds__(GSR_FWD_THREADS, GSR_FWD_MINCTAS) render_forward_kernel(const GsrView v, const uint2* __restrict__ ranges,
                                                              const uint32_t* __restrict__ tile_order,
                                                              const uint32_t* __restrict__ point_list,
                                                              const GsrRec* __restrict__ recs,
@@ -44,10 +61,16 @@ __global__ void __launch_bounds__(128, 9) render_forward_kernel(const GsrView v,
                                                              float* __restrict__ final_T,
                                                              uint32_t* __restrict__ n_contrib,
                                                              uint32_t* __restrict__ hits) {
+#if GSR_FWD_PERWARP
+  __shared__ float4 sRec[2][4][32];         // the warp's two staged chunks of four planes; plane 3 = cull plane
+  const int lane = threadIdx.x, warp = blockIdx.x & 3;
+  const int tile_slot = blockIdx.x >> 2;
+#else
   __shared__ float4 sRec[2][4][GSR_BATCH];  // two staged batches of four planes (render_common.cuh); plane 3 = cull plane
-
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tile = tile_order ? (int)tile_order[blockIdx.x] : (int)blockIdx.x;
+  const int tile_slot = blockIdx.x;
+#endif
+  const int tile = tile_order ? (int)tile_order[tile_slot] : tile_slot;
   const int tx = tile % v.gx, ty = tile / v.gx;
   // warp -> 8x8 block = sub-tiles A (upper 8x4) and B (lower 8x4); lane -> one pixel in each
   const int sx0 = tx * GSR_TILE + (warp & 1) * 8, sy0 = ty * GSR_TILE + (warp >> 1) * 8;
@@ -93,6 +116,47 @@ __global__ void __launch_bounds__(128, 9) render_forward_kernel(const GsrView v,
     ok##S##_bits |= ok ? bitm : 0u;                                                         \
   }
 
+#if GSR_FWD_PERWARP
+  const int nchunk = (n + 31) >> 5;
+  const uint32_t* __restrict__ plist = point_list + range.x;
+  const uint32_t aMine = aRec + (uint32_t)lane * 16u;
+  auto issue = [&](int c, uint32_t gidx) {                      // stage entry c * 32 + lane into buffer c & 1
+    const uint32_t dst = aMine + (uint32_t)(c & 1) * (4u * GSR_FWD_PLANE);
+    if (c * 32 + lane < n) {
+      const GsrRec* r = recs + gidx;
+      cp_async16(dst, &r->a);
+      cp_async16(dst + GSR_FWD_PLANE, &r->b);
+      cp_async16(dst + 2 * GSR_FWD_PLANE, &r->c);
+      cp_async16(dst + 3 * GSR_FWD_PLANE, &r->d);
+    } else {
+      // padding: never a hit.  The geometry planes the culling test reads are zeroed too: stale shared memory
+      // (another kernel's data) may hold -inf / NaN patterns, and -inf <= -inf would let a padded entry pass.
+      sts128(dst, 0.f, 0.f, 0.f, 0.f);
+      sts128(dst + GSR_FWD_PLANE, 0.f, 0.f, 0.f, 0.f);
+      sts128(dst + 3 * GSR_FWD_PLANE, 0.f, 0.f, NEG_INF, 0.f);
+    }
+    cp_async_commit();
+  };
+  uint32_t gnext = 0;
+  if (nchunk > 0) {
+    issue(0, lane < n ? plist[lane] : 0u);
+    if (32 + lane < n) gnext = plist[32 + lane];
+  }
+  for (int c = 0; c < nchunk; ++c) {
+    const int base = c * 32;
+    cp_async_wait_all();     // this lane's copies of chunk c have landed ...
+    __syncwarp();            // ... every lane's have, and the warp is done with the other buffer
+    if (c + 1 < nchunk) {
+      issue(c + 1, gnext);
+      if (base + 64 + lane < n) gnext = plist[base + 64 + lane];
+    }
+    const uint32_t aBuf = aRec + (uint32_t)(c & 1) * (4u * GSR_FWD_PLANE);
+    const float4* sGeo = &sRec[c & 1][0][0];
+    const float4* sHC = &sRec[c & 1][1][0];
+    const float4* sCull = &sRec[c & 1][3][0];
+    {
+      const int c0 = 0;
+#else
   // Batches of GSR_BATCH entries, double buffered: a thread copies ONE entry per batch (four 16-byte cp.async from the
   // entry's 64-byte record, whose Gaussian index it loaded a batch earlier), so the copies of batch b + 1 and the index
   // loads of batch b + 2 are in flight while the warps composite batch b; one barrier per batch.
@@ -137,6 +201,7 @@ __global__ void __launch_bounds__(128, 9) render_forward_kernel(const GsrView v,
     const float4* sCull = &sRec[b & 1][3][0];
 
     for (int c0 = 0; c0 < cnt; c0 += 32) {
+#endif
       // one splat per lane against the warp's two sub-tiles
       const float4 geo = sGeo[c0 + lane], cull = sCull[c0 + lane];   // {mean.x, mean.y, hA, hB}, {kx, ky, tauM, -}
       const float hCl = sHC[c0 + lane].x;
@@ -153,8 +218,8 @@ __global__ void __launch_bounds__(128, 9) render_forward_kernel(const GsrView v,
         mask ^= bitm;
         const uint32_t addr = aBuf + (uint32_t)(c0 + bit) * 16u;
         const float4 ra = lds128<0>(addr);                    // {mean.x, mean.y, hA, hB}
-        const float4 rb = lds128<GSR_PLANE>(addr);            // {hC, -opacity, r, g}
-        const float2 rc = lds64<2 * GSR_PLANE>(addr);         // {b, 1/z}
+        const float4 rb = lds128<GSR_FWD_PLANE>(addr);            // {hC, -opacity, r, g}
+        const float2 rc = lds64<2 * GSR_FWD_PLANE>(addr);         // {b, 1/z}
         const float mx = ra.x, my = ra.y, hA = ra.z, hB = ra.w, hC = rb.x, no = rb.y, cr = rb.z, cg = rb.w, cb = rc.x,
                     iz = rc.y;
         // e = hA dx^2 + hC dy^2 + hB dx dy, per pixel exactly quad_form()'s rounding sequence
@@ -238,7 +303,7 @@ cudaError_t launch_render_forward(const GsrView& v, const uint2* ranges, const u
                                   float* final_T, uint32_t* n_contrib, uint32_t* hits, cudaStream_t s) {
   const int tiles = v.gx * v.gy;
   if (tiles <= 0) return cudaSuccess;
-  render_forward_kernel<<<tiles, 128, 0, s>>>(v, ranges, tile_order, point_list, recs, out_color, out_invdepth, final_T,
+  render_forward_kernel<<<tiles * (128 / GSR_FWD_THREADS), GSR_FWD_THREADS, 0, s>>>(v, ranges, tile_order, point_list, recs, out_color, out_invdepth, final_T,
                                               n_contrib, hits);
   count_launch();
   return cudaGetLastError();
