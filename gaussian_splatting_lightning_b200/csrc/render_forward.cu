@@ -68,9 +68,10 @@ __global__ void __launch_bounds__(GSR_FWD_THREADS, GSR_FWD_MINCTAS) render_forwa
 #else
   __shared__ float4 sRec[2][4][GSR_BATCH];  // two staged batches of four planes (render_common.cuh); plane 3 = cull plane
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tile_slot = blockIdx.x;
+#define tile_slot blockIdx.x
 #endif
-  const int tile = tile_order ? (int)tile_order[tile_slot] : tile_slot;
+  const int tile = tile_order ? (int)tile_order[tile_slot] : (int)tile_slot;
+#undef tile_slot
   const int tx = tile % v.gx, ty = tile / v.gx;
   // warp -> 8x8 block = sub-tiles A (upper 8x4) and B (lower 8x4); lane -> one pixel in each
   const int sx0 = tx * GSR_TILE + (warp & 1) * 8, sy0 = ty * GSR_TILE + (warp >> 1) * 8;
