@@ -401,7 +401,8 @@ int gsr_preprocess_backward_views_range(const GsrViewState* views, int32_t num_v
   out.xyz_grad_accum = stats ? stats->xyz_grad_accum : nullptr;
   out.xyz_grad_count = stats ? stats->xyz_grad_count : nullptr;
   const bool debug = views[0].settings->debug != 0;
-  if (gsr::preprocess_backward_views_supported(g, out)) {
+  // (a single view: the per-view kernel -- one thread per Gaussian, SH block by bulk copy -- is the better shape)
+  if (num_views > 1 && gsr::preprocess_backward_views_supported(g, out)) {
     GSR_STAGE(ST_PREPROCESS_BWD, gsr::launch_preprocess_backward_views(num_views, vv.data(), radii.data(), geoms.data(),
                                                                        accs.data(), g, out, stream),
               "preprocess backward kernel (all views)", debug, stream);
