@@ -803,7 +803,7 @@ def headline(args, rig, counters, prof, clocks, value, fwd_value, ms_total, ms_f
                    "parallelism": f"view-parallel x{world}", "partition": args.partition,
                    "ffi": ffi_name(),
                    "preprocess_backward": "one fused pass per step over all views" if rig.fused else "per view",
-                   "l2": (lambda mb: f"inputs ({mb:.0f} MB of Gaussian parameters + {48 * P / 1e6:.0f} MB records) "
+                   "l2": (lambda mb: f"inputs ({mb:.0f} MB of Gaussian parameters + {64 * P / 1e6:.0f} MB records) "
                           + ("exceed the 126 MB L2; no flush" if mb > 126 else
                              "fit the 126 MB L2: a parity-test size, not a bench line"))((44 + 12 * M) * P / 1e6),
                    "num_rendered_mean": counters["R"], "visible_mean": counters["Pvis"],
