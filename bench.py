@@ -219,7 +219,9 @@ def stage_model(P, M, Pvis, R, L, A, HW, T, passes):
 # which roofline bounds a stage: the compositing kernels are bound by FP32 instruction issue, the
 # per-Gaussian kernels by HBM bytes, the binning stages by latency / L2 transactions (reported against HBM bytes)
 STAGE_BOUND = {"render_forward": "fp32_issue", "render_backward": "fp32_issue"}
-EXCHANGE_CHUNKS = 4      # Gaussian ranges the fused step backward + all-reduce are pipelined over (N > 1)
+EXCHANGE_CHUNKS = int(os.environ.get("GSR_EXCHANGE_CHUNKS", "1"))   # Gaussian ranges the fused step backward + all-reduce are pipelined over (N > 1).
+# Measured on 8 B200 (C3, 248 MB per step): 1 chunk 11.29 ms per step, 2: 11.39, 4: 11.49, 8: 11.59 -- the smaller collectives lose
+# more than the overlap with the fused pass (0.77 ms) wins; on 2 GPUs 4 chunks won 0.08 ms.  Default: one collective.
 DENSIFY_INTERVAL = 100   # gs_lightning/lightning/gs_lightning_module.py:32,198: densification reads max_radii2D every 100 steps
 NCU_COUNTS = os.path.join(ROOT, "profiles", "ncu_counts.json")   # per-launch counters of the committed ncu capture
 
