@@ -72,7 +72,7 @@ class GsrStateExport(C.Structure):
 EXPORTED_SYMBOLS = [
     "gsr_version", "gsr_last_error", "gsr_geom_bytes", "gsr_img_bytes", "gsr_binning_bytes",
     "gsr_backward_scratch_bytes", "gsr_forward", "gsr_backward", "gsr_preprocess_backward_views", "gsr_preprocess_backward_views_range", "gsr_mark_visible", "gsr_export_state",
-    "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count", "gsr_profile_enable", "gsr_profile_reset",
+    "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count", "gsr_set_binning", "gsr_get_binning", "gsr_profile_enable", "gsr_profile_reset",
     "gsr_profile_collect", "gsr_profile_stage_count", "gsr_profile_stage_name", "gsr_profile_stage_ms",
     "gsr_profile_stage_calls", "gsr_l1_loss_scratch_bytes", "gsr_l1_loss", "gsr_adam_step", "gsr_densify_fold", "gsr_fused_ssim_scratch_bytes",
     "gsr_fused_ssim", "gsr_photometric_loss",
@@ -184,6 +184,15 @@ def ext():
         warnings.warn(f"{EXT_PATH} has not been built (python -m gaussian_splatting_lightning_b200.build); "
                       "using the ctypes binding of libgsr_b200.so")
     return _ext
+
+
+def set_binning(mode: str) -> None:
+    """'tile' (default: tile-segmented binning) or 'onesweep' (global radix sort); process-wide, at run time."""
+    check(lib().gsr_set_binning({"tile": 0, "onesweep": 1}[mode]), "gsr_set_binning")
+
+
+def get_binning() -> str:
+    return ("tile", "onesweep")[int(lib().gsr_get_binning())]
 
 
 def profile_enable(on: bool) -> None:

@@ -95,12 +95,18 @@ thread_local Mailbox g_mail[MAX_DEVICES];
 
 // Which binning the forward runs: tile-segmented (tile_binning.cu, default) or the global onesweep
 // radix sort (GSR_BINNING=onesweep; kept for A/B measurements and as the gsr_sort_pairs primitive).
+// Which binning the forward runs: tile-segmented (tile_binning.cu, default) or the global onesweep radix sort (kept for
+// A/B measurements and as the gsr_sort_pairs primitive).  Initial value from GSR_BINNING=onesweep; gsr_set_binning() changes
+// it at run time (process-wide; forward, backward and export of a frame must see the same mode).
+std::atomic<int> g_binning{-1};
 bool binning_segmented() {
-  static const bool seg = [] {
+  int m = g_binning.load(std::memory_order_relaxed);
+  if (m < 0) {
     const char* e = getenv("GSR_BINNING");
-    return !(e && strcmp(e, "onesweep") == 0);
-  }();
-  return seg;
+    m = (e && strcmp(e, "onesweep") == 0) ? GSR_BINNING_ONESWEEP : GSR_BINNING_TILE;
+    g_binning.store(m, std::memory_order_relaxed);
+  }
+  return m == GSR_BINNING_TILE;
 }
 
 int get_mailbox(Mailbox** out) {
@@ -172,6 +178,12 @@ extern "C" {
 const char* gsr_version(void) { return "gsr_b200 0.1 sm_100a"; }
 const char* gsr_last_error(void) { return g_err.c_str(); }
 int64_t gsr_launch_count(void) { return (int64_t)g_launches.load(); }
+int gsr_set_binning(int32_t mode) {
+  if (mode != GSR_BINNING_TILE && mode != GSR_BINNING_ONESWEEP) return fail(GSR_EINVAL, "set_binning: unknown mode");
+  g_binning.store(mode, std::memory_order_relaxed);
+  return GSR_OK;
+}
+int32_t gsr_get_binning(void) { return binning_segmented() ? GSR_BINNING_TILE : GSR_BINNING_ONESWEEP; }
 
 size_t gsr_geom_bytes(int32_t P) { return GeomState::carve(nullptr, P).bytes; }
 size_t gsr_img_bytes(int32_t W, int32_t H) { return ImgState::carve(nullptr, W, H).bytes; }

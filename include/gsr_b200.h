@@ -148,7 +148,7 @@ size_t gsr_backward_scratch_bytes(int32_t P);
 /* Forward: preprocess (+ per-tile instance counts) -> tile scan (ranges) -> scatter of the
  * (depth, index) composites into the tile segments -> per-tile sort -> compositing; the lists
  * equal those of a global stable sort of (tile << 32 | depth, index) pairs.  With the
- * environment variable GSR_BINNING=onesweep (read once per process): preprocess -> scan ->
+ * environment variable GSR_BINNING=onesweep or gsr_set_binning(GSR_BINNING_ONESWEEP): preprocess -> scan ->
  * duplicate keys -> onesweep radix sort -> tile ranges -> compositing.  Writes out_color (3,H,W), radii (P) int32, out_invdepth (1,H,W).
  *
  * binning_hint = 0 reproduces upstream's behaviour: one blocking read of num_rendered
@@ -268,6 +268,15 @@ int gsr_adam_step(const GsrAdamGroup* groups, int32_t num_groups, int32_t step, 
  * The three outputs may be NULL. */
 int gsr_densify_fold(int32_t P, const float* d_max_radii, const float* d_accum, const float* d_count,
                      float* max_radii2D, float* xyz_grad_accum, float* xyz_grad_count, void* stream);
+
+/* The binning the forward runs: GSR_BINNING_TILE (default: tile-segmented, csrc/tile_binning.cu) or GSR_BINNING_ONESWEEP
+ * (scan + key duplication + onesweep radix sort + ranges).  Same sorted lists and ranges, bit for bit.  Process-wide;
+ * initial value from the environment variable GSR_BINNING=onesweep.  The forward, backward and export of one frame must
+ * run under the same mode. */
+#define GSR_BINNING_TILE 0
+#define GSR_BINNING_ONESWEEP 1
+int gsr_set_binning(int32_t mode);
+int32_t gsr_get_binning(void);
 
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 int64_t gsr_launch_count(void);

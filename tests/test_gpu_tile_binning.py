@@ -4,6 +4,7 @@ above 8 192 (the in-place network through L2), and depths with many exact ties (
 them the way the reference's stable radix sort does).  Bit-exact: sorted keys, sorted point list, ranges."""
 import numpy as np
 import pytest
+import torch
 
 import gpu_utils as U
 
@@ -61,19 +62,34 @@ def test_too_small_hint_reruns_to_the_same_lists(name):
             assert np.array_equal(o[k], base[k]), (hint, k)
 
 
-def test_global_onesweep_binning_still_passes_the_list_tests():
-    """GSR_BINNING=onesweep (read once per process) selects the global radix-sort binning: the bit-exact list tests
-    and this file's crowded / tied scenes must hold for it too."""
-    import os
-    import subprocess
-    import sys
-    here = os.path.dirname(os.path.abspath(__file__))
-    env = dict(os.environ, GSR_BINNING="onesweep")
-    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-p", "no:cacheprovider",
-                        os.path.join(here, "test_gpu_parity.py") + "::test_keys_sort_ranges_bit_exact",
-                        os.path.join(here, "test_gpu_tile_binning.py") + "::test_segmented_binning_equals_global_stable_sort"],
-                       env=env, capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+def test_global_onesweep_binning_gives_the_same_lists():
+    """gsr_set_binning(GSR_BINNING_ONESWEEP) selects the global radix-sort binning at run time: the same sorted lists,
+    ranges, images and gradients as the tile-segmented binning, on this file's crowded / tied scenes and the parity
+    scenes, in ONE process (round 1 needed a subprocess: the mode was a process-static)."""
+    from gaussian_splatting_lightning_b200 import _native as N
+    import test_gpu_parity as TP
+    assert N.get_binning() == "tile"
+    names = list(CASES) if "CASES" in globals() else []
+    cases = [(_case(n)) for n in names] + [TP._case(n) for n in ("g2_deg3_100x70", "deg3_20k_320x200", "deg1_ragged_203x117_view3of8")]
+    rng = np.random.default_rng(0)
+    for cam, arrays in cases:
+        H, W = cam.image_height, cam.image_width
+        dC = rng.standard_normal((3, H, W)).astype(np.float32)
+        a = U.run_cuda_forward(cam, arrays)
+        sa, ga = U.export(a), U.run_cuda_backward(a, dC, None)
+        try:
+            N.set_binning("onesweep")
+            assert N.get_binning() == "onesweep"
+            b = U.run_cuda_forward(cam, arrays)
+            sb, gb = U.export(b), U.run_cuda_backward(b, dC, None)
+        finally:
+            N.set_binning("tile")
+        for k in ("keys_sorted", "vals_sorted", "ranges", "n_contrib", "keys_unsorted", "vals_unsorted"):
+            assert np.array_equal(sa[k], sb[k]), k
+        assert torch.equal(a["color"], b["color"]) and a["R"] == b["R"]
+        for k in ga:
+            s_ = max(1.0, float(np.abs(ga[k]).max()))
+            assert np.abs(ga[k] - gb[k]).max() / s_ <= 1e-5, k
 
 
 @pytest.mark.parametrize("n", [1, 15, 16, 17, 255, 511, 512, 513, 1023, 1024, 1025, 2047, 2048, 2049, 4097, 8191, 8192,

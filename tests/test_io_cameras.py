@@ -118,3 +118,41 @@ def test_settings_from_collated_batch():
         assert torch.equal(s.viewmatrix, it["viewmatrix"]) and torch.equal(s.projmatrix, it["projmatrix"])
         assert torch.equal(s.campos, it["campos"]) and s.tanfovx == it["tanfovx"] and s.tanfovy == it["tanfovy"]
         assert (s.image_height, s.image_width) == (480, 640) and s.bg.tolist() == [0, 0, 0]
+
+
+def test_save_ply_bytes_spelled_out(tmp_path):
+    """f3 pin without `plyfile` (absent from the image): the exact bytes GaussianModel.save_ply writes
+    (gs_lightning/modules/gaussian_model.py:150-171) for two Gaussians of SH degree 1, spelled out by hand from the
+    format: plyfile's header for a structured array of 'f4' fields (`property float <name>`, binary_little_endian 1.0,
+    one element `vertex`), property order x y z nx ny nz f_dc_* f_rest_* opacity scale_* rot_*, normals zero, and the
+    features written CHANNEL-major (`features.transpose(1, 2)` then flatten, gaussian_model.py:157-158)."""
+    import struct
+    import torch
+    from gaussian_splatting_lightning_b200 import io
+    xyz = torch.tensor([[1.0, 2.0, 3.0], [-4.0, 5.5, 0.25]])
+    f_dc = torch.tensor([[[0.1, 0.2, 0.3]], [[0.4, 0.5, 0.6]]])                       # (N, 1, 3): [coef][channel]
+    f_rest = torch.arange(18, dtype=torch.float32).reshape(2, 3, 3) + 10.0             # (N, 3, 3): [coef][channel]
+    opacity = torch.tensor([[-1.5], [2.5]])
+    scaling = torch.tensor([[-3.0, -2.0, -1.0], [0.5, 0.25, 0.125]])
+    rotation = torch.tensor([[1.0, 0.0, 0.0, 0.0], [0.5, -0.5, 0.5, -0.5]])
+    path = str(tmp_path / "two.ply")
+    io.save_ply(path, xyz, f_dc, f_rest, opacity, scaling, rotation)
+    names = (["x", "y", "z", "nx", "ny", "nz", "f_dc_0", "f_dc_1", "f_dc_2"] + [f"f_rest_{i}" for i in range(9)]
+             + ["opacity", "scale_0", "scale_1", "scale_2", "rot_0", "rot_1", "rot_2", "rot_3"])
+    header = ("ply\nformat binary_little_endian 1.0\nelement vertex 2\n"
+              + "".join(f"property float {n}\n" for n in names) + "end_header\n").encode("ascii")
+    f32 = lambda *v: struct.pack("<%df" % len(v), *v)
+    row0 = (f32(1.0, 2.0, 3.0) + f32(0.0, 0.0, 0.0) + f32(0.1, 0.2, 0.3)
+            # f_rest of Gaussian 0 is [[10,11,12],[13,14,15],[16,17,18]] ([coef][channel]); channel-major: R of the three
+            # coefficients, then G, then B
+            + f32(10.0, 13.0, 16.0, 11.0, 14.0, 17.0, 12.0, 15.0, 18.0)
+            + f32(-1.5) + f32(-3.0, -2.0, -1.0) + f32(1.0, 0.0, 0.0, 0.0))
+    row1 = (f32(-4.0, 5.5, 0.25) + f32(0.0, 0.0, 0.0) + f32(0.4, 0.5, 0.6)
+            + f32(19.0, 22.0, 25.0, 20.0, 23.0, 26.0, 21.0, 24.0, 27.0)
+            + f32(2.5) + f32(0.5, 0.25, 0.125) + f32(0.5, -0.5, 0.5, -0.5))
+    assert open(path, "rb").read() == header + row0 + row1
+    # and the reference loader's reading of those bytes (lexicographic property order, no transpose back:
+    # gaussian_model.py:112-147) is what load_ply returns by default
+    ck = io.load_ply(path)
+    assert ck["xyz"].tolist() == xyz.tolist() and ck["active_sh_degree"] == int(np.sqrt(3 + 1))
+    assert ck["features_rest"].reshape(2, -1)[0].tolist() == [10.0, 13.0, 16.0, 11.0, 14.0, 17.0, 12.0, 15.0, 18.0]
