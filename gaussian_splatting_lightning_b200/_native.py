@@ -74,7 +74,7 @@ EXPORTED_SYMBOLS = [
     "gsr_backward_scratch_bytes", "gsr_forward", "gsr_backward", "gsr_preprocess_backward_views", "gsr_preprocess_backward_views_range", "gsr_mark_visible", "gsr_export_state",
     "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count", "gsr_set_binning", "gsr_get_binning", "gsr_profile_enable", "gsr_profile_reset",
     "gsr_profile_collect", "gsr_profile_stage_count", "gsr_profile_stage_name", "gsr_profile_stage_ms",
-    "gsr_profile_stage_calls", "gsr_l1_loss_scratch_bytes", "gsr_l1_loss", "gsr_adam_step", "gsr_densify_fold", "gsr_fused_ssim_scratch_bytes",
+    "gsr_profile_stage_calls", "gsr_l1_loss_scratch_bytes", "gsr_l1_loss", "gsr_l1_loss_noalloc", "gsr_adam_step", "gsr_densify_fold", "gsr_fused_ssim_scratch_bytes",
     "gsr_fused_ssim", "gsr_photometric_loss",
 ]
 
@@ -134,6 +134,8 @@ def lib():
     L.gsr_l1_loss_scratch_bytes.argtypes = []
     L.gsr_l1_loss.restype = C.c_int
     L.gsr_l1_loss.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gsr_l1_loss_noalloc.restype = C.c_int
+    L.gsr_l1_loss_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     L.gsr_fused_ssim_scratch_bytes.restype = C.c_size_t
     L.gsr_fused_ssim_scratch_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int32]
     L.gsr_fused_ssim.restype = C.c_int

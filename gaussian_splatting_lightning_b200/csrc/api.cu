@@ -487,6 +487,18 @@ int gsr_l1_loss(const float* image, const float* target, int64_t n, float* dL_di
   return GSR_OK;
 }
 
+int gsr_l1_loss_noalloc(const float* image, const float* target, int64_t n, float* dL_dimage, float* out_loss,
+                        void* stream) {
+  if (n <= 0 || !image || !target || !out_loss) return fail(GSR_EINVAL, "l1_loss_noalloc: bad arguments");
+  if (n > (int64_t)GSR_L1_NOALLOC_MAX_ELEMENTS)
+    return fail(GSR_ELIMIT, "l1_loss_noalloc: n exceeds GSR_L1_NOALLOC_MAX_ELEMENTS (2^28); use gsr_l1_loss with caller scratch");
+  if ((((uintptr_t)image) | ((uintptr_t)target) | ((uintptr_t)dL_dimage)) & 15)
+    return fail(GSR_EINVAL, "l1_loss_noalloc: image, target and dL_dimage must be 16-byte aligned");
+  GSR_CUDA(gsr::launch_l1_loss_noalloc(image, target, (long long)n, dL_dimage, out_loss, (cudaStream_t)stream),
+           "l1_loss_noalloc (cudaGetSymbolAddress / memset / kernel)");
+  return GSR_OK;
+}
+
 size_t gsr_fused_ssim_scratch_bytes(int32_t planes, int32_t H, int32_t W) { return gsr::ssim_scratch_bytes(planes, H, W); }
 
 int gsr_fused_ssim(const float* img1, const float* img2, int32_t planes, int32_t H, int32_t W, float C1, float C2,

@@ -300,6 +300,8 @@ cudaError_t launch_export_geom(int P, const int32_t* radii, const GeomState& geo
 size_t l1_scratch_bytes();
 cudaError_t launch_l1_loss(const float* image, const float* target, long long n, float* dL_dimage, float* out_loss,
                            void* scratch, cudaStream_t s);
+cudaError_t launch_l1_loss_noalloc(const float* image, const float* target, long long n, float* dL_dimage,
+                                   float* out_loss, cudaStream_t s);
 size_t ssim_scratch_bytes(int planes, int H, int W);
 cudaError_t launch_fused_ssim(const float* img1, const float* img2, int planes, int H, int W, float C1, float C2,
                               int valid, float w_l1, float w_ssim, float w_const, float* dL_dimg1, float* out_loss,

@@ -103,6 +103,39 @@ cudaError_t launch_l1_loss(const float* image, const float* target, long long n,
 }
 }  // namespace gsr
 
+// ---- gsr_l1_loss_noalloc: the same kernel on scratch that lives in the library image -----------------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  The
+// scratch (ticket + one double per CTA: GSR_L1_NOALLOC_SCRATCH_BYTES = 9600 bytes) is a file-scope __device__
+// array: every GPU that loads the library holds it until exit.  In HOST code the array's name is only a stand-in
+// for the symbol, not a device address: its address is asked for once per device (that device current) with
+// cudaGetSymbolAddress and kept.  All calls share the array: calls that overlap on the GPU (two streams, two
+// threads) race on the ticket and the partial sums.
+static __device__ __align__(256) unsigned char g_l1_noalloc_scratch[GSR_L1_NOALLOC_SCRATCH_BYTES];
+
+namespace gsr {
+cudaError_t launch_l1_loss_noalloc(const float* image, const float* target, long long n, float* dL_dimage,
+                                   float* out_loss, cudaStream_t s) {
+  static_assert(GSR_L1_NOALLOC_SCRATCH_BYTES >= (size_t)L1_MAX_CTAS * sizeof(double) + 128, "scratch too small");
+  constexpr int MAX_DEVICES = 64;
+  static void* volatile addr_of_device[MAX_DEVICES] = {};   // set once per device; a race sets the same value twice
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= MAX_DEVICES) return cudaErrorInvalidDevice;
+  void* scratch = addr_of_device[dev];
+  if (!scratch) {
+    e = cudaGetSymbolAddress(&scratch, g_l1_noalloc_scratch);   // the CURRENT device's copy of the array
+    if (e != cudaSuccess) return e;
+    if (!scratch) return cudaErrorInvalidSymbol;
+    addr_of_device[dev] = scratch;
+  }
+  // the array keeps the last call's contents: the ticket must start at zero (the partials are written before read)
+  e = cudaMemsetAsync(scratch, 0, 128, s);
+  if (e != cudaSuccess) return e;
+  return launch_l1_loss(image, target, n, dL_dimage, out_loss, scratch, s);
+}
+}  // namespace gsr
+
 // ---- fused SSIM: value + gradient in ONE kernel ----------------------------------------------------------
 // Reference: submodules/fused-ssim (ssim.cu:187-366 fusedssimCUDA / fusedssim_backwardCUDA, fused_ssim/__init__.py:8-41),
 // used as `1 - fused_ssim(rendered, gt)` at gs_lightning/lightning/gs_lightning_module.py:100,279.

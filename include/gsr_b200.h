@@ -226,6 +226,19 @@ size_t gsr_l1_loss_scratch_bytes(void);
 int gsr_l1_loss(const float* image, const float* target, int64_t n, float* dL_dimage, float* out_loss,
                 void* scratch, void* stream);
 
+/* gsr_l1_loss without any allocation, for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.
+ * Same kernel, same result as gsr_l1_loss; the scratch (GSR_L1_NOALLOC_SCRATCH_BYTES) is a static
+ * __device__ array inside the library, held by every GPU that loads the library until the process exits.  n above
+ * GSR_L1_NOALLOC_MAX_ELEMENTS returns GSR_ELIMIT.  Calls no cudaMalloc / cudaFree / allocating routine (one
+ * cudaGetSymbolAddress per device on first use, a 128-byte cudaMemsetAsync and the kernel per call, on `stream`
+ * of the CURRENT device).  All calls share the one array: calls that may overlap on the GPU (different streams
+ * or host threads) race -- serialise them, or use gsr_l1_loss with a scratch buffer per stream. */
+#define GSR_L1_NOALLOC_MAX_ELEMENTS (1 << 28) /* 2^28 floats per image (1 GiB): 3 x 8192 x 8192 fits */
+#define GSR_L1_NOALLOC_SCRATCH_BYTES 9600     /* 128 (ticket) + 148 * 8 CTAs x 8 bytes               */
+int gsr_l1_loss_noalloc(const float* image, const float* target, int64_t n, float* dL_dimage, float* out_loss,
+                        void* stream);
+
 /* fused_ssim(img1, img2, padding, train) of submodules/fused-ssim (fused_ssim/__init__.py:33-41, ssim.cu:187-444),
  * used as `1 - fused_ssim(rendered, gt)` at gs_lightning_module.py:100,279: *out_ssim = mean of the SSIM map
  * (11x11 Gaussian window, sigma 1.5, zero padding; padding_valid != 0 averages the map without its 5-pixel border)
