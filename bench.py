@@ -394,6 +394,7 @@ class E2E:
         if rig.bufs.num_chunks == 1:
             parameter_groups_on(rig.bufs, self.params)     # .grad = the parameter's rows of the step buffer
         self.copy_stream = torch.cuda.Stream(dev)
+        self.cam_stream = torch.cuda.Stream(dev)
         self.n_slots = rig.n_streams + 2
         self.slots = [dict(cam=torch.empty(38, device=dev), gt=torch.empty(3, H, W, device=dev),
                            gt_u8=torch.empty(3, H, W, dtype=torch.uint8, device=dev), cam_ready=torch.cuda.Event(),
@@ -415,15 +416,17 @@ class E2E:
         while self.uploaded < g_end:
             g = self.uploaded
             sl, j = self.slots[g % self.n_slots], g % vpr
+            with torch.cuda.stream(self.cam_stream):              # the forward needs only the camera (152 bytes): its
+                self.cam_stream.wait_event(sl["free"])            # copy does not queue behind the previous view's image
+                sl["cam"].copy_(self.cam_host[j], non_blocking=True)
+                sl["cam_ready"].record(self.cam_stream)
             with torch.cuda.stream(self.copy_stream):
                 self.copy_stream.wait_event(sl["free"])           # the view that used this slot last is done with it
-                sl["cam"].copy_(self.cam_host[j], non_blocking=True)
-                sl["cam_ready"].record(self.copy_stream)          # the forward needs only the camera ...
                 if self.u8:
                     sl["gt_u8"].copy_(self.gt_host_u8[j], non_blocking=True)
                 else:
                     sl["gt"].copy_(self.gt_host[j], non_blocking=True)
-                sl["ready"].record(self.copy_stream)              # ... the loss the image
+                sl["ready"].record(self.copy_stream)              # the loss needs the image
             self.uploaded += 1
 
     def view(self, j):
@@ -462,6 +465,7 @@ class E2E:
 
     def step(self):
         rig = self.rig
+        t_host = time.perf_counter()
         main = torch.cuda.current_stream()
         rig.bufs.zero_(keep_max_radii=rig.world > 1, stats_only=rig.fused)
         self.upload_until(self.steps * rig.vpr + self.n_slots - 1)
@@ -481,6 +485,9 @@ class E2E:
         # synchronize)
         self.done[self.steps & 1].record(main)
         self.steps += 1
+        # host time inside the step before the loss read: enqueueing + every forward's wait for its view's
+        # num_rendered (the mailbox read of gsr_forward, which ties the host to the GPU about one view ahead)
+        self.host_busy_ms = (time.perf_counter() - t_host) * 1e3
         if self.steps >= 2:
             self.done[self.steps & 1].synchronize()      # step s - 1
             return float(self.loss_host[self.steps & 1].sum())
@@ -644,6 +651,7 @@ def run_ours(args):
     if not args.no_e2e:
         E = E2E(rig)
         ms_e2e, e2e_regions, _ = regions(E.step, K, 3, device, world, warmup=2)
+        e2e_host_ms = E.host_busy_ms
         E.loss_kind = "full"     # the reference's training loss: 0.8 L1 + 0.2 (1 - SSIM), one fused kernel
         ms_e2e_full, _, _ = regions(E.step, K, 3, device, world, warmup=2)
         E.loss_kind = "l1"
@@ -652,6 +660,7 @@ def run_ours(args):
         E.u8 = False
         e2e = {"value": frames / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": E.h2d_bytes_per_step,
                "d2h_bytes_per_step": E.d2h_bytes_per_step, "regions_ms_per_step": [round(m / K, 3) for m in e2e_regions],
+               "host_ms_per_step_before_loss_read": round(e2e_host_ms, 3),
                "what": "GaussianRasterizer autograd API (through the `_C` torch extension) + fused L1 loss (training.l1_loss) "
                        "with fused gradient accumulation (accumulate_gradients_into) on the same CUDA streams as `value`; "
                        "per view: pinned GT image and camera H2D (copy stream, ring of streams+1 slots, inside the timed "

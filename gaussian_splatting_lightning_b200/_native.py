@@ -72,7 +72,7 @@ class GsrStateExport(C.Structure):
 EXPORTED_SYMBOLS = [
     "gsr_version", "gsr_last_error", "gsr_geom_bytes", "gsr_img_bytes", "gsr_binning_bytes",
     "gsr_backward_scratch_bytes", "gsr_forward", "gsr_backward", "gsr_preprocess_backward_views", "gsr_preprocess_backward_views_range", "gsr_mark_visible", "gsr_export_state",
-    "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count", "gsr_set_binning", "gsr_get_binning", "gsr_profile_enable", "gsr_profile_reset",
+    "gsr_sort_workspace_bytes", "gsr_sort_pairs", "gsr_launch_count", "gsr_set_binning", "gsr_get_binning", "gsr_set_priority_lanes", "gsr_get_priority_lanes", "gsr_profile_enable", "gsr_profile_reset",
     "gsr_profile_collect", "gsr_profile_stage_count", "gsr_profile_stage_name", "gsr_profile_stage_ms",
     "gsr_profile_stage_calls", "gsr_l1_loss_scratch_bytes", "gsr_l1_loss", "gsr_l1_loss_noalloc", "gsr_adam_step", "gsr_densify_fold", "gsr_fused_ssim_scratch_bytes",
     "gsr_fused_ssim", "gsr_photometric_loss",
@@ -195,6 +195,15 @@ def set_binning(mode: str) -> None:
 
 def get_binning() -> str:
     return ("tile", "onesweep")[int(lib().gsr_get_binning())]
+
+
+def set_priority_lanes(on: bool) -> None:
+    """Run the stages before compositing on a high-priority stream per caller stream (include/gsr_b200.h)."""
+    check(lib().gsr_set_priority_lanes(int(bool(on))), "gsr_set_priority_lanes")
+
+
+def get_priority_lanes() -> bool:
+    return bool(lib().gsr_get_priority_lanes())
 
 
 def profile_enable(on: bool) -> None:

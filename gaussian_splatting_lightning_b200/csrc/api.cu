@@ -7,12 +7,17 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
 
 #include "../../include/gsr_b200.h"
 #include "gsr_common.cuh"
+
+#ifndef GSR_PRIORITY_LANES_DEFAULT
+#define GSR_PRIORITY_LANES_DEFAULT 0
+#endif
 
 namespace {
 
@@ -122,6 +127,46 @@ int get_mailbox(Mailbox** out) {
   return GSR_OK;
 }
 
+// Priority lanes.  The stages before the compositing kernel (preprocess, tile scan, scatter, sort) are bound by memory
+// latency and L2 atomics, the compositing kernels by instruction issue: side by side on an SM they hardly slow each other
+// down.  But kernels of equal priority are dispatched grid after grid -- a binning kernel launched behind another
+// view's compositing grid gets its first CTA when that grid has no pending CTA left, so the views' streams overlap at
+// the grids' tails only.  With lanes on, gsr_forward runs the stages before compositing on a HIGH-PRIORITY stream of
+// its own (one per caller stream and device; fork / join by events), whose CTAs the block scheduler places ahead of
+// pending compositing CTAs as SM resources free up.  GSR_PRIORITY_LANES=0/1 sets the initial value, gsr_set_priority_lanes()
+// changes it at run time.
+struct Lane {
+  cudaStream_t hp = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+};
+std::mutex g_lane_mu;
+std::map<std::pair<int, cudaStream_t>, Lane> g_lanes;
+std::atomic<int> g_lanes_on{-1};
+bool lanes_on() {
+  int m = g_lanes_on.load(std::memory_order_relaxed);
+  if (m < 0) {
+    const char* e = getenv("GSR_PRIORITY_LANES");
+    m = e ? (atoi(e) != 0) : GSR_PRIORITY_LANES_DEFAULT;
+    g_lanes_on.store(m, std::memory_order_relaxed);
+  }
+  return m != 0;
+}
+int get_lane(cudaStream_t caller, Lane* out) {
+  int dev = 0;
+  GSR_CUDA(cudaGetDevice(&dev), "cudaGetDevice");
+  std::lock_guard<std::mutex> l(g_lane_mu);
+  Lane& ln = g_lanes[std::make_pair(dev, caller)];
+  if (!ln.hp) {
+    int lo = 0, hi = 0;   // hi = the numerically lowest value = the greatest priority
+    GSR_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi), "cudaDeviceGetStreamPriorityRange");
+    GSR_CUDA(cudaStreamCreateWithPriority(&ln.hp, cudaStreamNonBlocking, hi), "cudaStreamCreateWithPriority");
+    GSR_CUDA(cudaEventCreateWithFlags(&ln.fork, cudaEventDisableTiming), "cudaEventCreate(lane)");
+    GSR_CUDA(cudaEventCreateWithFlags(&ln.join, cudaEventDisableTiming), "cudaEventCreate(lane)");
+  }
+  *out = ln;
+  return GSR_OK;
+}
+
 int make_view(const GsrSettings* s, int M, GsrView* v) {
   if (!s) return fail(GSR_EINVAL, "settings is NULL");
   if (s->image_width <= 0 || s->image_height <= 0) return fail(GSR_EINVAL, "image size must be positive");
@@ -183,6 +228,11 @@ int gsr_set_binning(int32_t mode) {
   g_binning.store(mode, std::memory_order_relaxed);
   return GSR_OK;
 }
+int gsr_set_priority_lanes(int32_t on) {
+  g_lanes_on.store(on ? 1 : 0, std::memory_order_relaxed);
+  return GSR_OK;
+}
+int32_t gsr_get_priority_lanes(void) { return lanes_on() ? 1 : 0; }
 int32_t gsr_get_binning(void) { return binning_segmented() ? GSR_BINNING_TILE : GSR_BINNING_ONESWEEP; }
 
 size_t gsr_geom_bytes(int32_t P) { return GeomState::carve(nullptr, P).bytes; }
@@ -224,29 +274,41 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
 
   // GSR_BINNING=onesweep selects the global radix sort (K3-K6); the default is the tile-segmented binning.
   const bool segmented = binning_segmented();
+  // the stages before compositing: on the caller's stream, or on its high-priority lane (fork here, join before the
+  // compositing kernel; see Lane above)
+  Lane lane;
+  const bool lanes = lanes_on() && !debug && P > 0;
+  cudaStream_t work = stream;
+  if (lanes) {
+    rc = get_lane(stream, &lane);
+    if (rc) return rc;
+    work = lane.hp;
+    GSR_CUDA(cudaEventRecord(lane.fork, stream), "event record (lane fork)");
+    GSR_CUDA(cudaStreamWaitEvent(work, lane.fork, 0), "stream wait (lane fork)");
+  }
   // one memset clears ranges + tile counters + control block, one the scan status words
-  GSR_CUDA(cudaMemsetAsync(img_ptr + img.ranges_off, 0, img.bytes - img.ranges_off, stream), "memset(ranges)");
-  if (!segmented) GSR_CUDA(cudaMemsetAsync(geom.scan_state, 0, geom.scan_state_bytes(P), stream), "memset(scan state)");
+  GSR_CUDA(cudaMemsetAsync(img_ptr + img.ranges_off, 0, img.bytes - img.ranges_off, work), "memset(ranges)");
+  if (!segmented) GSR_CUDA(cudaMemsetAsync(geom.scan_state, 0, geom.scan_state_bytes(P), work), "memset(scan state)");
 
-  GSR_STAGE(ST_PREPROCESS, gsr::launch_preprocess(v, g, radii, geom, segmented ? img.tile_count : nullptr, stream),
-            "preprocess kernel", debug, stream);
+  GSR_STAGE(ST_PREPROCESS, gsr::launch_preprocess(v, g, radii, geom, segmented ? img.tile_count : nullptr, work),
+            "preprocess kernel", debug, work);
   if (segmented)
     GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(P > 0 ? v.gx : 0, v.gy, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
-                                             img.tile_scan_state, img.ctrl, img.tile_order, stream),
-              "tile scan kernel", debug, stream);
+                                             img.tile_scan_state, img.ctrl, img.tile_order, work),
+              "tile scan kernel", debug, work);
   else
-    GSR_STAGE(ST_SCAN, gsr::launch_scan(P, geom, img.ctrl, stream), "scan kernel", debug, stream);
+    GSR_STAGE(ST_SCAN, gsr::launch_scan(P, geom, img.ctrl, work), "scan kernel", debug, work);
   if (!segmented || P == 0) {  // the tile scan writes the compositing kernels' tile order; without it: raster order
-    iota_u32_kernel<<<(num_tiles + 255) / 256, 256, 0, stream>>>(img.tile_order, num_tiles);
+    iota_u32_kernel<<<(num_tiles + 255) / 256, 256, 0, work>>>(img.tile_order, num_tiles);
     gsr::count_launch();
   }
 
   Mailbox* mail = nullptr;
   rc = get_mailbox(&mail);
   if (rc) return rc;
-  GSR_CUDA(cudaMemcpyAsync(mail->host, &img.ctrl->num_rendered, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream),
+  GSR_CUDA(cudaMemcpyAsync(mail->host, &img.ctrl->num_rendered, sizeof(unsigned int), cudaMemcpyDeviceToHost, work),
            "memcpy(num_rendered)");
-  GSR_CUDA(cudaEventRecord(mail->ev, stream), "event record");
+  GSR_CUDA(cudaEventRecord(mail->ev, work), "event record");
 
   int64_t R = -1;
   int64_t cap = binning_hint;
@@ -260,34 +322,42 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
     char* bin_ptr = (char*)alloc(alloc_user, GSR_BUF_BINNING, BinningState::carve(nullptr, cap, num_tiles).bytes);
     if (!bin_ptr) return fail(GSR_EALLOC, "allocator returned NULL");
     BinningState bin = BinningState::carve(bin_ptr, cap, num_tiles);
+    if (lanes && attempt > 0) {  // the truncated frame's compositing kernel still reads what the stages rewrite
+      GSR_CUDA(cudaEventRecord(lane.fork, stream), "event record (lane fork)");
+      GSR_CUDA(cudaStreamWaitEvent(work, lane.fork, 0), "stream wait (lane fork)");
+    }
     if (cap > 0 && P > 0 && segmented) {
       if (attempt > 0) {  // rebuild the un-truncated ranges, rewind the cursors (scan state and list counters zeroed)
-        GSR_CUDA(cudaMemsetAsync(img.tile_scan_state, 0, img.tile_scan_state_bytes, stream), "memset(tile scan state)");
-        GSR_CUDA(cudaMemsetAsync(img.ctrl, 0, sizeof(GsrControl), stream), "memset(control)");
+        GSR_CUDA(cudaMemsetAsync(img.tile_scan_state, 0, img.tile_scan_state_bytes, work), "memset(tile scan state)");
+        GSR_CUDA(cudaMemsetAsync(img.ctrl, 0, sizeof(GsrControl), work), "memset(control)");
         GSR_STAGE(ST_SCAN, gsr::launch_tile_scan(v.gx, v.gy, img.tile_count, img.ranges, img.tile_cursor, img.large_tiles,
-                                                 img.tile_scan_state, img.ctrl, img.tile_order, stream),
-                  "tile scan kernel", debug, stream);
+                                                 img.tile_scan_state, img.ctrl, img.tile_order, work),
+                  "tile scan kernel", debug, work);
       }
       GSR_STAGE(ST_DUPLICATE, gsr::launch_tile_scatter(v, P, radii, geom, img.tile_cursor, bin.keys_a,
-                                                       (uint32_t)cap, img.ctrl, bin.header, stream),
-                "tile scatter kernel", debug, stream);
+                                                       (uint32_t)cap, img.ctrl, bin.header, work),
+                "tile scatter kernel", debug, work);
       GSR_STAGE(ST_SORT, gsr::launch_tile_sort(num_tiles, img.ranges, img.large_tiles, img.ctrl, bin.keys_a, bin.vals_a, (uint32_t)cap,
-                                                    stream),
-                "tile sort kernel", debug, stream);
+                                                    work),
+                "tile sort kernel", debug, work);
     } else if (cap > 0 && P > 0) {
-      GSR_CUDA(cudaMemsetAsync(bin.sort_ws_base, 0, bin.sort_ws.bytes, stream), "memset(sort workspace)");
+      GSR_CUDA(cudaMemsetAsync(bin.sort_ws_base, 0, bin.sort_ws.bytes, work), "memset(sort workspace)");
       // start in the buffer that makes the last pass land in (keys_a, vals_a)
       unsigned long long* k0 = (npass % 2 == 0) ? bin.keys_a : bin.keys_b;
       uint32_t* v0 = (npass % 2 == 0) ? bin.vals_a : bin.vals_b;
       unsigned long long* k1 = (npass % 2 == 0) ? bin.keys_b : bin.keys_a;
       uint32_t* v1 = (npass % 2 == 0) ? bin.vals_b : bin.vals_a;
-      GSR_STAGE(ST_DUPLICATE, gsr::launch_duplicate(v, P, radii, geom, k0, v0, (uint32_t)cap, img.ctrl, bin.header, bin.sort_ws.hist, npass, stream), "duplicate kernel",
-                debug, stream);
+      GSR_STAGE(ST_DUPLICATE, gsr::launch_duplicate(v, P, radii, geom, k0, v0, (uint32_t)cap, img.ctrl, bin.header, bin.sort_ws.hist, npass, work), "duplicate kernel",
+                debug, work);
       GSR_STAGE(ST_SORT, gsr::launch_onesweep(k0, v0, k1, v1, &img.ctrl->num_rendered, (uint32_t)cap, end_bit, bin.sort_ws,
-                                     true, stream),
-                "onesweep radix sort", debug, stream);
-      GSR_STAGE(ST_RANGES, gsr::launch_tile_ranges(bin.keys_a, &img.ctrl->num_rendered, (uint32_t)cap, img.ranges, stream),
-                "tile ranges kernel", debug, stream);
+                                     true, work),
+                "onesweep radix sort", debug, work);
+      GSR_STAGE(ST_RANGES, gsr::launch_tile_ranges(bin.keys_a, &img.ctrl->num_rendered, (uint32_t)cap, img.ranges, work),
+                "tile ranges kernel", debug, work);
+    }
+    if (lanes) {
+      GSR_CUDA(cudaEventRecord(lane.join, work), "event record (lane join)");
+      GSR_CUDA(cudaStreamWaitEvent(stream, lane.join, 0), "stream wait (lane join)");
     }
     GSR_STAGE(ST_RENDER_FWD, gsr::launch_render_forward(v, img.ranges, img.tile_order, bin.vals_a, geom.recs, out_color,
                                                         out_invdepth, img.final_T, img.n_contrib, bin.hits, stream),
@@ -300,7 +370,7 @@ int gsr_forward(const GsrSettings* settings, const GsrGaussians* gaussians, floa
     // the hint was too small: the frame above rendered a truncated list. Redo binning + compositing.
     cap = R + R / 8 + 1024;
     if (!segmented)
-      GSR_CUDA(cudaMemsetAsync(img.ranges, 0, (size_t)num_tiles * sizeof(uint2), stream), "memset(ranges)");
+      GSR_CUDA(cudaMemsetAsync(img.ranges, 0, (size_t)num_tiles * sizeof(uint2), stream), "memset(ranges)");  // before the next fork
   }
   if (R >= 0xFFFFFFFFll) return fail(GSR_ELIMIT, "more than 2^32 tile instances");
   if (num_rendered) *num_rendered = R;

@@ -19,6 +19,7 @@
 
 #include <cstddef>
 #include <cstdint>
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 #define GSR_TILE 16
@@ -297,6 +298,13 @@ cudaError_t launch_export_geom(int P, const int32_t* radii, const GeomState& geo
                                float* cov3D, float* conic_opacity, float* rgb, uint8_t* clamped,
                                uint32_t* tiles_touched, uint32_t* point_offsets, cudaStream_t s);
 // loss.cu / optimizer.cu
+// CTA size of a kernel from the environment (32 / 64 / 128 / 256; anything else: the default), read once
+inline int env_threads(const char* name, int dflt) {
+  const char* e = getenv(name);
+  if (!e) return dflt;
+  const int v = atoi(e);
+  return (v == 32 || v == 64 || v == 128 || v == 256) ? v : dflt;
+}
 size_t l1_scratch_bytes();
 cudaError_t launch_l1_loss(const float* image, const float* target, long long n, float* dL_dimage, float* out_loss,
                            void* scratch, cudaStream_t s);

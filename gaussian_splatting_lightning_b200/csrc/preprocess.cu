@@ -85,14 +85,15 @@ __device__ __forceinline__ void load_and_eval_sh(const float* __restrict__ row, 
   eval_sh_row<DEG>(sh, dx, dy, dz, rgb, clamp_bits);
 }
 
-__global__ void __launch_bounds__(256) preprocess_kernel(const PreArgs a) {
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) preprocess_kernel(const PreArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) unsigned long long sh_bar;
   const int tid = threadIdx.x;
-  const int base = blockIdx.x * 256;
+  const int base = blockIdx.x * THREADS;
   const int i = base + tid;
   const int P = a.g.P, M = a.g.M;
-  const int nvalid = min(256, P - base);
+  const int nvalid = min(THREADS, P - base);
   const bool want_sh = a.g.colors_precomp == nullptr;
   const uint32_t chunk_bytes = (uint32_t)nvalid * (uint32_t)M * 12u;
   const bool bulk = want_sh && a.use_bulk && (chunk_bytes % 16u == 0u);
@@ -237,14 +238,17 @@ cudaError_t launch_preprocess(const GsrView& v, const GsrGaussiansDev& g, int32_
   a.v = v; a.g = g; a.radii = radii;
   a.recs = geom.recs; a.cov3D = geom.cov3D; a.clamped = geom.clamped; a.tiles_touched = geom.tiles_touched;
   a.tile_count = tile_count;
-  const size_t smem = g.shs ? (size_t)256 * g.M * 12 : 0;
-  // bulk copies need a 16-byte aligned source; the per-CTA offset 256*M*12 is always a multiple of 16
+  static const int threads = env_threads("GSR_PRE_THREADS", 64);
+  const size_t smem = g.shs ? (size_t)threads * g.M * 12 : 0;
+  // bulk copies need a 16-byte aligned source; the per-CTA offset threads*M*12 is always a multiple of 16
   a.use_bulk = g.shs && ((reinterpret_cast<uintptr_t>(g.shs) & 15) == 0) && smem <= 200 * 1024;
+  void (*kern)(const PreArgs) = threads == 32 ? preprocess_kernel<32> : threads == 64 ? preprocess_kernel<64>
+                              : threads == 128 ? preprocess_kernel<128> : preprocess_kernel<256>;
   if (a.use_bulk && smem > 48 * 1024 - 64) {  // per-device attribute: set on every launch that needs it
-    cudaError_t e = cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return e;
   }
-  preprocess_kernel<<<(g.P + 255) / 256, 256, a.use_bulk ? smem : 0, s>>>(a);
+  kern<<<(g.P + threads - 1) / threads, threads, a.use_bulk ? smem : 0, s>>>(a);
   count_launch();
   return cudaGetLastError();
 }

@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int gx, int gy
                                                            const GsrRec* __restrict__ recs, uint32_t* cursor,
                                                            unsigned long long* __restrict__ comp, uint32_t capacity,
                                                            GsrControl* ctrl, BinningHeader* header) {
-  const int i = blockIdx.x * 256 + threadIdx.x;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i == 0 && header) { header->capacity = capacity; header->num_tiles = (uint32_t)(gx * gy); header->segmented = 1u; }
   if (i >= P) return;
   const int r = radii[i];
@@ -232,8 +232,9 @@ cudaError_t launch_tile_scatter(const GsrView& v, int P, const int32_t* radii, c
                                 unsigned long long* comp, uint32_t capacity, GsrControl* ctrl, BinningHeader* header,
                                 cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
-  tile_scatter_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, v.gx, v.gy, radii, geom.recs, cursor, comp, capacity, ctrl,
-                                                      header);
+  static const int threads = env_threads("GSR_SCATTER_THREADS", 256);
+  tile_scatter_kernel<<<(P + threads - 1) / threads, threads, 0, s>>>(P, v.gx, v.gy, radii, geom.recs, cursor, comp,
+                                                                      capacity, ctrl, header);
   count_launch();
   return cudaGetLastError();
 }

@@ -291,6 +291,15 @@ int gsr_densify_fold(int32_t P, const float* d_max_radii, const float* d_accum, 
 int gsr_set_binning(int32_t mode);
 int32_t gsr_get_binning(void);
 
+/* Priority lanes (no counterpart in the reference: a scheduling choice of this library).  With lanes on, gsr_forward
+ * runs the stages before the compositing kernel (preprocess, tile scan, scatter, sort: bound by latency and L2 atomics)
+ * on a high-priority stream of its own -- one per (device, caller stream), forked from and joined back into the
+ * caller's stream by events -- so that, when several views are in flight on several streams, those stages run BESIDE
+ * another view's issue-bound compositing kernel instead of queueing behind its grid.  Results are identical.
+ * Process-wide; initial value from the environment variable GSR_PRIORITY_LANES (0 / 1). */
+int gsr_set_priority_lanes(int32_t on);
+int32_t gsr_get_priority_lanes(void);
+
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 int64_t gsr_launch_count(void);
 

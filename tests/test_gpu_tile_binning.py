@@ -122,3 +122,45 @@ def test_one_segment_of_exactly_n_instances(n):
     want = np.lexsort((np.arange(n), depth_bits)).astype(np.uint32)
     assert np.array_equal(st["vals_sorted"].view(np.uint32), want)
     assert np.array_equal(st["keys_sorted"].view(np.uint64), (np.uint64(5) << np.uint64(32)) | depth_bits[want].astype(np.uint64))
+
+
+def test_priority_lanes_give_the_same_frames_on_several_streams():
+    """gsr_set_priority_lanes(1): the stages before compositing run on a high-priority stream per caller stream (fork /
+    join by events).  Same lists, images and gradients as on the caller's stream alone -- also with several views in
+    flight on several streams, with a too-small binning hint (the retry forks again) and on reused streams."""
+    from gaussian_splatting_lightning_b200 import _native as N
+    import test_gpu_parity as TP
+    cases = [TP._case(n) for n in ("g2_deg3_100x70", "deg3_20k_320x200", "deg1_ragged_203x117_view3of8")]
+    rng = np.random.default_rng(1)
+    before = N.get_priority_lanes()
+    try:
+        results = {}
+        for on in (False, True):
+            N.set_priority_lanes(on)
+            assert N.get_priority_lanes() == on
+            streams = [torch.cuda.Stream(device=U.DEV) for _ in range(3)]
+            outs = []
+            prepared = [(U.settings_from_camera(cam), U.to_dev(arrays)) for cam, arrays in cases]
+            torch.cuda.synchronize()
+            for rep in range(2):                 # second round: the lanes' streams and events are reused
+                for k, (rs, d) in enumerate(prepared):
+                    with torch.cuda.stream(streams[k % 3]):      # no synchronisation between the views
+                        R, color, radii, geom, binning, img, invdepth, cap = U.forward_raw(
+                            rs, d["means3D"], d.get("shs"), d.get("colors_precomp"), d["opacities"], d.get("scales"),
+                            d.get("rotations"), d.get("cov3D_precomp"), binning_hint=(0 if rep == 0 else 7))
+                    outs.append(dict(rs=rs, d=d, R=R, color=color, radii=radii, geom=geom, binning=binning, img=img,
+                                     invdepth=invdepth, cap=cap))
+            torch.cuda.synchronize()
+            results[on] = outs
+        for a, b, (cam, arrays) in zip(results[False], results[True], cases + cases):
+            sa, sb = U.export(a), U.export(b)
+            for k in ("keys_sorted", "vals_sorted", "ranges", "n_contrib"):
+                assert np.array_equal(sa[k], sb[k]), k
+            assert torch.equal(a["color"], b["color"]) and torch.equal(a["invdepth"], b["invdepth"]) and a["R"] == b["R"]
+            dC = rng.standard_normal((3, cam.image_height, cam.image_width)).astype(np.float32)
+            ga, gb = U.run_cuda_backward(a, dC, None), U.run_cuda_backward(b, dC, None)
+            for k in ga:
+                s_ = max(1.0, float(np.abs(ga[k]).max()))
+                assert np.abs(ga[k] - gb[k]).max() / s_ <= 1e-5, k
+    finally:
+        N.set_priority_lanes(before)
