@@ -31,7 +31,20 @@ __global__ void __launch_bounds__(L1_THREADS) l1_loss_kernel(const float* __rest
   float4* g4 = reinterpret_cast<float4*>(dL_dimage);
   float acc = 0.f;
   const long long stride = (long long)gridDim.x * L1_THREADS;
-  for (long long i = (long long)blockIdx.x * L1_THREADS + threadIdx.x; i < n4; i += stride) {
+  long long i = (long long)blockIdx.x * L1_THREADS + threadIdx.x;
+  // two grid strides per trip: four 16-byte loads in flight per thread (the sum keeps the order of the one-stride loop)
+  for (; i + stride < n4; i += 2 * stride) {
+    const float4 a = __ldg(a4 + i), b = __ldg(b4 + i), c = __ldg(a4 + i + stride), d = __ldg(b4 + i + stride);
+    const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, dw = a.w - b.w;
+    const float ex = c.x - d.x, ey = c.y - d.y, ez = c.z - d.z, ew = c.w - d.w;
+    acc += (fabsf(dx) + fabsf(dy)) + (fabsf(dz) + fabsf(dw));
+    acc += (fabsf(ex) + fabsf(ey)) + (fabsf(ez) + fabsf(ew));
+    if (GRAD) {
+      g4[i] = make_float4(sgn(dx) * inv_n, sgn(dy) * inv_n, sgn(dz) * inv_n, sgn(dw) * inv_n);
+      g4[i + stride] = make_float4(sgn(ex) * inv_n, sgn(ey) * inv_n, sgn(ez) * inv_n, sgn(ew) * inv_n);
+    }
+  }
+  for (; i < n4; i += stride) {
     const float4 a = __ldg(a4 + i), b = __ldg(b4 + i);
     const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, dw = a.w - b.w;
     acc += (fabsf(dx) + fabsf(dy)) + (fabsf(dz) + fabsf(dw));

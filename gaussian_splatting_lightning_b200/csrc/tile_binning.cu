@@ -232,7 +232,7 @@ cudaError_t launch_tile_scatter(const GsrView& v, int P, const int32_t* radii, c
                                 unsigned long long* comp, uint32_t capacity, GsrControl* ctrl, BinningHeader* header,
                                 cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
-  static const int threads = env_threads("GSR_SCATTER_THREADS", 256);
+  static const int threads = env_threads("GSR_SCATTER_THREADS", 32);
   tile_scatter_kernel<<<(P + threads - 1) / threads, threads, 0, s>>>(P, v.gx, v.gy, radii, geom.recs, cursor, comp,
                                                                       capacity, ctrl, header);
   count_launch();
