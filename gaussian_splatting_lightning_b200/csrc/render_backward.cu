@@ -106,7 +106,9 @@ __global__ void __launch_bounds__(GSR_BWD_THREADS, GSR_BWD_CTAS * (128 / GSR_BWD
   const uint32_t aRow = keep_u32(aRed + (uint32_t)lane * (RED_STRIDE * 4u));           // row this lane adds at a flush
   const uint32_t aId = keep_u32((uint32_t)__cvta_generic_to_shared(sRedId[wslot]));
   const int red_visit = lane / 10, red_sum = lane - red_visit * 10;   // the row lane `lane` adds at a flush
-  float* const acc_col = grad_acc + red_sum;
+  // (pinned: ptxas otherwise recomputes lane / 10, the remainder and the pointer at every flush)
+  const unsigned long long acc_col = keep_u64((unsigned long long)__cvta_generic_to_global(grad_acc + red_sum));
+  const int lane_pinned = (int)keep_u32((uint32_t)lane);
   const uint32_t aIdMine = keep_u32(aId + (uint32_t)red_visit * 4u);
   uint32_t aPark = aPark0;                                             // parking address of the next visit
   int nslot = 0;                                                       // visits parked in the buffer (warp-uniform)
@@ -115,7 +117,7 @@ __global__ void __launch_bounds__(GSR_BWD_THREADS, GSR_BWD_CTAS * (128 / GSR_BWD
 #define GSR_BWD_FLUSH()                                                                                   \
   {                                                                                                       \
     __syncwarp();                                                                                         \
-    if (lane < nslot * 10) {                                                                              \
+    if (lane_pinned < nslot * 10) {                                                                       \
       f32x2 a0, a1, a2, a3, a4, a5, a6, a7, a8, a9, a10, a11, a12, a13, a14, a15;                        \
       lds2x64<0>(aRow, a0, a1); lds2x64<16>(aRow, a2, a3); lds2x64<32>(aRow, a4, a5); lds2x64<48>(aRow, a6, a7);   \
       lds2x64<64>(aRow, a8, a9); lds2x64<80>(aRow, a10, a11); lds2x64<96>(aRow, a12, a13);                \
@@ -128,7 +130,8 @@ __global__ void __launch_bounds__(GSR_BWD_THREADS, GSR_BWD_CTAS * (128 / GSR_BWD
       float slo, shi;                                                                                     \
       upk2(a0, slo, shi);                                                                                 \
       const float sum = slo + shi;                                                                        \
-      atomicAdd(acc_col + (size_t)lds32u<0>(aIdMine) * 12, sum);                                          \
+      asm volatile("red.global.add.f32 [%0], %1;" ::"l"(acc_col + (unsigned long long)lds32u<0>(aIdMine) * 48ull), \
+                   "f"(sum) : "memory");                                                                  \
     }                                                                                                     \
     __syncwarp();                                                                                         \
     nslot = 0;                                                                                            \

@@ -81,6 +81,12 @@ __device__ __forceinline__ uint32_t keep_u32(uint32_t v) {
   asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v));
   return r;
 }
+// the same for a 64-bit value (a per-lane global pointer the hot loop adds into)
+__device__ __forceinline__ unsigned long long keep_u64(unsigned long long v) {
+  unsigned long long r;
+  asm volatile("mov.b64 %0, %1;" : "=l"(r) : "l"(v));
+  return r;
+}
 template <int OFF>
 __device__ __forceinline__ void sts32u(uint32_t addr, uint32_t v) {
   asm volatile("st.shared.u32 [%0+%1], %2;" : : "r"(addr), "n"(OFF), "r"(v) : "memory");
