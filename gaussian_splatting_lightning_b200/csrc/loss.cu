@@ -166,8 +166,12 @@ namespace {
 constexpr int SS_TX = 32, SS_TY = 32, SS_R = 5;
 constexpr int SS_W2 = SS_TX + 2 * SS_R, SS_H2 = SS_TY + 2 * SS_R;      // derivative-map region 42 x 42
 constexpr int SS_W1 = SS_TX + 4 * SS_R, SS_H1 = SS_TY + 4 * SS_R;      // image region 52 x 52
-constexpr int SS_THREADS = 384;
-constexpr size_t SS_SMEM = (size_t)(2 * SS_H1 * SS_W1 + 5 * SS_H1 * SS_W2 + 3 * SS_H2 * SS_W2) * sizeof(float);
+constexpr int SS_THREADS = 256;
+// the derivative maps (3 x 42 x 42 floats) live in the image region (2 x 52 x 52), which is dead once the horizontal sums
+// are taken: 65.3 KB per CTA, THREE CTAs of 256 threads per SM (86.5 KB and 2 x 384 threads before: the six barrier-
+// separated phases of a CTA leave the SM to the other CTAs while it waits)
+constexpr size_t SS_SMEM = (size_t)(2 * SS_H1 * SS_W1 + 5 * SS_H1 * SS_W2) * sizeof(float);
+static_assert(3 * SS_H2 * SS_W2 <= 2 * SS_H1 * SS_W1, "the derivative maps must fit into the image region");
 
 __constant__ float kGauss[11] = {0.001028380123898387f, 0.0075987582094967365f, 0.036000773310661316f,
                                  0.10936068743467331f,  0.21300552785396576f,   0.26601171493530273f,
@@ -186,7 +190,7 @@ constexpr int SS_N1 = SS_H1 * SS_W1, SS_NH = SS_H1 * SS_W2, SS_N2 = SS_H2 * SS_W
 struct SsimLossWeights { float w_l1, w_ssim, w_const, inv_n_l1; };
 
 template <bool GRAD>
-__global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* __restrict__ img1,
+__global__ void __launch_bounds__(SS_THREADS, 3) fused_ssim_kernel(const float* __restrict__ img1,
                                                                 const float* __restrict__ img2, int H, int W, float C1,
                                                                 float C2, int valid, float inv_n,
                                                                 const SsimLossWeights lw, float* __restrict__ dL_dimg1,
@@ -198,7 +202,7 @@ __global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* 
   float2* hA = reinterpret_cast<float2*>(smem + 2 * SS_N1);         // [52][42] (sum x, sum y)
   float2* hB = hA + SS_NH;                                          // [52][42] (sum xx, sum yy)
   float* hC = reinterpret_cast<float*>(hB + SS_NH);                 // [52][42] sum xy
-  float2* pA = reinterpret_cast<float2*>(hC + SS_NH);               // [42][42] w (dm/dmu1, dm/ds11)
+  float2* pA = reinterpret_cast<float2*>(smem);                     // [42][42] w (dm/dmu1, dm/ds11): over sxy, after step 2
   float* pC = reinterpret_cast<float*>(pA + SS_N2);                 // [42][42] w dm/ds12
   const int tid = threadIdx.x;
   const int x0 = blockIdx.x * SS_TX, y0 = blockIdx.y * SS_TY;
@@ -210,7 +214,8 @@ __global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* 
   for (int k = 0; k < 11; ++k) g[k] = kGauss[k];
 
   // 1. the two images on the tile + 10-pixel halo (zero outside the image); all of a thread's loads are issued
-  //    before the first store so that their latencies overlap
+  //    before the first store so that their latencies overlap.  The L1 term is taken here, from the tile's own pixels.
+  float local = 0.f, local_l1 = 0.f;
   {
     constexpr int IT = (SS_N1 + SS_THREADS - 1) / SS_THREADS;
     float2 t[IT];
@@ -227,6 +232,9 @@ __global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* 
     for (int k = 0; k < IT; ++k) {
       const int i = tid + k * SS_THREADS;
       if (i < SS_N1) sxy[i] = t[k];
+      const int r = i / SS_W1, c = i - r * SS_W1;
+      const bool centre = i < SS_N1 && r >= 2 * SS_R && r < 2 * SS_R + SS_TY && c >= 2 * SS_R && c < 2 * SS_R + SS_TX;
+      if (centre) local_l1 += fabsf(t[k].x - t[k].y);     // zero outside the image
     }
   }
   __syncthreads();
@@ -262,7 +270,6 @@ __global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* 
   }
   __syncthreads();
   // 3. vertical sums -> statistics -> m and its three partial derivatives: a thread owns 3 consecutive rows of one column
-  float local = 0.f, local_l1 = 0.f;
   for (int it = tid; it < (SS_H2 / 3) * SS_W2; it += SS_THREADS) {
     const int rs = it / SS_W2, c = it - rs * SS_W2, r0 = rs * 3;
     f32x2 vA[13], vB[13];
@@ -302,10 +309,6 @@ __global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* 
       const float m = CD * rAB;
       const bool centre = r >= SS_R && r < SS_R + SS_TY && c >= SS_R && c < SS_R + SS_TX;
       if (centre && counted) local += m;
-      if (centre && in_img) {
-        const float2 px = sxy[(r + SS_R) * SS_W1 + c + SS_R];
-        local_l1 += fabsf(px.x - px.y);
-      }
       if (GRAD) {
         const float wgt = counted ? inv_n : 0.f;
         const float wm = wgt * m;                                     // w C D / (A B)
@@ -370,7 +373,8 @@ __global__ void __launch_bounds__(SS_THREADS, 2) fused_ssim_kernel(const float* 
         if (y < H && x < W) {
           float t0, t1;
           upk2(t01, t0, t1);
-          const float2 px = sxy[(r0 + j + 2 * SS_R) * SS_W1 + c + 2 * SS_R];
+          // the pixel itself: from global memory again (an L2 hit; its shared-memory copy holds the derivative maps now)
+          const float2 px = make_float2(__ldg(a + (size_t)y * W + x), __ldg(b + (size_t)y * W + x));
           const float dss = t0 + 2.f * px.x * t1 + px.y * t2;          // d ssim / d x
           const float d = px.x - px.y;
           const float sg = (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f);
